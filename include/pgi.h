@@ -1,0 +1,149 @@
+/* pgi.h — C ABI of the B200-native find_mems hot path (libpgi.so).
+ *
+ * This is the drop-in boundary. The reference (parsaeskandar/pangenome-index)
+ * has no FFI layer of its own: its surface is the C++ classes panindexer::FastLocate / TagArray and
+ * the header-only find_all_mems. Each entry point below names the reference interface it replaces
+ * (file:line relative to the reference tree). Host C++ (the facade in pangenome-index_b200/host/)
+ * and the Python test/bench harness call ONLY these functions; all CUDA lives behind them.
+ *
+ * Conventions: plain pointers and sizes, no C++ or torch types; every function returns 0 on success
+ * or a negative pgi_status; the message of the last failure on the calling thread is available from
+ * pgi_last_error(). No exception crosses this boundary. There is NO CPU fallback: every compute
+ * entry point fails with PGI_ENODEVICE when no CUDA device is usable.
+ */
+#ifndef PGI_H
+#define PGI_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    PGI_OK = 0,
+    PGI_EINVAL = -1,     /* bad argument */
+    PGI_EFORMAT = -2,    /* file is not a FastLocate .ri / tags file, or is corrupt / unsupported */
+    PGI_ENODEVICE = -3,  /* no usable CUDA device */
+    PGI_ECUDA = -4,      /* CUDA runtime error (message in pgi_last_error) */
+    PGI_ENOMEM = -5
+} pgi_status;
+
+/* Tag file layouts. */
+enum { PGI_TAGS_SDSL_COMPACT = 0,   /* TagArray::load_compressed_tags_compact, src/tag_arrays.cpp:766-776 */
+       PGI_TAGS_BYTECODE_LEN = 1 }; /* TagArray::load_compressed_tags,         src/tag_arrays.cpp:739-763 */
+
+/* Opaque device-resident index: the flattened r-index (+ optional tag arrays) on one GPU.
+ * Immutable after creation; any number of host threads may query it concurrently. */
+typedef struct pgi_index pgi_index;
+
+/* Opaque reusable batch context: one CUDA stream + grow-only device / pinned-host work buffers. */
+typedef struct pgi_batch pgi_batch;
+
+/* struct MEM, include/pangenome_index/algorithm.hpp:644-651 (end is exclusive). */
+typedef struct { uint64_t start, end, bwt_start; int64_t size; } pgi_mem;
+
+/* FastLocate::bi_interval, include/pangenome_index/r-index.hpp:118-130. */
+typedef struct { uint64_t forward, reverse; int64_t size; } pgi_bi_interval;
+
+/* Result of one batch, in read order; MEMs of a read in discovery order.
+ * Pointers are HOST pointers (pinned) for pgi_find_mems / pgi_batch_fetch, DEVICE pointers for
+ * pgi_batch_device_result. They stay valid until the next run on the same batch or its destruction
+ * (pgi_find_mems: until pgi_result_free). */
+typedef struct {
+    uint64_t n_reads, n_mems, n_tags;
+    uint64_t *mem_off;   /* n_reads + 1 : MEMs of read i are mems[mem_off[i] .. mem_off[i+1])            */
+    pgi_mem  *mems;      /* n_mems                                                                      */
+    uint64_t *tag_off;   /* n_mems + 1  : tags of MEM m are tags[tag_off[m] .. tag_off[m+1])            */
+    uint64_t *tags;      /* n_tags      : sorted unique encoded graph positions (node<<11|rev<<10|off)  */
+    uint64_t *n_runs;    /* n_mems      : the reference's number_of_runs out-parameter                  */
+    uint64_t extensions; /* FMD extensions executed (work counter; equals the oracle's E)               */
+    void *owner;         /* internal */
+} pgi_result;
+
+/* Index facts (pgi_index_info). */
+typedef struct {
+    uint64_t n;              /* FastLocate::bwt_size(), r-index.hpp:337 */
+    uint64_t sigma;          /* C.size() */
+    uint64_t is_encoded;     /* file had ENCODED_BLOCKS (flag bit 0) */
+    uint64_t n_ref_blocks;   /* ones in blocks_start_pos */
+    uint64_t n_runs;         /* logical runs in the file */
+    uint64_t n_dev_blocks;   /* 64-byte device run blocks */
+    uint64_t dir_shift;      /* log2 of the positions covered by one block-directory bucket */
+    uint64_t has_quirk_slot; /* legacy file with an absent nuc symbol */
+    uint64_t has_tags, tag_layout, tag_runs, tag_items, tag_item_width, tag_universe;
+    uint64_t device_bytes;   /* bytes of HBM held by the index */
+    uint64_t C[8];
+    uint8_t  sym_map[256];
+} pgi_index_info_t;
+
+const char *pgi_last_error(void);
+int pgi_device_count(void);   /* number of CUDA devices (0 when none / no driver) */
+
+/* Replaces FastLocate::load_encoded (src/r-index.cpp:406-459; falls back to the legacy layout of
+ * FastLocate::load :378-404 when flag bit 0 is clear) + TagArray::load_compressed_tags_compact /
+ * load_compressed_tags, and flattens both into the device layout on GPU `device`.
+ * tag_bytes may be NULL (MEM finding only). The input buffers are not retained. */
+int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
+                     int tag_layout, int device, pgi_index **out);
+/* Replica of an index on another GPU (device-to-device copy over NVLink; no host round trip). */
+int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **out);
+void pgi_index_free(pgi_index *);
+int pgi_index_info(const pgi_index *, pgi_index_info_t *out);
+
+/* Batched FastLocate::backward_extend_encoded (src/r-index.cpp:713-756) / forward_extend_encoded
+ * (:758-764): out[i] = extend(in[i], sym[i]); dir[i] 0 = backward, 1 = forward. Host buffers. */
+int pgi_extend_batch(pgi_index *, uint64_t n, const pgi_bi_interval *in, const uint8_t *sym,
+                     const uint8_t *dir, pgi_bi_interval *out);
+/* Batched FastLocate::rank_at_cached_encoded (src/r-index.cpp:619-641): out8[8*i + j] = R(pos[i])[j], j < sigma. */
+int pgi_rank_batch(pgi_index *, uint64_t n, const uint64_t *pos, uint64_t *out8);
+/* Batched TagArray::query_compressed_compact (src/tag_arrays.cpp:856-890) / query_compressed (:780-854),
+ * chosen by the layout the index was created with. Intervals are [start[i], end[i]] inclusive.
+ * Result: tag_off / tags / n_runs of `out` (n_mems = n; mems, mem_off are NULL). Free with pgi_result_free. */
+int pgi_tag_query_batch(pgi_index *, uint64_t n, const uint64_t *start, const uint64_t *end, pgi_result *out);
+
+/* The hot path: for every read, find_all_mems (include/pangenome_index/algorithm.hpp:739-757) and,
+ * when the index has tags, the tag query of src/find_mems.cpp:128 for every MEM.
+ * reads = concatenated read bytes, read i = reads[read_off[i] .. read_off[i+1]). HOST buffers (pinned
+ * recommended); host->device and device->host copies happen inside. cuda_stream: a cudaStream_t or NULL
+ * (library-owned stream). Blocks until the result is complete in host memory. Free with pgi_result_free. */
+int pgi_find_mems(pgi_index *, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                  uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out);
+void pgi_result_free(pgi_result *);
+
+/* Explicit batch contexts, for callers that pipeline several batches per GPU (the find_mems driver)
+ * or keep inputs / results resident in HBM (bench.py's device-resident figure). */
+int pgi_batch_create(pgi_index *, void *cuda_stream /* or NULL */, pgi_batch **out);
+void pgi_batch_free(pgi_batch *);
+/* Asynchronously stage host reads into the batch's device buffers (pinned source recommended). */
+int pgi_batch_upload(pgi_batch *, const char *reads, const uint64_t *read_off, uint64_t n_reads);
+/* Use reads already resident in device memory (d_reads must be readable up to the next multiple of 8 bytes). */
+int pgi_batch_set_device_reads(pgi_batch *, const char *d_reads, const uint64_t *d_read_off,
+                               uint64_t n_reads, uint64_t total_bytes);
+/* Run MEM finding + tag lookup on the staged reads; results stay in HBM. Returns after the last kernel
+ * has completed (it has to read sizes back to size the next stage). */
+int pgi_batch_run(pgi_batch *, uint64_t min_len, uint64_t min_occ);
+/* Device pointers of the last run's result. */
+int pgi_batch_device_result(pgi_batch *, pgi_result *out);
+/* Copy the last run's result into the batch's pinned host buffers and wait for it. */
+int pgi_batch_fetch(pgi_batch *, pgi_result *out);
+/* Device time of the stages of the last run, from CUDA events on the batch's stream, in milliseconds:
+ * [0] MEM kernel (fmd_mem_kernel), [1] MEM ordering (scan + scatter), [2] tag sizing, [3] tag decode + sort,
+ * [4] tag unique + compaction, [5] whole run, [6] number of kernel launches in the run, [7] MEM kernel re-runs. */
+int pgi_batch_stage_ms(pgi_batch *, double ms[8]);
+
+/* Text of src/find_mems.cpp:115-139 (+ tag lines of src/tag_arrays.cpp:885-889) for a host result;
+ * sequence numbers start at first_seq. Host-side formatting (no GPU work). Returns a malloc'd buffer
+ * (free with pgi_free), length in *len. with_tags = 0 omits the two tag lines per MEM. */
+char *pgi_format_text(const pgi_result *, uint64_t first_seq, int with_tags, uint64_t *len);
+void pgi_free(void *);
+
+/* M1 microbenchmark: independent random `bytes_per_access`-byte (32, 64 or 128) gathers
+ * over a buffer of buf_bytes on `device`; returns GB/s of useful bytes in *gbs. The random-access roofline. */
+int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t bytes_per_access, uint64_t n_access,
+                          int chain /* dependent chain length per thread, >= 1 */, double *gbs);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,380 @@
+// pgi_flatten.hpp — host side of the index: parse the reference's on-disk files and flatten them
+// into the device layout (DESIGN.md "Data layout in HBM"). Pure C++17, no CUDA, no SDSL/GBWT.
+//
+// Replaces (reference file:line):
+//   FastLocate::load_encoded / load            src/r-index.cpp:406-459 / :378-404
+//   Run_blocks::load                           include/pangenome_index/r-index.hpp:283-292
+//   EncodedBlock stream grammar                src/r-index.cpp:65-156
+//   TagArray::load_compressed_tags_sdsl        src/tag_arrays.cpp:766-776
+//   TagArray::load_compressed_tags             src/tag_arrays.cpp:739-763
+// The SDSL containers (int_vector, bit_vector, sd_vector + its two select supports) and
+// gbwt::ByteCode are read straight from their serialized form.
+//
+// Nothing here answers queries on the CPU: the output is a set of flat arrays that pgi_capi.cu
+// uploads; all query arithmetic is in pgi_core.cuh and runs on the GPU.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "pgi_layout.h"
+
+namespace pgi {
+
+struct FormatError : std::runtime_error { using std::runtime_error::runtime_error; };
+
+// ---------------------------------------------------------------------------------- byte reader
+class Reader {
+public:
+    Reader(const void *p, size_t n) : base_((const uint8_t *) p), len_(n), off_(0) {}
+    size_t tell() const { return off_; }
+    size_t remaining() const { return len_ - off_; }
+    const uint8_t *take(size_t n) {
+        if (n > len_ - off_) throw FormatError("truncated file at byte " + std::to_string(off_));
+        const uint8_t *r = base_ + off_; off_ += n; return r;
+    }
+    template <typename T> T get() { T v; std::memcpy(&v, take(sizeof(T)), sizeof(T)); return v; }
+private:
+    const uint8_t *base_; size_t len_, off_;
+};
+
+// A serialized sdsl::int_vector viewed in place (payload words are not copied).
+struct IntVectorView {
+    uint64_t bits = 0; unsigned width = 0; const uint8_t *payload = nullptr;
+    // fixed == 0 -> int_vector<0> (width byte present)
+    void parse(Reader &r, unsigned fixed) {
+        bits = r.get<uint64_t>();
+        width = fixed ? fixed : r.get<uint8_t>();
+        payload = r.take((size_t) ((bits + 63) / 64) * 8);
+    }
+    uint64_t size() const { return width ? bits / width : 0; }
+    uint64_t word(uint64_t w) const { uint64_t v; std::memcpy(&v, payload + 8 * w, 8); return v; }
+    uint64_t at(uint64_t i) const {
+        uint64_t b = i * width, w = b >> 6; unsigned s = (unsigned) (b & 63);
+        uint64_t v = word(w) >> s;
+        if (s + width > 64) v |= word(w + 1) << (64 - s);
+        return width >= 64 ? v : v & ((1ULL << width) - 1);
+    }
+};
+
+inline void skip_select_support(Reader &r) {
+    uint64_t cnt = r.get<uint64_t>();
+    if (!cnt) return;
+    IntVectorView v; v.parse(r, 0); v.parse(r, 1);
+    for (uint64_t i = 0, sb = (cnt + 4095) / 4096; i < sb; ++i) v.parse(r, 0);
+}
+
+// A serialized sdsl::sd_vector<> viewed in place; enumerates its 1-positions in increasing order.
+struct SdVectorView {
+    uint64_t size = 0; unsigned wl = 0; IntVectorView low, high; uint64_t ones = 0;
+    void parse(Reader &r) {
+        size = r.get<uint64_t>(); wl = r.get<uint8_t>();
+        low.parse(r, 0); high.parse(r, 1);
+        skip_select_support(r); skip_select_support(r);
+        ones = 0;
+        for (uint64_t w = 0, nw = (high.bits + 63) / 64; w < nw; ++w) {
+            uint64_t x = high.word(w);
+            if ((w + 1) * 64 > high.bits) x &= (high.bits & 63) ? ((1ULL << (high.bits & 63)) - 1) : ~0ULL;
+            ones += (uint64_t) __builtin_popcountll(x);
+        }
+        if (wl && low.size() != ones) throw FormatError("sd_vector: low/high parts disagree");
+    }
+    template <typename F> void for_each_one(F &&f) const {
+        uint64_t j = 0;
+        for (uint64_t w = 0, nw = (high.bits + 63) / 64; w < nw; ++w) {
+            uint64_t x = high.word(w);
+            if ((w + 1) * 64 > high.bits) x &= (high.bits & 63) ? ((1ULL << (high.bits & 63)) - 1) : ~0ULL;
+            while (x) {
+                unsigned b = (unsigned) __builtin_ctzll(x); x &= x - 1;
+                uint64_t hi = w * 64 + b - j;
+                f(j, (hi << wl) | (wl ? low.at(j) : 0));
+                ++j;
+            }
+        }
+    }
+};
+
+// gbwt::ByteCode value at p (7 data bits per byte, low group first, bit 7 = continue).
+inline uint64_t bytecode_next(const uint8_t *&p, const uint8_t *end) {
+    uint64_t v = 0; unsigned sh = 0;
+    for (;;) {
+        if (p >= end) throw FormatError("ByteCode value runs past the end of its stream");
+        uint8_t b = *p++;
+        if (sh < 64) v |= (uint64_t) (b & 0x7F) << sh;
+        sh += 7;
+        if (!(b & 0x80)) return v;
+    }
+}
+
+// ---------------------------------------------------------------------------------- flat images
+struct RiImage {
+    RiConsts k;                          // scalars + tables copied to the device as one struct
+    std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte run block
+    std::vector<uint64_t> dir;           // block directory, (n >> dir_shift) + 2 entries
+    std::vector<uint64_t> q_start, q_val;// quirk slot tables (legacy files with an absent nuc symbol)
+    uint64_t n_file_runs = 0, n_ref_blocks = 0; bool encoded = false;
+};
+struct SparseRankImage {
+    SparseRankConsts k; std::vector<uint64_t> dir; std::vector<uint8_t> low;
+};
+struct TagImage {
+    int layout = 0; SparseRankImage intervals;
+    std::vector<uint64_t> starts;        // select_1(j + 1) of encoded_runs_starts_sd
+    uint64_t n_items = 0; unsigned width = 0;
+    std::vector<uint64_t> words;         // sdsl-compact items, bit-packed exactly as in the file
+    std::vector<uint8_t> stream;         // ByteCode layout
+    bool starts_regular = false;         // starts[j] == 10 j for every j (lookup collapses to arithmetic)
+};
+
+static const unsigned char kNuc[6] = {'\n', 'A', 'C', 'G', 'N', 'T'};   // include/pangenome_index/utils.hpp:11
+
+// ---------------------------------------------------------------------------------- run blocks
+// Packs (code, length) runs into 64-byte device blocks of PGI_RUNS_PER_BLOCK entries (pgi_layout.h).
+class BlockBuilder {
+public:
+    explicit BlockBuilder(std::vector<uint64_t> &out) : out_(out) {}
+    uint64_t cum[6] = {0, 0, 0, 0, 0, 0}; uint64_t pos = 0;      // state of the emitted entries
+    uint64_t lcum[6] = {0, 0, 0, 0, 0, 0}; uint64_t lpos = 0;    // state of the runs added so far
+    std::vector<uint64_t> starts;        // start position of every emitted block
+    void add(unsigned code, uint64_t len) {
+        if (!len) return;
+        lcum[code] += len; lpos += len;
+        if (code == pcode_) { plen_ += len; return; }
+        flush_pending(); pcode_ = code; plen_ = len;
+    }
+    void finish() { flush_pending(); if (ne_) emit(); }
+private:
+    std::vector<uint64_t> &out_; unsigned pcode_ = 8; uint64_t plen_ = 0;
+    uint64_t bstart_ = 0, bcum_[6]; uint16_t ent_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
+    void flush_pending() {
+        while (plen_) {
+            uint64_t t = plen_ < PGI_MAX_RUN_ENTRY ? plen_ : PGI_MAX_RUN_ENTRY;
+            if (!ne_) { bstart_ = pos; std::memcpy(bcum_, cum, sizeof(cum)); }
+            ent_[ne_++] = (uint16_t) (pcode_ | (t << 3));
+            cum[pcode_] += t; pos += t; plen_ -= t;
+            if (ne_ == PGI_RUNS_PER_BLOCK) emit();
+        }
+    }
+    void emit() {
+        if (bstart_ >> 40 || bcum_[1] >> 40 || bcum_[2] >> 40 || bcum_[3] >> 40 || bcum_[5] >> 40)
+            throw FormatError("index longer than 2^40 positions is not supported by the device layout");
+        if (bcum_[0] >> 32 || bcum_[4] >> 32)
+            throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
+        uint64_t r[4] = {0, 0, 0, 0};   // 15 x 16-bit entries = 240 bits, starting at bit 16 of word 4
+        for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) {
+            uint64_t e = i < ne_ ? ent_[i] : 0; unsigned bit = 16 + 16 * i;
+            r[bit >> 6] |= e << (bit & 63);
+        }
+        const uint64_t A = bcum_[1], C = bcum_[2], G = bcum_[3], T = bcum_[5], NL = bcum_[0], N = bcum_[4];
+        uint64_t w[PGI_BLOCK_WORDS];
+        w[0] = bstart_ | (A << 40);                       // start(40) | A[0..24)
+        w[1] = (A >> 24) | (C << 16);                     // A[24..40) | C(40) | 8 spare bits
+        w[2] = G | (T << 40);                             // G(40) | T[0..24)
+        w[3] = (T >> 24) | (NL << 16) | (N << 48);        // T[24..40) | NL(32) | N[0..16)
+        w[4] = (N >> 16) | r[0];                          // N[16..32) | runs 0..2
+        w[5] = r[1]; w[6] = r[2]; w[7] = r[3];
+        out_.insert(out_.end(), w, w + PGI_BLOCK_WORDS);
+        starts.push_back(bstart_);
+        ne_ = 0;
+    }
+};
+
+inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, uint64_t n) {
+    const uint64_t nb = starts.size();
+    if (nb == 0) throw FormatError("r-index has no runs");
+    if (nb >> 32) throw FormatError("too many run blocks for the 32-bit block directory");
+    // about two directory buckets per block: most buckets then hold at most one block boundary
+    unsigned S = 0;
+    while (S < 31 && (n >> (S + 1)) >= 2 * nb) ++S;
+    const uint64_t nbuckets = (n >> S) + 1;
+    im.k.dir_shift = S; im.k.n_blocks = nb;
+    im.dir.assign(nbuckets + 1, 0);
+    uint64_t idx = 0;
+    for (uint64_t b = 0; b <= nbuckets; ++b) {
+        const uint64_t lo = b << S;
+        while (idx + 1 < nb && starts[idx + 1] <= lo) ++idx;
+        uint64_t off = 0xFFFFFFFFull;
+        if (idx + 1 < nb && starts[idx + 1] - lo < (1ULL << S)) off = starts[idx + 1] - lo;
+        im.dir[b] = idx | (off << 32);
+    }
+}
+
+// Per-byte extension descriptors: SURVEY.md App. B2/B3 folded into weights over true ranks
+// (DESIGN.md "Quirk-exact extension"). slot[i] says where R(pos)[i] comes from.
+inline void build_descriptors(RiImage &im, const bool present[6], bool legacy) {
+    RiConsts &k = im.k;
+    const unsigned sigma = (unsigned) k.sigma;
+    unsigned slot[8];
+    for (unsigned i = 0; i < 8; ++i) slot[i] = PGI_SRC_ZERO;
+    k.has_quirk = 0;
+    for (unsigned i = 0; i < sigma && i < 6; ++i) {
+        if (legacy) {
+            // R[i] = cnt_b(nuc[i], rel) + cum_b[sym_map[nuc[i]]]          (r-index.cpp:593-603)
+            if (present[i]) slot[i] = i; else { slot[i] = PGI_SRC_QUIRK; k.has_quirk = 1; }
+        } else {
+            // R[i] = full[sym_map[nuc[i]]], full[c] = true rank of nuc[c] or 0 when absent (r-index.cpp:619-641, 65-82)
+            unsigned col = k.sym_map[kNuc[i]];
+            slot[i] = (col < 6 && present[col]) ? col : PGI_SRC_ZERO;
+        }
+    }
+    uint8_t comp[256];
+    for (int i = 0; i < 256; ++i) comp[i] = (uint8_t) i;                   // r-index.cpp:1512-1529
+    comp['A'] = 'T'; comp['C'] = 'G'; comp['G'] = 'C'; comp['T'] = 'A';
+    comp['a'] = 't'; comp['c'] = 'g'; comp['g'] = 'c'; comp['t'] = 'a';
+    uint32_t desc[256];
+    for (int a = 0; a < 256; ++a) {
+        unsigned w[8] = {0, 0, 0, 0, 0, 0, 0, 0};                          // weights per source
+        const unsigned ci = k.sym_map[comp[a]];
+        for (unsigned b = 0; b < 6 && k.sym_map[kNuc[b]] < ci; ++b)         // r-index.cpp:733-740 (a while loop: stops at the first failure)
+            w[slot[k.sym_map[comp[kNuc[b]]]]]++;
+        const unsigned mi = k.sym_map[a];
+        uint32_t d = 0;
+        for (unsigned c = 0; c < 6; ++c) d |= (uint32_t) w[c] << (3 * c);
+        d |= (uint32_t) w[PGI_SRC_QUIRK] << 18;
+        d |= (uint32_t) slot[mi] << 21;
+        d |= (uint32_t) mi << 24;
+        desc[a] = d;
+    }
+    for (int a = 0; a < 256; ++a) { k.desc_b[a] = desc[a]; k.desc_f[a] = desc[comp[a]]; }
+}
+
+// ---------------------------------------------------------------------------------- .ri
+inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
+    Reader r(bytes, len);
+    if (r.get<uint32_t>() != 0x6B3741D8u) throw FormatError("FastLocate: Invalid tag");       // r-index.hpp:85-115
+    uint32_t version = r.get<uint32_t>();
+    if (version != 1) throw FormatError("FastLocate: Expected v1, got v" + std::to_string(version));
+    (void) r.get<uint64_t>();                      // max_length
+    const uint64_t flags = r.get<uint64_t>();
+    IntVectorView iv; SdVectorView sd;
+    iv.parse(r, 0); sd.parse(r); iv.parse(r, 0);   // samples, last, last_to_run: not on the find_mems path
+    iv.parse(r, 8);
+    if (iv.size() != 256) throw FormatError("sym_map must have 256 entries");
+    RiConsts &k = im.k; std::memset(&k, 0, sizeof(k));
+    for (int i = 0; i < 256; ++i) k.sym_map[i] = (uint8_t) iv.at(i);
+    iv.parse(r, 64);
+    k.sigma = iv.size();
+    if (k.sigma < 1 || k.sigma > 6) throw FormatError("alphabet size outside [1,6] is not supported (nuc has 6 symbols)");
+    for (uint64_t i = 0; i < k.sigma; ++i) k.C[i] = iv.at(i);
+    for (int i = 0; i < 256; ++i) if (k.sym_map[i] >= k.sigma) throw FormatError("sym_map entry outside the alphabet");
+    SdVectorView bsp; bsp.parse(r);
+    k.n = r.get<uint64_t>();
+    im.n_ref_blocks = bsp.ones; im.encoded = (flags & 1) != 0;
+    std::vector<uint64_t> ref_starts; ref_starts.reserve(bsp.ones);
+    bsp.for_each_one([&](uint64_t, uint64_t p) { ref_starts.push_back(p); });
+
+    BlockBuilder bb(im.blocks);
+    im.n_file_runs = 0;
+    unsigned code_of[256]; for (int i = 0; i < 256; ++i) code_of[i] = 8;
+    for (unsigned c = 0; c < 6; ++c) code_of[kNuc[c]] = c;
+    auto check_block = [&](uint64_t b, const uint64_t *file_cum, unsigned ncum) {
+        if (b >= ref_starts.size() || ref_starts[b] != bb.lpos) throw FormatError("blocks_start_pos disagrees with the run blocks");
+        for (unsigned c = 0; c < 6; ++c) {           // file cumulatives are in sym_map order; ours are per nuc code
+            if (!bb.lcum[c]) continue;               // an absent symbol has no column of its own
+            unsigned col = k.sym_map[kNuc[c]];
+            if (col >= ncum || file_cum[col] != bb.lcum[c]) throw FormatError("block cumulative counts disagree with the runs");
+        }
+    };
+    if (!im.encoded) {
+        const uint64_t nblk = r.get<uint64_t>();
+        for (uint64_t b = 0; b < nblk; ++b) {
+            IntVectorView cum; cum.parse(r, 64);
+            uint64_t fc[8] = {0}; unsigned nc = (unsigned) (cum.size() < 8 ? cum.size() : 8);
+            for (unsigned i = 0; i < nc; ++i) fc[i] = cum.at(i);
+            const uint64_t nr = r.get<uint64_t>();
+            if (nr) { check_block(b, fc, nc); im.q_val.push_back(fc[0]); }
+            for (uint64_t j = 0; j < nr; ++j) {
+                uint64_t sym = r.get<uint64_t>(), l = r.get<uint64_t>();
+                if (sym > 255 || code_of[sym] > 5) throw FormatError("BWT symbol outside {\\n,A,C,G,N,T} is not supported");
+                bb.add(code_of[sym], l); ++im.n_file_runs;
+            }
+        }
+        im.q_start = ref_starts;
+    } else {
+        const uint64_t ebs = r.get<uint64_t>(); (void) ebs;
+        const bool hasN = r.get<uint8_t>() != 0;
+        const unsigned cum_len = hasN ? 6 : 5;                                  // r-index.cpp:630
+        if (k.sigma != cum_len) throw FormatError("encoded r-index whose alphabet size disagrees with its N flag (unreadable by the reference too)");
+        IntVectorView offs; offs.parse(r, 0);
+        const uint64_t nbytes = r.get<uint64_t>();
+        const uint8_t *stream = r.take(nbytes);
+        const uint64_t nblk = bsp.ones;                                         // blocks without a start bit are never reached
+        if (offs.size() < nblk) throw FormatError("encoded block offsets are shorter than blocks_start_pos");
+        for (uint64_t b = 0; b < nblk; ++b) {
+            const uint8_t *p = stream + offs.at(b);
+            const uint8_t *end = (b + 1 < offs.size()) ? stream + offs.at(b + 1) : stream + nbytes;
+            if (p > end || end > stream + nbytes) throw FormatError("encoded block offsets out of range");
+            uint64_t fc[8] = {0};
+            for (unsigned i = 0; i < cum_len; ++i) fc[i] = bytecode_next(p, end);
+            check_block(b, fc, cum_len);
+            while (p < end) {
+                uint8_t h = *p++; unsigned code = h >> 5; uint64_t l = (h & 31) + 1;
+                if ((h & 31) == 31) l = 32 + bytecode_next(p, end);
+                if (code > 5) throw FormatError("encoded run with symbol code > 5");
+                bb.add(code, l); ++im.n_file_runs;
+            }
+        }
+    }
+    bb.finish();
+    if (bb.pos != k.n) throw FormatError("run lengths do not add up to the BWT size");
+    bool present[6]; for (unsigned c = 0; c < 6; ++c) present[c] = bb.cum[c] != 0;
+    // totals of every nuc code = R(pos >= n)
+    build_block_dir(im, bb.starts, k.n);
+    build_descriptors(im, present, !im.encoded);
+    if (!k.has_quirk) { im.q_start.clear(); im.q_val.clear(); }
+    k.n_quirk = im.q_start.size();
+    k.mem_tail = r.remaining();   // bytes after the index (0 for a well-formed file)
+}
+
+// ---------------------------------------------------------------------------------- sparse rank
+// Sorted set of positions in [0, size) -> bucket directory + per-element low parts.
+inline void build_sparse_rank(const SdVectorView &sd, SparseRankImage &im) {
+    SparseRankConsts &k = im.k; std::memset(&k, 0, sizeof(k));
+    k.size = sd.size; k.m = sd.ones;
+    unsigned S = 0;                              // about four elements per bucket
+    if (sd.ones) while (S < 62 && (sd.size >> S) > sd.ones / 4 + 1) ++S;
+    else S = 62;
+    k.shift = S; k.low_bytes = S <= 8 ? 1 : S <= 16 ? 2 : S <= 32 ? 4 : 8;
+    const uint64_t nbuckets = (sd.size >> S) + 1;
+    im.dir.assign(nbuckets + 1, 0);
+    im.low.assign((size_t) (sd.ones * k.low_bytes + 16), 0);   // 16 spare bytes: vector loads may over-read
+    uint64_t prev = 0; bool first = true;
+    sd.for_each_one([&](uint64_t j, uint64_t p) {
+        if (p >= sd.size || (!first && p <= prev)) throw FormatError("sd_vector positions are not strictly increasing inside the universe");
+        first = false; prev = p;
+        im.dir[(p >> S) + 1]++;
+        uint64_t lowv = p & ((S >= 64) ? ~0ULL : ((1ULL << S) - 1));
+        std::memcpy(&im.low[(size_t) (j * k.low_bytes)], &lowv, k.low_bytes);
+    });
+    for (uint64_t b = 0; b < nbuckets; ++b) im.dir[b + 1] += im.dir[b];
+    k.n_buckets = nbuckets;
+}
+
+// ---------------------------------------------------------------------------------- tags
+inline void flatten_tags(const void *bytes, size_t len, int layout, TagImage &im) {
+    Reader r(bytes, len);
+    im.layout = layout;
+    if (layout == 0) {
+        IntVectorView items; items.parse(r, 0);
+        if (items.width == 0 || items.width > 64) throw FormatError("tag item width outside [1,64]");
+        im.n_items = items.size(); im.width = items.width;
+        size_t nw = (size_t) ((items.bits + 63) / 64);
+        im.words.assign(nw + 2, 0);
+        std::memcpy(im.words.data(), items.payload, nw * 8);
+    } else if (layout == 1) {
+        uint64_t nbytes = r.get<uint64_t>();
+        const uint8_t *p = r.take(nbytes);
+        im.stream.assign(p, p + nbytes);
+        im.n_items = nbytes; im.width = 8;
+        im.stream.resize((size_t) nbytes + 16, 0);      // reads past the end see zero bytes (defined UB)
+    } else throw FormatError("unknown tag layout");
+    SdVectorView starts; starts.parse(r);
+    im.starts.reserve(starts.ones);
+    im.starts_regular = layout == 0;
+    starts.for_each_one([&](uint64_t j, uint64_t p) { im.starts.push_back(p); if (p != 10 * j) im.starts_regular = false; });
+    SdVectorView iv; iv.parse(r);
+    build_sparse_rank(iv, im.intervals);
+}
+
+} // namespace pgi

@@ -1,0 +1,96 @@
+// TEST INFRASTRUCTURE ONLY — not part of the product library.
+//
+// Compiles the product's device arithmetic (pangenome-index_b200/csrc/pgi_core.cuh, PGI_HD empty) and
+// its host flattener as plain C++ so that, on the GPU-less build box, `pytest -m "not gpu"` can check
+// the flattened layout, the lane state machine and the tag plan against the oracle step by step.
+// libpgi.so never contains or calls this code; the GPU tests exercise the same header through the kernels.
+#include "../../pangenome-index_b200/csrc/pgi_flatten.hpp"
+#include "../../pangenome-index_b200/csrc/pgi_core.cuh"
+#include <algorithm>
+#include <cstdlib>
+#include <string>
+
+using namespace pgi;
+
+struct sim_index { RiImage ri; TagImage tg; bool has_tags = false; RiDev rd; TagDev td; };
+static thread_local std::string g_err;
+
+static void bind(sim_index *s) {
+    RiDev &d = s->rd; const RiImage &im = s->ri;
+    d.blocks = im.blocks.data(); d.dir = im.dir.data();
+    d.q_start = im.q_start.empty() ? nullptr : im.q_start.data(); d.q_val = im.q_val.empty() ? nullptr : im.q_val.data();
+    d.n = im.k.n; d.n_blocks = im.k.n_blocks; d.n_quirk = im.k.n_quirk; d.dir_shift = im.k.dir_shift; d.has_quirk = im.k.has_quirk;
+    for (int i = 0; i < 8; ++i) d.C[i] = im.k.C[i];
+    if (s->has_tags) {
+        TagDev &t = s->td; const TagImage &g = s->tg;
+        t.iv.dir = g.intervals.dir.data(); t.iv.low = g.intervals.low.data();
+        t.iv.size = g.intervals.k.size; t.iv.m = g.intervals.k.m; t.iv.shift = g.intervals.k.shift; t.iv.low_bytes = g.intervals.k.low_bytes;
+        t.starts = g.starts.data(); t.n_starts = g.starts.size();
+        t.words = g.words.data(); t.stream = g.stream.data(); t.n_items = g.n_items;
+        t.width = g.width; t.layout = (uint32_t) g.layout; t.starts_regular = g.starts_regular; t.pad = 0;
+    }
+}
+
+extern "C" {
+const char *sim_last_error() { return g_err.c_str(); }
+sim_index *sim_create(const void *ri, uint64_t ri_len, const void *tg, uint64_t tg_len, int layout) {
+    try {
+        sim_index *s = new sim_index();
+        flatten_ri(ri, ri_len, s->ri);
+        if (tg && tg_len) { flatten_tags(tg, tg_len, layout, s->tg); s->has_tags = true; }
+        bind(s);
+        return s;
+    } catch (const std::exception &e) { g_err = e.what(); return nullptr; }
+}
+void sim_free(sim_index *s) { delete s; }
+// info: n, sigma, n_blocks, dir_shift, has_quirk, n_file_runs, n_ref_blocks, encoded, tag m, tag shift, tag low_bytes, starts_regular
+void sim_info(const sim_index *s, uint64_t *info) {
+    info[0] = s->ri.k.n; info[1] = s->ri.k.sigma; info[2] = s->ri.k.n_blocks; info[3] = s->ri.k.dir_shift; info[4] = s->ri.k.has_quirk;
+    info[5] = s->ri.n_file_runs; info[6] = s->ri.n_ref_blocks; info[7] = s->ri.encoded;
+    info[8] = s->has_tags ? s->tg.intervals.k.m : 0; info[9] = s->has_tags ? s->tg.intervals.k.shift : 0;
+    info[10] = s->has_tags ? s->tg.intervals.k.low_bytes : 0; info[11] = s->has_tags ? s->tg.starts_regular : 0;
+}
+void sim_extend_batch(const sim_index *s, uint64_t n, const uint64_t *in3, const uint8_t *sym, const uint8_t *dir, uint64_t *out3) {
+    for (uint64_t i = 0; i < n; ++i) {
+        BiInt b{in3[3 * i], in3[3 * i + 1], (int64_t) in3[3 * i + 2]};
+        if (dir[i]) { std::swap(b.k, b.kp); b = extend_desc(s->rd, b, s->ri.k.desc_f[sym[i]]); std::swap(b.k, b.kp); }
+        else b = extend_desc(s->rd, b, s->ri.k.desc_b[sym[i]]);
+        out3[3 * i] = b.k; out3[3 * i + 1] = b.kp; out3[3 * i + 2] = (uint64_t) b.s;
+    }
+}
+// find_all_mems of one read through the lane state machine; returns the MEM count (records of 4 u64 into out, up to cap).
+uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint64_t min_len, uint64_t min_occ, uint64_t *out, uint64_t cap, uint64_t *n_ext) {
+    MemLane L; lane_begin(L, len, min_len, s->rd.n);
+    uint64_t nm = 0, ext = 0;
+    for (;;) {
+        bool need = lane_settle(L, min_len, s->rd.n);
+        if (L.emit) {
+            if (nm < cap) { out[4 * nm] = L.x; out[4 * nm + 1] = L.e; out[4 * nm + 2] = L.k2; out[4 * nm + 3] = (uint64_t) L.s2; }
+            ++nm; L.emit = 0; continue;
+        }
+        if (!need) break;
+        const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
+        if (L.phase == PH_P2) { std::swap(L.b.k, L.b.kp); L.b = extend_desc(s->rd, L.b, s->ri.k.desc_f[a]); std::swap(L.b.k, L.b.kp); }
+        else L.b = extend_desc(s->rd, L.b, s->ri.k.desc_b[a]);
+        ++ext;
+        lane_after_ext(L, min_len, min_occ, s->rd.n);
+    }
+    if (n_ext) *n_ext = ext;
+    return nm;
+}
+// one tag query through tag_plan + item decoders; returns number_of_runs, *n_out sorted unique values written (<= cap)
+uint64_t sim_tag_query(const sim_index *s, uint64_t start, uint64_t end, uint64_t *out, uint64_t cap, uint64_t *n_out) {
+    TagPlan p = tag_plan(s->td, start, end);
+    std::vector<uint64_t> v; v.reserve(p.count);
+    if (s->td.layout == 0) for (uint64_t i = 0; i < p.count; ++i) v.push_back(tag_item_compact(s->td, p.first_item + p.skip + i));
+    else {
+        uint64_t loc = p.first_item;
+        for (uint64_t i = 0; i < p.skip; ++i) (void) tag_bytecode_next(s->td, loc);
+        for (uint64_t i = 0; i < p.count; ++i) v.push_back(tag_value_bytecode(tag_bytecode_next(s->td, loc)));
+    }
+    std::sort(v.begin(), v.end()); v.erase(std::unique(v.begin(), v.end()), v.end());
+    *n_out = v.size();
+    for (size_t i = 0; i < v.size() && i < cap; ++i) out[i] = v[i];
+    return p.n_runs;
+}
+}

@@ -1,0 +1,109 @@
+"""ctypes binding of the CPU oracle (oracle/liborc.so) — test infrastructure; the checker, never the product."""
+import ctypes, os, subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_DIR = os.path.join(ROOT, "oracle")
+_lib = None
+
+class OrcResult(ctypes.Structure):
+    _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
+                ("mem_off", ctypes.POINTER(ctypes.c_uint64)), ("mems", ctypes.POINTER(ctypes.c_uint64)),
+                ("tag_off", ctypes.POINTER(ctypes.c_uint64)), ("tags", ctypes.POINTER(ctypes.c_uint64)),
+                ("n_runs", ctypes.POINTER(ctypes.c_uint64)), ("counters", ctypes.c_uint64 * 8)]
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(_DIR, "liborc.so")
+        if not os.path.exists(path):
+            subprocess.check_call(["make", "-s", "-C", _DIR])
+        L = ctypes.CDLL(path)
+        L.orc_last_error.restype = ctypes.c_char_p
+        L.orc_index_load.restype = ctypes.c_void_p
+        L.orc_index_load.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int,
+                                     ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
+        L.orc_index_free.argtypes = [ctypes.c_void_p]
+        L.orc_index_info.argtypes = [ctypes.c_void_p] * 4
+        L.orc_extend_batch.argtypes = [ctypes.c_void_p, ctypes.c_uint64] + [ctypes.c_void_p] * 4
+        L.orc_rank_batch.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
+        L.orc_tag_query.restype = ctypes.c_uint64
+        L.orc_tag_query.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64,
+                                    ctypes.POINTER(ctypes.c_uint64)]
+        L.orc_find_mems.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64,
+                                    ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OrcResult)]
+        L.orc_result_free.argtypes = [ctypes.POINTER(OrcResult)]
+        L.orc_format_text.restype = ctypes.c_void_p
+        L.orc_format_text.argtypes = [ctypes.POINTER(OrcResult), ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
+        L.orc_free.argtypes = [ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+def _np(ptr, n, dtype=np.uint64):
+    if n == 0:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+class Index:
+    """Oracle index: FastLocate (+ TagArray). tag_layout 0 = sdsl-compact, 1 = ByteCode+len9."""
+    def __init__(self, ri: bytes, tags: bytes = None, tag_layout=0):
+        L = lib(); a = ctypes.c_uint64(); b = ctypes.c_uint64()
+        self.h = L.orc_index_load(ri, len(ri), tags, len(tags) if tags else 0, tag_layout, ctypes.byref(a), ctypes.byref(b))
+        if not self.h:
+            raise RuntimeError(L.orc_last_error().decode())
+        self.ri_consumed, self.tags_consumed = a.value, b.value
+        self.has_tags = bool(tags)
+        info = (ctypes.c_uint64 * 16)(); C = (ctypes.c_uint64 * 8)(); sm = (ctypes.c_uint8 * 256)()
+        L.orc_index_info(self.h, info, C, sm)
+        self.info = list(info); self.n = info[0]; self.sigma = info[1]
+        self.C = list(C)[: self.sigma]; self.sym_map = bytes(sm)
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_index_free(self.h); self.h = None
+    def extend_batch(self, iv3, sym, direction):
+        iv3 = np.ascontiguousarray(iv3, dtype=np.uint64); sym = np.ascontiguousarray(sym, dtype=np.uint8)
+        direction = np.ascontiguousarray(direction, dtype=np.uint8); out = np.zeros_like(iv3)
+        lib().orc_extend_batch(self.h, len(sym), iv3.ctypes.data, sym.ctypes.data, direction.ctypes.data, out.ctypes.data)
+        return out
+    def rank_batch(self, pos):
+        pos = np.ascontiguousarray(pos, dtype=np.uint64); out = np.zeros((len(pos), 8), dtype=np.uint64)
+        lib().orc_rank_batch(self.h, len(pos), pos.ctypes.data, out.ctypes.data)
+        return out
+    def search(self, pattern: bytes):
+        iv = np.array([[0, 0, self.n]], dtype=np.uint64)
+        for ch in reversed(pattern):
+            iv = self.extend_batch(iv, [ch], [0])
+        return tuple(int(x) for x in iv[0])
+    def tag_query(self, start, end, cap=1 << 20):
+        out = np.zeros(cap, dtype=np.uint64); n = ctypes.c_uint64()
+        nr = lib().orc_tag_query(self.h, start, end, out.ctypes.data, cap, ctypes.byref(n))
+        return nr, out[: n.value].copy()
+    def find_mems(self, reads, read_off, min_len, min_occ, with_tags=None, threads=0, count_work=False):
+        """reads: uint8 array (concatenated), read_off: uint64 [n+1] -> dict of numpy arrays."""
+        reads = np.ascontiguousarray(reads, dtype=np.uint8); read_off = np.ascontiguousarray(read_off, dtype=np.uint64)
+        if with_tags is None:
+            with_tags = self.has_tags
+        res = OrcResult()
+        if lib().orc_find_mems(self.h, reads.ctypes.data, read_off.ctypes.data, len(read_off) - 1, min_len, min_occ,
+                               int(with_tags), threads, int(count_work), ctypes.byref(res)):
+            raise RuntimeError(lib().orc_last_error().decode())
+        out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags,
+                   mem_off=_np(res.mem_off, res.n_reads + 1), mems=_np(res.mems, 4 * res.n_mems).reshape(-1, 4),
+                   tag_off=_np(res.tag_off, res.n_mems + 1), tags=_np(res.tags, res.n_tags), n_runs=_np(res.n_runs, res.n_mems),
+                   counters=dict(zip(["E", "D", "M", "tag_runs", "tag_skipped", "tag_item_sectors"], list(res.counters)[:6])))
+        ln = ctypes.c_uint64()
+        p = lib().orc_format_text(ctypes.byref(res), 1, int(with_tags), ctypes.byref(ln))
+        out["text"] = ctypes.string_at(p, ln.value); lib().orc_free(p)
+        lib().orc_result_free(ctypes.byref(res))
+        return out
+
+def pack_reads(reads):
+    """list of bytes -> (uint8 concatenation, uint64 offsets)."""
+    off = np.zeros(len(reads) + 1, dtype=np.uint64)
+    off[1:] = np.cumsum([len(r) for r in reads], dtype=np.uint64)
+    buf = np.frombuffer(b"".join(reads), dtype=np.uint8) if len(reads) else np.zeros(0, dtype=np.uint8)
+    return buf.copy(), off
+
+def algorithmic_bytes(counters):
+    """128*D + 96*M + 32*sum ceil(8*(skip+runs)/32)."""
+    return 128 * counters["D"] + 96 * counters["M"] + 32 * counters["tag_item_sectors"]

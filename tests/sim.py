@@ -1,0 +1,53 @@
+"""ctypes binding of tests/hostsim (product device arithmetic compiled as plain C++; test-only)."""
+import ctypes, os, subprocess
+import numpy as np
+
+_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "hostsim")
+_lib = None
+
+def lib():
+    global _lib
+    if _lib is None:
+        subprocess.check_call(["make", "-s", "-C", _DIR])
+        L = ctypes.CDLL(os.path.join(_DIR, "libpgi_hostsim.so"))
+        L.sim_last_error.restype = ctypes.c_char_p
+        L.sim_create.restype = ctypes.c_void_p
+        L.sim_create.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_int]
+        L.sim_free.argtypes = [ctypes.c_void_p]
+        L.sim_info.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.sim_extend_batch.argtypes = [ctypes.c_void_p, ctypes.c_uint64] + [ctypes.c_void_p] * 4
+        L.sim_find_mems.restype = ctypes.c_uint64
+        L.sim_find_mems.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_uint64,
+                                    ctypes.c_void_p, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
+        L.sim_tag_query.restype = ctypes.c_uint64
+        L.sim_tag_query.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64,
+                                    ctypes.POINTER(ctypes.c_uint64)]
+        _lib = L
+    return _lib
+
+class Index:
+    def __init__(self, ri, tags=None, tag_layout=0):
+        L = lib()
+        self.h = L.sim_create(ri, len(ri), tags, len(tags) if tags else 0, tag_layout)
+        if not self.h:
+            raise RuntimeError(L.sim_last_error().decode())
+        info = (ctypes.c_uint64 * 16)(); L.sim_info(self.h, info)
+        keys = ["n", "sigma", "n_blocks", "dir_shift", "has_quirk", "n_file_runs", "n_ref_blocks", "encoded",
+                "tag_m", "tag_shift", "tag_low_bytes", "starts_regular"]
+        self.info = dict(zip(keys, list(info)))
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().sim_free(self.h); self.h = None
+    def extend_batch(self, iv3, sym, direction):
+        iv3 = np.ascontiguousarray(iv3, dtype=np.uint64); sym = np.ascontiguousarray(sym, dtype=np.uint8)
+        direction = np.ascontiguousarray(direction, dtype=np.uint8); out = np.zeros_like(iv3)
+        lib().sim_extend_batch(self.h, len(sym), iv3.ctypes.data, sym.ctypes.data, direction.ctypes.data, out.ctypes.data)
+        return out
+    def find_mems(self, read: bytes, min_len, min_occ, cap=4096):
+        out = np.zeros((cap, 4), dtype=np.uint64); ne = ctypes.c_uint64()
+        n = lib().sim_find_mems(self.h, read, len(read), min_len, min_occ, out.ctypes.data, cap, ctypes.byref(ne))
+        return out[:n].copy(), ne.value
+    def tag_query(self, start, end, cap=1 << 20):
+        out = np.zeros(cap, dtype=np.uint64); n = ctypes.c_uint64()
+        nr = lib().sim_tag_query(self.h, start, end, out.ctypes.data, cap, ctypes.byref(n))
+        return nr, out[: n.value].copy()
