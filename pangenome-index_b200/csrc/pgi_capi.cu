@@ -1,0 +1,632 @@
+// pgi_capi.cu — the C ABI of include/pgi.h: index upload, batch contexts and the launch pipeline.
+// Everything a caller can reach goes through here; there is no CPU implementation of any query.
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_segmented_sort.cuh>
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <string>
+#include <vector>
+#include "../../include/pgi.h"
+#include "pgi_flatten.hpp"
+#include "pgi_tag_kernels.cuh"
+
+using namespace pgi;
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string &msg) { g_err = msg; return code; }
+
+struct CudaError { cudaError_t e; const char *what; };
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) throw CudaError{e_, #call}; } while (0)
+
+// Grow-only device / pinned-host buffers.
+struct DevBuf {
+    void *p = nullptr; size_t cap = 0;
+    void need(size_t bytes) {
+        if (bytes <= cap) return;
+        if (p) CK(cudaFree(p));
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        CK(cudaMalloc(&p, want)); cap = want;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <typename T> T *as() const { return (T *) p; }
+};
+struct PinBuf {
+    void *p = nullptr; size_t cap = 0;
+    void need(size_t bytes) {
+        if (bytes <= cap) return;
+        if (p) CK(cudaFreeHost(p));
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        CK(cudaHostAlloc(&p, want, cudaHostAllocDefault)); cap = want;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <typename T> T *as() const { return (T *) p; }
+};
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); CK(cudaSetDevice(dev)); }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+template <typename T> T *upload(const std::vector<T> &v, std::vector<void *> &owned, uint64_t &bytes, size_t pad_elems = 0) {
+    size_t n = v.size() + pad_elems;
+    if (n == 0) n = 1;
+    void *d = nullptr;
+    CK(cudaMalloc(&d, n * sizeof(T)));
+    owned.push_back(d); bytes += n * sizeof(T);
+    CK(cudaMemset(d, 0, n * sizeof(T)));
+    if (!v.empty()) CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return (T *) d;
+}
+
+} // namespace
+
+struct pgi_index {
+    int device = 0;
+    RiDev ri; TagDev tg; bool has_tags = false;
+    RiConsts consts; SparseRankConsts ivk;
+    uint32_t *d_desc = nullptr;
+    std::vector<void *> owned;
+    // sizes of the uploaded arrays, for clone
+    uint64_t n_block_words = 0, n_dir = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
+    pgi_index_info_t info;
+    std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
+    int sm_count = 0;
+};
+
+extern "C" const char *pgi_last_error(void) { return g_err.c_str(); }
+
+extern "C" int pgi_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+static int check_device(int device) {
+    int n = pgi_device_count();
+    if (n <= 0) return fail(PGI_ENODEVICE, "no usable CUDA device: libpgi has no CPU path");
+    if (device < 0 || device >= n) return fail(PGI_EINVAL, "device index out of range");
+    return 0;
+}
+
+static void fill_info(pgi_index *ix, const RiImage &ri, const TagImage *tg, uint64_t bytes) {
+    pgi_index_info_t &f = ix->info; std::memset(&f, 0, sizeof(f));
+    f.n = ri.k.n; f.sigma = ri.k.sigma; f.is_encoded = ri.encoded; f.n_ref_blocks = ri.n_ref_blocks; f.n_runs = ri.n_file_runs;
+    f.n_dev_blocks = ri.k.n_blocks; f.dir_shift = ri.k.dir_shift; f.has_quirk_slot = ri.k.has_quirk;
+    if (tg) {
+        f.has_tags = 1; f.tag_layout = (uint64_t) tg->layout; f.tag_runs = tg->intervals.k.m; f.tag_items = tg->n_items;
+        f.tag_item_width = tg->width; f.tag_universe = tg->intervals.k.size;
+    }
+    f.device_bytes = bytes;
+    for (int i = 0; i < 8; ++i) f.C[i] = ri.k.C[i];
+    std::memcpy(f.sym_map, ri.k.sym_map, 256);
+}
+
+extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
+                                int tag_layout, int device, pgi_index **out) {
+    if (!ri_bytes || !out) return fail(PGI_EINVAL, "null argument");
+    if (int rc = check_device(device)) return rc;
+    pgi_index *ix = nullptr;
+    try {
+        RiImage ri; TagImage tg; bool has_tags = tag_bytes && tag_len;
+        flatten_ri(ri_bytes, ri_len, ri);
+        if (has_tags) flatten_tags(tag_bytes, tag_len, tag_layout, tg);
+        DeviceGuard g(device);
+        ix = new pgi_index(); ix->device = device; ix->consts = ri.k;
+        cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
+        uint64_t bytes = 0;
+        RiDev &d = ix->ri;
+        d.blocks = upload(ri.blocks, ix->owned, bytes); ix->n_block_words = ri.blocks.size();
+        d.dir = upload(ri.dir, ix->owned, bytes); ix->n_dir = ri.dir.size();
+        d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
+        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk;
+        for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
+        std::vector<uint32_t> desc(512);
+        for (int i = 0; i < 256; ++i) { desc[i] = ri.k.desc_b[i]; desc[256 + i] = ri.k.desc_f[i]; }
+        ix->d_desc = upload(desc, ix->owned, bytes);
+        std::memset(&ix->tg, 0, sizeof(ix->tg));
+        if (has_tags) {
+            TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = tg.intervals.k;
+            t.iv.dir = upload(tg.intervals.dir, ix->owned, bytes); ix->n_iv_dir = tg.intervals.dir.size();
+            t.iv.low = upload(tg.intervals.low, ix->owned, bytes); ix->n_iv_low = tg.intervals.low.size();
+            t.iv.size = tg.intervals.k.size; t.iv.m = tg.intervals.k.m; t.iv.shift = tg.intervals.k.shift; t.iv.low_bytes = tg.intervals.k.low_bytes;
+            t.starts = upload(tg.starts, ix->owned, bytes); t.n_starts = tg.starts.size(); ix->n_starts = tg.starts.size();
+            t.words = upload(tg.words, ix->owned, bytes); ix->n_words = tg.words.size();
+            t.stream = upload(tg.stream, ix->owned, bytes); ix->n_stream = tg.stream.size();
+            t.n_items = tg.n_items; t.width = tg.width; t.layout = (uint32_t) tg.layout; t.starts_regular = tg.starts_regular; t.pad = 0;
+        }
+        fill_info(ix, ri, has_tags ? &tg : nullptr, bytes);
+        CK(cudaDeviceSynchronize());
+        *out = ix;
+        return PGI_OK;
+    } catch (const FormatError &e) { pgi_index_free(ix); return fail(PGI_EFORMAT, e.what());
+    } catch (const CudaError &e) { pgi_index_free(ix); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e));
+    } catch (const std::bad_alloc &) { pgi_index_free(ix); return fail(PGI_ENOMEM, "out of host memory while flattening the index");
+    } catch (const std::exception &e) { pgi_index_free(ix); return fail(PGI_EINVAL, e.what()); }
+}
+
+extern "C" int pgi_index_info(const pgi_index *ix, pgi_index_info_t *out) {
+    if (!ix || !out) return fail(PGI_EINVAL, "null argument");
+    *out = ix->info; return PGI_OK;
+}
+
+// ------------------------------------------------------------------------------------------ clone / free
+template <typename T> static T *clone_arr(const T *src, int src_dev, uint64_t n, int dst_dev, std::vector<void *> &owned) {
+    size_t bytes = (n ? n : 1) * sizeof(T);
+    void *d = nullptr;
+    CK(cudaMalloc(&d, bytes)); owned.push_back(d);
+    if (n) CK(cudaMemcpyPeer(d, dst_dev, src, src_dev, n * sizeof(T)));     // device to device over NVLink, no host bounce
+    else CK(cudaMemset(d, 0, bytes));
+    return (T *) d;
+}
+
+extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **out) {
+    if (!src || !out) return fail(PGI_EINVAL, "null argument");
+    if (int rc = check_device(device)) return rc;
+    pgi_index *ix = nullptr;
+    try {
+        DeviceGuard g(device);
+        ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
+        cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
+        ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags;
+        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
+        ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
+        const int sd = src->device;
+        ix->ri.blocks = clone_arr(src->ri.blocks, sd, src->n_block_words, device, ix->owned);
+        ix->ri.dir = clone_arr(src->ri.dir, sd, src->n_dir, device, ix->owned);
+        ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
+        ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
+        ix->d_desc = clone_arr(src->d_desc, sd, 512, device, ix->owned);
+        if (src->has_tags) {
+            ix->tg.iv.dir = clone_arr(src->tg.iv.dir, sd, src->n_iv_dir, device, ix->owned);
+            ix->tg.iv.low = clone_arr(src->tg.iv.low, sd, src->n_iv_low, device, ix->owned);
+            ix->tg.starts = clone_arr(src->tg.starts, sd, src->n_starts, device, ix->owned);
+            ix->tg.words = clone_arr(src->tg.words, sd, src->n_words, device, ix->owned);
+            ix->tg.stream = clone_arr(src->tg.stream, sd, src->n_stream, device, ix->owned);
+        }
+        CK(cudaDeviceSynchronize());
+        *out = ix; return PGI_OK;
+    } catch (const CudaError &e) { pgi_index_free(ix); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+}
+
+// ------------------------------------------------------------------------------------------ batch context
+enum { EV_START = 0, EV_MEM, EV_ORDER, EV_PLAN, EV_DECODE, EV_END, EV_COUNT };
+
+struct pgi_batch {
+    pgi_index *ix = nullptr;
+    cudaStream_t stream = nullptr; bool own_stream = false;
+    cudaEvent_t ev[EV_COUNT]; bool ev_ok = false;
+    // inputs
+    DevBuf d_reads, d_read_off; const uint64_t *reads64 = nullptr; const uint64_t *read_off = nullptr; uint64_t n_reads = 0;
+    // MEM stage
+    DevBuf d_ctr, d_mem_buf, d_mem_key, d_nmems, d_mem_off, d_mems, d_cub;
+    // tag stage
+    DevBuf d_n_runs, d_cnt, d_raw_off, d_first, d_skip, d_raw, d_raw2, d_ucnt, d_tag_off, d_tags, d_large, d_seg_b, d_seg_e;
+    PinBuf h_ctr, h_mem_off, h_mems, h_tag_off, h_tags, h_n_runs;
+    double mems_per_read = 4.0;
+    uint64_t n_mems = 0, n_tags = 0, extensions = 0;
+    double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool has_result = false;
+    void release_all() {
+        DevBuf *db[] = {&d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
+                        &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e};
+        for (DevBuf *b : db) b->release();
+        PinBuf *pb[] = {&h_ctr, &h_mem_off, &h_mems, &h_tag_off, &h_tags, &h_n_runs};
+        for (PinBuf *b : pb) b->release();
+    }
+};
+
+extern "C" void pgi_batch_free(pgi_batch *b) {
+    if (!b) return;
+    int prev = -1; cudaGetDevice(&prev); cudaSetDevice(b->ix->device);
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    b->release_all();
+    if (b->ev_ok) for (int i = 0; i < EV_COUNT; ++i) cudaEventDestroy(b->ev[i]);
+    if (b->own_stream && b->stream) cudaStreamDestroy(b->stream);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete b;
+}
+
+extern "C" void pgi_index_free(pgi_index *ix) {
+    if (!ix) return;
+    for (pgi_batch *b : ix->pool) pgi_batch_free(b);
+    int prev = -1; cudaGetDevice(&prev); cudaSetDevice(ix->device);
+    for (void *p : ix->owned) cudaFree(p);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete ix;
+}
+
+extern "C" int pgi_batch_create(pgi_index *ix, void *cuda_stream, pgi_batch **out) {
+    if (!ix || !out) return fail(PGI_EINVAL, "null argument");
+    pgi_batch *b = nullptr;
+    try {
+        DeviceGuard g(ix->device);
+        b = new pgi_batch(); b->ix = ix;
+        if (cuda_stream) b->stream = (cudaStream_t) cuda_stream;
+        else { CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking)); b->own_stream = true; }
+        for (int i = 0; i < EV_COUNT; ++i) CK(cudaEventCreate(&b->ev[i]));
+        b->ev_ok = true;
+        b->d_ctr.need(64); b->h_ctr.need(64);
+        *out = b; return PGI_OK;
+    } catch (const CudaError &e) { if (b) { b->ix = ix; pgi_batch_free(b); } return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+}
+
+extern "C" int pgi_batch_upload(pgi_batch *b, const char *reads, const uint64_t *read_off, uint64_t n_reads) {
+    if (!b || (!reads && n_reads) || !read_off) return fail(PGI_EINVAL, "null argument");
+    try {
+        DeviceGuard g(b->ix->device);
+        if (read_off[0] != 0) return fail(PGI_EINVAL, "read_off[0] must be 0");
+        const uint64_t total = read_off[n_reads];
+        b->d_reads.need(total + 16); b->d_read_off.need((n_reads + 1) * 8);
+        if (total) CK(cudaMemcpyAsync(b->d_reads.p, reads, total, cudaMemcpyHostToDevice, b->stream));
+        CK(cudaMemsetAsync((char *) b->d_reads.p + total, 0, 16, b->stream));
+        CK(cudaMemcpyAsync(b->d_read_off.p, read_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, b->stream));
+        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false;
+        return PGI_OK;
+    } catch (const CudaError &e) { return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+}
+
+extern "C" int pgi_batch_set_device_reads(pgi_batch *b, const char *d_reads, const uint64_t *d_read_off, uint64_t n_reads, uint64_t total_bytes) {
+    if (!b || !d_read_off || (!d_reads && n_reads)) return fail(PGI_EINVAL, "null argument");
+    if (((uintptr_t) d_reads & 7) != 0) return fail(PGI_EINVAL, "device reads must be 8-byte aligned");
+    (void) total_bytes;
+    b->reads64 = (const uint64_t *) d_reads; b->read_off = d_read_off; b->n_reads = n_reads; b->has_result = false;
+    return PGI_OK;
+}
+
+// ------------------------------------------------------------------------------------------ the pipeline
+namespace {
+
+inline unsigned grid_for(uint64_t n, unsigned threads) { return (unsigned) std::max<uint64_t>(1, (n + threads - 1) / threads); }
+
+// Exclusive prefix sum of n + 1 u64 values (the last input is forced to 0 by the caller) -> out[0..n].
+void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_plus_1, int &launches) {
+    size_t tmp = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, out, (int64_t) n_plus_1, b->stream));
+    b->d_cub.need(tmp);
+    CK(cub::DeviceScan::ExclusiveSum(b->d_cub.p, tmp, in, out, (int64_t) n_plus_1, b->stream));
+    launches += 2;
+}
+
+// counters in d_ctr / h_ctr (u64): [0] cursor, [1] mem_count, [2] ext_count, [3] large_count
+uint64_t read_back(pgi_batch *b, const void *dptr) {
+    CK(cudaMemcpyAsync(b->h_ctr.p, dptr, 8, cudaMemcpyDeviceToHost, b->stream));
+    CK(cudaStreamSynchronize(b->stream));
+    return *b->h_ctr.as<uint64_t>();
+}
+
+// MEM finding: K1 (+ re-run with a larger append buffer if it overflowed), scan, scatter.
+void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launches, int &reruns) {
+    pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
+    b->d_nmems.need((n + 1) * 8); b->d_mem_off.need((n + 1) * 8);
+    uint64_t cap = std::max<uint64_t>(1024, (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
+    int blocks_per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fmd_mem_kernel, PGI_MEM_THREADS, 0));
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+    const uint64_t want_blocks = (n + PGI_MEM_THREADS - 1) / PGI_MEM_THREADS;
+    const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, want_blocks));
+    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
+    uint64_t total = 0;
+    for (;;) {
+        b->d_mem_buf.need(cap * 32); b->d_mem_key.need(cap * 8);
+        CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
+        CK(cudaMemsetAsync(b->d_nmems.p, 0, (n + 1) * 8, b->stream));
+        MemArgs a;
+        a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
+        a.n_reads = n; a.min_len = min_len; a.min_occ = min_occ;
+        a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = cap;
+        a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
+        if (n) { fmd_mem_kernel<<<grid, PGI_MEM_THREADS, 0, b->stream>>>(a); ++launches; }
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(b->h_ctr.p, ctr, 32, cudaMemcpyDeviceToHost, b->stream));
+        CK(cudaStreamSynchronize(b->stream));
+        total = b->h_ctr.as<uint64_t>()[1]; b->extensions = b->h_ctr.as<uint64_t>()[2];
+        if (total <= cap) break;
+        cap = total + 1024; ++reruns;                    // append buffer overflowed: the count is exact, run again
+    }
+    if (n) b->mems_per_read = std::max(1.0, (double) total / (double) n);
+    b->n_mems = total;
+    CK(cudaEventRecord(b->ev[EV_MEM], b->stream));
+    exclusive_scan(b, b->d_nmems.as<uint64_t>(), b->d_mem_off.as<uint64_t>(), n + 1, launches);
+    b->d_mems.need(std::max<uint64_t>(1, total) * 32);
+    if (total) {
+        mem_scatter_kernel<<<grid_for(total, 256), 256, 0, b->stream>>>(b->d_mem_buf.as<uint4>(), b->d_mem_key.as<uint64_t>(),
+                                                                          b->d_mem_off.as<uint64_t>(), total, b->d_mems.as<uint4>());
+        ++launches; CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
+}
+
+// Tag lookup for nm intervals given either as ordered MEM records or as start/end arrays (device pointers).
+void run_tag_stage(pgi_batch *b, uint64_t nm, const uint4 *mems, const uint64_t *start, const uint64_t *end, int &launches) {
+    pgi_index *ix = b->ix; cudaStream_t st = b->stream;
+    b->d_n_runs.need((nm + 1) * 8); b->d_cnt.need((nm + 1) * 8); b->d_raw_off.need((nm + 1) * 8); b->d_first.need((nm + 1) * 8);
+    b->d_skip.need((nm + 1) * 4); b->d_ucnt.need((nm + 1) * 8); b->d_tag_off.need((nm + 1) * 8); b->d_large.need((nm + 1) * 8);
+    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
+    CK(cudaMemsetAsync(ctr + 3, 0, 8, st));
+    CK(cudaMemsetAsync(b->d_cnt.as<uint64_t>() + nm, 0, 8, st));
+    CK(cudaMemsetAsync(b->d_ucnt.as<uint64_t>() + nm, 0, 8, st));
+    if (nm) {
+        tag_plan_kernel<<<grid_for(nm, 256), 256, 0, st>>>(ix->tg, nm, mems, start, end, b->d_n_runs.as<uint64_t>(), b->d_cnt.as<uint64_t>(),
+                                                           b->d_first.as<uint64_t>(), b->d_skip.as<uint32_t>());
+        ++launches; CK(cudaGetLastError());
+    }
+    exclusive_scan(b, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), nm + 1, launches);
+    const uint64_t total_raw = read_back(b, b->d_raw_off.as<uint64_t>() + nm);
+    CK(cudaEventRecord(b->ev[EV_PLAN], st));
+    b->d_raw.need(std::max<uint64_t>(1, total_raw) * 8);
+    if (nm) {
+        tag_small_kernel<<<grid_for(nm, 128), 128, 0, st>>>(ix->tg, nm, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_first.as<uint64_t>(),
+                                                            b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(), b->d_ucnt.as<uint64_t>(),
+                                                            b->d_large.as<uint64_t>(), ctr + 3);
+        ++launches; CK(cudaGetLastError());
+    }
+    const uint64_t n_large = nm ? read_back(b, ctr + 3) : 0;
+    if (n_large) {
+        b->d_raw2.need(total_raw * 8); b->d_seg_b.need(n_large * 8); b->d_seg_e.need(n_large * 8);
+        const unsigned g = grid_for(n_large * 32, 256);
+        tag_large_decode_kernel<<<g, 256, 0, st>>>(ix->tg, n_large, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                   b->d_first.as<uint64_t>(), b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(),
+                                                   b->d_seg_b.as<uint64_t>(), b->d_seg_e.as<uint64_t>());
+        CK(cudaGetLastError());
+        size_t tmp = 0;
+        CK(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) total_raw, (int64_t) n_large,
+                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), st));
+        b->d_cub.need(tmp);
+        CK(cub::DeviceSegmentedSort::SortKeys(b->d_cub.p, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) total_raw, (int64_t) n_large,
+                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), st));
+        tag_large_unique_kernel<<<g, 256, 0, st>>>(n_large, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                   b->d_raw2.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_ucnt.as<uint64_t>());
+        CK(cudaGetLastError());
+        launches += 5;
+    }
+    CK(cudaEventRecord(b->ev[EV_DECODE], st));
+    exclusive_scan(b, b->d_ucnt.as<uint64_t>(), b->d_tag_off.as<uint64_t>(), nm + 1, launches);
+    const uint64_t n_tags = read_back(b, b->d_tag_off.as<uint64_t>() + nm);
+    b->d_tags.need(std::max<uint64_t>(1, n_tags) * 8);
+    if (nm) {
+        tag_copy_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_tag_off.as<uint64_t>(),
+                                                           b->d_raw.as<uint64_t>(), b->d_tags.as<uint64_t>());
+        ++launches; CK(cudaGetLastError());
+    }
+    if (n_large) {
+        tag_large_copy_kernel<<<grid_for(n_large * 32, 256), 256, 0, st>>>(n_large, b->d_large.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                                           b->d_tag_off.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_tags.as<uint64_t>());
+        ++launches; CK(cudaGetLastError());
+    }
+    b->n_tags = n_tags;
+}
+
+float ev_ms(pgi_batch *b, int from, int to) { float ms = 0; cudaEventElapsedTime(&ms, b->ev[from], b->ev[to]); return ms; }
+
+} // namespace
+
+#define PGI_CATCH \
+    catch (const CudaError &e) { return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); } \
+    catch (const std::bad_alloc &) { return fail(PGI_ENOMEM, "out of host memory"); } \
+    catch (const std::exception &e) { return fail(PGI_EINVAL, e.what()); }
+
+extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) {
+    if (!b) return fail(PGI_EINVAL, "null argument");
+    if (!b->read_off) return fail(PGI_EINVAL, "no reads staged: call pgi_batch_upload or pgi_batch_set_device_reads first");
+    if (b->n_reads >> 32) return fail(PGI_EINVAL, "more than 2^32 reads in one batch");
+    try {
+        DeviceGuard g(b->ix->device);
+        int launches = 0, reruns = 0;
+        CK(cudaEventRecord(b->ev[EV_START], b->stream));
+        run_mem_stage(b, min_len, min_occ, launches, reruns);
+        const uint64_t nm = b->n_mems;
+        if (b->ix->has_tags) run_tag_stage(b, nm, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
+        else {
+            b->d_tag_off.need((nm + 1) * 8); b->d_n_runs.need((nm + 1) * 8); b->d_tags.need(8);
+            CK(cudaMemsetAsync(b->d_tag_off.p, 0, (nm + 1) * 8, b->stream));
+            CK(cudaMemsetAsync(b->d_n_runs.p, 0, (nm + 1) * 8, b->stream));
+            CK(cudaEventRecord(b->ev[EV_PLAN], b->stream)); CK(cudaEventRecord(b->ev[EV_DECODE], b->stream));
+            b->n_tags = 0;
+        }
+        CK(cudaEventRecord(b->ev[EV_END], b->stream));
+        CK(cudaStreamSynchronize(b->stream));
+        b->stage_ms[0] = ev_ms(b, EV_START, EV_MEM); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
+        b->stage_ms[3] = ev_ms(b, EV_PLAN, EV_DECODE); b->stage_ms[4] = ev_ms(b, EV_DECODE, EV_END); b->stage_ms[5] = ev_ms(b, EV_START, EV_END);
+        b->stage_ms[6] = launches; b->stage_ms[7] = reruns;
+        b->has_result = true;
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+extern "C" int pgi_batch_stage_ms(pgi_batch *b, double ms[8]) {
+    if (!b || !ms) return fail(PGI_EINVAL, "null argument");
+    for (int i = 0; i < 8; ++i) ms[i] = b->stage_ms[i];
+    return PGI_OK;
+}
+
+extern "C" int pgi_batch_device_result(pgi_batch *b, pgi_result *out) {
+    if (!b || !out) return fail(PGI_EINVAL, "null argument");
+    if (!b->has_result) return fail(PGI_EINVAL, "no completed run on this batch");
+    std::memset(out, 0, sizeof(*out));
+    out->n_reads = b->n_reads; out->n_mems = b->n_mems; out->n_tags = b->n_tags; out->extensions = b->extensions;
+    out->mem_off = b->d_mem_off.as<uint64_t>(); out->mems = b->d_mems.as<pgi_mem>(); out->tag_off = b->d_tag_off.as<uint64_t>();
+    out->tags = b->d_tags.as<uint64_t>(); out->n_runs = b->d_n_runs.as<uint64_t>();
+    return PGI_OK;
+}
+
+extern "C" int pgi_batch_fetch(pgi_batch *b, pgi_result *out) {
+    if (!b || !out) return fail(PGI_EINVAL, "null argument");
+    if (!b->has_result) return fail(PGI_EINVAL, "no completed run on this batch");
+    try {
+        DeviceGuard g(b->ix->device);
+        const uint64_t n = b->n_reads, nm = b->n_mems, nt = b->n_tags; cudaStream_t st = b->stream;
+        b->h_mem_off.need((n + 1) * 8); b->h_mems.need((nm + 1) * 32); b->h_tag_off.need((nm + 1) * 8);
+        b->h_tags.need((nt + 1) * 8); b->h_n_runs.need((nm + 1) * 8);
+        CK(cudaMemcpyAsync(b->h_mem_off.p, b->d_mem_off.p, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (nm) CK(cudaMemcpyAsync(b->h_mems.p, b->d_mems.p, nm * 32, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(b->h_tag_off.p, b->d_tag_off.p, (nm + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (nt) CK(cudaMemcpyAsync(b->h_tags.p, b->d_tags.p, nt * 8, cudaMemcpyDeviceToHost, st));
+        if (nm) CK(cudaMemcpyAsync(b->h_n_runs.p, b->d_n_runs.p, nm * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        std::memset(out, 0, sizeof(*out));
+        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = b->extensions;
+        out->mem_off = b->h_mem_off.as<uint64_t>(); out->mems = b->h_mems.as<pgi_mem>(); out->tag_off = b->h_tag_off.as<uint64_t>();
+        out->tags = b->h_tags.as<uint64_t>(); out->n_runs = b->h_n_runs.as<uint64_t>();
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+// ------------------------------------------------------------------------------------------ one-call API
+static pgi_batch *pool_take(pgi_index *ix) {
+    { std::lock_guard<std::mutex> l(ix->pool_mu); if (!ix->pool.empty()) { pgi_batch *b = ix->pool.back(); ix->pool.pop_back(); return b; } }
+    pgi_batch *b = nullptr;
+    return pgi_batch_create(ix, nullptr, &b) == PGI_OK ? b : nullptr;
+}
+static void pool_give(pgi_index *ix, pgi_batch *b) { std::lock_guard<std::mutex> l(ix->pool_mu); ix->pool.push_back(b); }
+
+extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                             uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out) {
+    if (!ix || !read_off || !out) return fail(PGI_EINVAL, "null argument");
+    pgi_batch *b = pool_take(ix);
+    if (!b) return PGI_ECUDA;
+    cudaStream_t own = b->stream;
+    if (cuda_stream) b->stream = (cudaStream_t) cuda_stream;
+    int rc = pgi_batch_upload(b, reads, read_off, n_reads);
+    if (rc == PGI_OK) rc = pgi_batch_run(b, min_len, min_occ);
+    if (rc == PGI_OK) rc = pgi_batch_fetch(b, out);
+    b->stream = own;
+    if (rc != PGI_OK) { pool_give(ix, b); return rc; }
+    out->owner = b;                                      // the result lives in the batch's pinned buffers
+    return PGI_OK;
+}
+
+extern "C" void pgi_result_free(pgi_result *r) {
+    if (!r || !r->owner) return;
+    pgi_batch *b = (pgi_batch *) r->owner;
+    pool_give(b->ix, b);
+    std::memset(r, 0, sizeof(*r));
+}
+
+extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *start, const uint64_t *end, pgi_result *out) {
+    if (!ix || !out || ((!start || !end) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!ix->has_tags) return fail(PGI_EINVAL, "index was created without tags");
+    pgi_batch *b = pool_take(ix);
+    if (!b) return PGI_ECUDA;
+    try {
+        DeviceGuard g(ix->device);
+        b->d_reads.need(std::max<uint64_t>(1, n) * 16);
+        uint64_t *ds = b->d_reads.as<uint64_t>(), *de = ds + n;
+        if (n) { CK(cudaMemcpyAsync(ds, start, n * 8, cudaMemcpyHostToDevice, b->stream)); CK(cudaMemcpyAsync(de, end, n * 8, cudaMemcpyHostToDevice, b->stream)); }
+        int launches = 0;
+        CK(cudaEventRecord(b->ev[EV_START], b->stream));
+        run_tag_stage(b, n, nullptr, ds, de, launches);
+        b->n_reads = 0; b->n_mems = n; b->extensions = 0; b->has_result = true;
+        b->d_mem_off.need(8); CK(cudaMemsetAsync(b->d_mem_off.p, 0, 8, b->stream));
+        b->d_mems.need(std::max<uint64_t>(1, n) * 32);
+        b->read_off = nullptr;
+        int rc = pgi_batch_fetch(b, out);
+        if (rc != PGI_OK) { pool_give(ix, b); return rc; }
+        out->mems = nullptr; out->mem_off = nullptr; out->owner = b;
+        return PGI_OK;
+    } catch (const CudaError &e) { pool_give(ix, b); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+}
+
+extern "C" int pgi_extend_batch(pgi_index *ix, uint64_t n, const pgi_bi_interval *in, const uint8_t *sym, const uint8_t *dir, pgi_bi_interval *out) {
+    if (!ix || ((!in || !sym || !dir || !out) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!n) return PGI_OK;
+    try {
+        DeviceGuard g(ix->device);
+        DevBuf d_in, d_sym, d_dir, d_out;
+        d_in.need(n * 24); d_sym.need(n); d_dir.need(n); d_out.need(n * 24);
+        CK(cudaMemcpy(d_in.p, in, n * 24, cudaMemcpyHostToDevice)); CK(cudaMemcpy(d_sym.p, sym, n, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_dir.p, dir, n, cudaMemcpyHostToDevice));
+        fmd_extend_kernel<<<grid_for(n, 128), 128>>>(ix->ri, ix->d_desc, n, d_in.as<uint64_t>(), d_sym.as<uint8_t>(), d_dir.as<uint8_t>(), d_out.as<uint64_t>());
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(out, d_out.p, n * 24, cudaMemcpyDeviceToHost));
+        d_in.release(); d_sym.release(); d_dir.release(); d_out.release();
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+extern "C" int pgi_rank_batch(pgi_index *ix, uint64_t n, const uint64_t *pos, uint64_t *out8) {
+    if (!ix || ((!pos || !out8) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!n) return PGI_OK;
+    try {
+        DeviceGuard g(ix->device);
+        DevBuf d_pos, d_out; d_pos.need(n * 8); d_out.need(n * 64);
+        CK(cudaMemcpy(d_pos.p, pos, n * 8, cudaMemcpyHostToDevice));
+        SlotTable st; for (int i = 0; i < 8; ++i) st.s[i] = ix->consts.slot[i]; st.sigma = (uint32_t) ix->consts.sigma;
+        rank_kernel<<<grid_for(n, 128), 128>>>(ix->ri, st, n, d_pos.as<uint64_t>(), d_out.as<uint64_t>());
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(out8, d_out.p, n * 64, cudaMemcpyDeviceToHost));
+        d_pos.release(); d_out.release();
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+// ------------------------------------------------------------------------------------------ text + microbenchmark
+static inline void put_u64(std::string &s, uint64_t v) {
+    char buf[24]; int i = 24;
+    do { buf[--i] = (char) ('0' + v % 10); v /= 10; } while (v);
+    s.append(buf + i, 24 - i);
+}
+static inline void put_i64(std::string &s, int64_t v) {
+    if (v < 0) { s.push_back('-'); put_u64(s, (uint64_t) 0 - (uint64_t) v); } else put_u64(s, (uint64_t) v);
+}
+
+// stdout grammar of src/find_mems.cpp:115-139 and src/tag_arrays.cpp:885-889.
+extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int with_tags, uint64_t *len) {
+    if (!r || !len) { fail(PGI_EINVAL, "null argument"); return nullptr; }
+    std::string s;
+    s.reserve((size_t) (r->n_reads * 16 + r->n_mems * 96 + r->n_tags * 12));
+    for (uint64_t i = 0; i < r->n_reads; ++i) {
+        s += "Seq: "; put_u64(s, first_seq + i); s.push_back('\n');
+        for (uint64_t m = r->mem_off[i]; m < r->mem_off[i + 1]; ++m) {
+            const pgi_mem &x = r->mems[m];
+            s += "MEM START: "; put_u64(s, x.start); s += ", MEM END: "; put_u64(s, x.end);
+            s += " BWT START: "; put_u64(s, x.bwt_start); s += " SIZE: "; put_i64(s, x.size); s.push_back('\n');
+            if (with_tags) {
+                const uint64_t a = r->tag_off[m], e = r->tag_off[m + 1];
+                s += "Number of unique positions: "; put_u64(s, e - a); s.push_back('\n');
+                for (uint64_t t = a; t < e; ++t) { put_u64(s, r->tags[t]); s += ", "; }
+                s.push_back('\n');
+            }
+        }
+        s.push_back('\n');
+    }
+    char *buf = (char *) std::malloc(s.size() + 1);
+    if (!buf) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
+    std::memcpy(buf, s.data(), s.size()); buf[s.size()] = 0; *len = s.size();
+    return buf;
+}
+extern "C" void pgi_free(void *p) { std::free(p); }
+
+extern "C" int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t bytes_per_access, uint64_t n_access, int chain, double *gbs) {
+    if (!gbs || chain < 1 || (bytes_per_access != 32 && bytes_per_access != 64 && bytes_per_access != 128)) return fail(PGI_EINVAL, "bad argument");
+    if (int rc = check_device(device)) return rc;
+    try {
+        DeviceGuard g(device);
+        DevBuf buf, sink; buf.need(buf_bytes); sink.need(8);
+        CK(cudaMemset(buf.p, 1, buf_bytes)); CK(cudaMemset(sink.p, 0, 8));
+        const uint64_t n_slots = buf_bytes / bytes_per_access, n_threads = std::max<uint64_t>(1, n_access / (uint64_t) chain);
+        cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep) {              // rep 0 is the warm-up
+            CK(cudaEventRecord(e0));
+            const unsigned grid = grid_for(n_threads, 256);
+            if (bytes_per_access == 32) gather_kernel<32><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
+            else if (bytes_per_access == 64) gather_kernel<64><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
+            else gather_kernel<128><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
+            CK(cudaGetLastError());
+            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+            float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+            if (rep > 0 && ms < best) best = ms;
+        }
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        *gbs = (double) n_threads * chain * bytes_per_access / (best * 1e-3) / 1e9;
+        buf.release(); sink.release();
+        return PGI_OK;
+    } PGI_CATCH
+}

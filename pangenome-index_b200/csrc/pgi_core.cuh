@@ -184,14 +184,42 @@ PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
     uint64_t p2 = in.k + (uint64_t) in.s, p1 = in.k;
     if (p2 > ix.n) p2 = ix.n;
     if (p1 > ix.n) p1 = ix.n;
-    uint64_t t1[6], t2[6];
-    rank_pair(ix, p1, p2, t1, t2);
-    uint64_t kp = in.kp, x = 0, y = 0;
+    const uint64_t b1 = locate_block(ix, p1), b2 = locate_block(ix, p2);
+    uint64_t w[8], v[8];
+    ld_block(ix.blocks + b1 * PGI_BLOCK_WORDS, w);
+    const bool same = b1 == b2;
+    if (!same) ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);     // both block loads are in flight together
     const uint32_t ms = (d >> 21) & 7;
+    uint64_t kp = in.kp, x = 0, y = 0;
+    {
+        const uint64_t st = w[0] & 0xFFFFFFFFFFull;
+        Packed6 c1, c2; uint64_t cum[6];
+        block_scan2(w, p1 - st, same ? p2 - st : 0, c1, c2);
+        block_cums(w, cum);
 #pragma unroll
-    for (int c = 0; c < 6; ++c) {
-        kp += (uint64_t) ((d >> (3 * c)) & 7) * (t2[c] - t1[c]);
-        if (ms == (uint32_t) c) { x = t2[c]; y = t1[c]; }
+        for (int c = 0; c < 6; ++c) {
+            const uint64_t wt = (d >> (3 * c)) & 7;
+            const uint64_t r1 = cum[c] + packed_get(c1, c);
+            kp -= wt * r1;
+            if (ms == (uint32_t) c) y = r1;
+            if (same) {
+                const uint64_t r2 = cum[c] + packed_get(c2, c);
+                kp += wt * r2;
+                if (ms == (uint32_t) c) x = r2;
+            }
+        }
+    }
+    if (!same) {
+        const uint64_t st = v[0] & 0xFFFFFFFFFFull;
+        Packed6 c2, dd; uint64_t cum[6];
+        block_scan2(v, p2 - st, 0, c2, dd);
+        block_cums(v, cum);
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            const uint64_t r2 = cum[c] + packed_get(c2, c);
+            kp += (uint64_t) ((d >> (3 * c)) & 7) * r2;
+            if (ms == (uint32_t) c) x = r2;
+        }
     }
     if (ix.has_quirk) {
         const uint32_t wq = (d >> 18) & 7;

@@ -218,6 +218,7 @@ inline void build_descriptors(RiImage &im, const bool present[6], bool legacy) {
             slot[i] = (col < 6 && present[col]) ? col : PGI_SRC_ZERO;
         }
     }
+    for (unsigned i = 0; i < 8; ++i) k.slot[i] = slot[i];
     uint8_t comp[256];
     for (int i = 0; i < 256; ++i) comp[i] = (uint8_t) i;                   // r-index.cpp:1512-1529
     comp['A'] = 'T'; comp['C'] = 'G'; comp['G'] = 'C'; comp['T'] = 'A';

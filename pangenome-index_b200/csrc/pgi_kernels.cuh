@@ -1,0 +1,158 @@
+// pgi_kernels.cuh — the CUDA kernels of the find_mems hot path (sm_100a). Integer / bit work over
+// random-access HBM traffic: no tensor cores, nothing here is a dense contraction.
+//
+//   fmd_mem_kernel      K1  find_all_mems for a batch of reads      (algorithm.hpp:653-757)
+//   mem_scatter_kernel  K4  MEMs into read order
+//   tag_plan_kernel     K2a rank/select part of query_compressed*   (tag_arrays.cpp:857-874)
+//   tag_small_kernel    K2b decode + sort + unique, short lists
+//   tag_large_*         K2b/K3 the same for long lists, one warp per MEM
+//   tag_copy_kernel     K4  compaction of the unique lists
+//   fmd_extend_kernel / rank_kernel : batched single operations (parity tests, facade calls)
+//   gather_kernel       M1  random-access roofline microbenchmark
+#pragma once
+#include <cuda_runtime.h>
+#include "pgi_core.cuh"
+
+namespace pgi {
+
+#define PGI_MEM_THREADS 256
+#define PGI_TAG_SMALL 32u          // lists up to this many runs are handled by one thread
+
+struct MemArgs {
+    RiDev ix;
+    const uint32_t *desc;          // desc_b[256] followed by desc_f[256]
+    const uint64_t *reads64;       // read bytes viewed as aligned u64 words (buffer padded to 8 bytes)
+    const uint64_t *read_off;      // n_reads + 1 byte offsets
+    uint64_t n_reads, min_len, min_occ;
+    unsigned long long *cursor;    // next unassigned read
+    unsigned long long *mem_count; // MEMs appended so far (keeps counting past mem_cap)
+    unsigned long long *ext_count; // FMD extensions executed
+    uint64_t mem_cap;
+    uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
+    uint64_t *mem_key;             // read id << 32 | index of the MEM within its read
+    uint64_t *read_nmems;          // n_reads (+1) MEM counts per read
+};
+
+// K1. One lane = one read at a time; every trip of the loop performs exactly one FMD extension per
+// active lane, so a warp stays convergent while its 32 reads sit in different phases of
+// find_mems_function. Lanes that finish a read pull the next one from a warp-local queue that is
+// refilled 32 reads at a time from a global cursor (persistent grid: no tail of idle lanes inside a warp).
+__global__ void __launch_bounds__(PGI_MEM_THREADS) fmd_mem_kernel(const MemArgs a) {
+    __shared__ uint32_t s_desc[512];
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) s_desc[i] = a.desc[i];
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    MemLane L; L.phase = PH_DONE; L.emit = 0; L.len = 0; L.x = 0; L.j = 0; L.e = 0; L.k2 = 0; L.s2 = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
+    uint64_t rd = ~0ull, base = 0, wq_next = 0, wq_end = 0, n_ext = 0;
+    uint64_t cw = 0, cwi = ~0ull;      // cached 8-byte window of the read
+    uint32_t nm = 0;
+    bool exhausted = false, have = false;
+    for (;;) {
+        // ---- hand out reads to idle lanes
+        const bool want = !have && !exhausted;
+        const unsigned m = __ballot_sync(FULL, want);
+        if (m) {
+            if (wq_next >= wq_end) {
+                unsigned long long got = 0;
+                if (lane == 0) got = atomicAdd(a.cursor, 32ull);
+                got = __shfl_sync(FULL, got, 0);
+                wq_next = got; wq_end = got + 32 < a.n_reads ? got + 32 : a.n_reads;
+                if (wq_next >= a.n_reads) { wq_next = wq_end = a.n_reads; exhausted = true; }
+            }
+            if (want && !exhausted) {
+                const uint64_t id = wq_next + __popc(m & lt_mask);
+                if (id < wq_end) {
+                    rd = id; have = true; nm = 0;
+                    base = a.read_off[id];
+                    lane_begin(L, a.read_off[id + 1] - base, a.min_len, a.ix.n);
+                }
+            }
+            const uint64_t adv = wq_next + __popc(m);
+            wq_next = adv < wq_end ? adv : wq_end;
+        }
+        // ---- run to the next extension, writing out MEMs on the way
+        bool need = false;
+        if (have) {
+            for (;;) {
+                need = lane_settle(L, a.min_len, a.ix.n);
+                if (!L.emit) break;
+                const unsigned long long slot = atomicAdd(a.mem_count, 1ull);
+                if (slot < a.mem_cap) {
+                    a.mem_buf[2 * slot] = make_uint4((uint32_t) L.x, (uint32_t) (L.x >> 32), (uint32_t) L.e, (uint32_t) (L.e >> 32));
+                    a.mem_buf[2 * slot + 1] = make_uint4((uint32_t) L.k2, (uint32_t) (L.k2 >> 32), (uint32_t) (uint64_t) L.s2, (uint32_t) ((uint64_t) L.s2 >> 32));
+                    a.mem_key[slot] = (rd << 32) | nm;
+                }
+                ++nm; L.emit = 0;
+            }
+            if (!need) { a.read_nmems[rd] = nm; have = false; }
+        }
+        if (__all_sync(FULL, !have && exhausted)) break;
+        // ---- one FMD extension
+        if (need) {
+            uint32_t sym = 0;
+            if (L.j < L.len) {
+                const uint64_t o = base + L.j;
+                if ((o >> 3) != cwi) { cwi = o >> 3; cw = __ldg(a.reads64 + cwi); }
+                sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
+            }
+            if (L.phase == PH_P2) {
+                BiInt t; t.k = L.b.kp; t.kp = L.b.k; t.s = L.b.s;
+                t = extend_desc(a.ix, t, s_desc[256 + sym]);
+                L.b.k = t.kp; L.b.kp = t.k; L.b.s = t.s;
+            } else {
+                L.b = extend_desc(a.ix, L.b, s_desc[sym]);
+            }
+            ++n_ext;
+            lane_after_ext(L, a.min_len, a.min_occ, a.ix.n);
+        }
+    }
+    for (int o = 16; o; o >>= 1) n_ext += __shfl_xor_sync(FULL, n_ext, o);
+    if (lane == 0 && n_ext) atomicAdd(a.ext_count, (unsigned long long) n_ext);
+}
+
+// K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read.
+__global__ void mem_scatter_kernel(const uint4 *mem_buf, const uint64_t *mem_key, const uint64_t *mem_off,
+                                   uint64_t n_mems, uint4 *mems) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n_mems) return;
+    const uint64_t key = mem_key[i];
+    const uint64_t dst = mem_off[key >> 32] + (key & 0xFFFFFFFFull);
+    mems[2 * dst] = mem_buf[2 * i]; mems[2 * dst + 1] = mem_buf[2 * i + 1];
+}
+
+// Batched backward / forward extension (FastLocate::backward_extend_encoded / forward_extend_encoded).
+__global__ void fmd_extend_kernel(RiDev ix, const uint32_t *desc, uint64_t n, const uint64_t *in3, const uint8_t *sym,
+                                  const uint8_t *dir, uint64_t *out3) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    BiInt b; b.k = in3[3 * i]; b.kp = in3[3 * i + 1]; b.s = (int64_t) in3[3 * i + 2];
+    if (dir[i]) {
+        BiInt t; t.k = b.kp; t.kp = b.k; t.s = b.s;
+        t = extend_desc(ix, t, desc[256 + sym[i]]);
+        b.k = t.kp; b.kp = t.k; b.s = t.s;
+    } else b = extend_desc(ix, b, desc[sym[i]]);
+    out3[3 * i] = b.k; out3[3 * i + 1] = b.kp; out3[3 * i + 2] = (uint64_t) b.s;
+}
+
+// Batched rank vectors R(pos)[0..8) (FastLocate::rank_at_cached_encoded); slot = RiConsts::slot.
+struct SlotTable { uint32_t s[8]; uint32_t sigma; };
+__global__ void rank_kernel(RiDev ix, SlotTable st, uint64_t n, const uint64_t *pos, uint64_t *out8) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t p = pos[i]; if (p > ix.n) p = ix.n;
+    uint64_t t1[6], t2[6];
+    rank_pair(ix, p, p, t1, t2);
+    const uint64_t q = ix.has_quirk ? quirk_at(ix, p) : 0;
+    for (uint32_t j = 0; j < 8; ++j) {
+        uint64_t v = 0;
+        if (j < st.sigma) {
+            const uint32_t s = st.s[j];
+            if (s == PGI_SRC_QUIRK) v = q;
+            else if (s < 6) { v = 0; for (int c = 0; c < 6; ++c) if (s == (uint32_t) c) v = t1[c]; }
+        }
+        out8[8 * i + j] = v;
+    }
+}
+
+} // namespace pgi

@@ -28,6 +28,7 @@
 typedef struct {
     uint64_t n, sigma, n_blocks, n_quirk, mem_tail;
     uint32_t dir_shift, has_quirk;
+    uint32_t slot[8];          // source of R(pos)[i], i < sigma (0..5 true rank of that nuc code, PGI_SRC_QUIRK, PGI_SRC_ZERO)
     uint64_t C[8];
     uint8_t sym_map[256];
     uint32_t desc_b[256], desc_f[256];

@@ -1,0 +1,129 @@
+// pgi_tag_kernels.cuh — tag-array lookup kernels (K2a/K2b/K3/K4 of pgi_kernels.cuh's table) and the
+// random-access microbenchmark. Semantics: TagArray::query_compressed_compact / query_compressed,
+// src/tag_arrays.cpp:780-890 (rank on bwt_intervals, sampled select, decode, sort, unique).
+#pragma once
+#include "pgi_kernels.cuh"
+
+namespace pgi {
+
+// K2a. One thread per MEM: the two ranks and the select; sizes only.
+// Intervals come either from ordered MEM records (mems != nullptr: [bwt_start, bwt_start + size - 1])
+// or from explicit start/end arrays.
+__global__ void tag_plan_kernel(TagDev t, uint64_t n, const uint4 *mems, const uint64_t *start, const uint64_t *end,
+                                uint64_t *n_runs, uint64_t *cnt, uint64_t *first_item, uint32_t *skip) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint64_t s, e;
+    if (mems) {
+        const uint4 r = __ldg(mems + 2 * i + 1);
+        s = r.x | ((uint64_t) r.y << 32);
+        e = s + (r.z | ((uint64_t) r.w << 32)) - 1;
+    } else { s = start[i]; e = end[i]; }
+    const TagPlan p = tag_plan(t, s, e);
+    n_runs[i] = p.n_runs; cnt[i] = p.count; first_item[i] = p.first_item; skip[i] = (uint32_t) p.skip;
+}
+
+// K2b (short lists). One thread per MEM: decode <= PGI_TAG_SMALL runs, insertion sort, unique; the unique
+// values go to raw[raw_off[m] ..) and their number to ucnt[m]. Longer lists are queued for the warp kernels.
+__global__ void tag_small_kernel(TagDev t, uint64_t n, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *first_item,
+                                 const uint32_t *skip, uint64_t *raw, uint64_t *ucnt, uint64_t *large_list,
+                                 unsigned long long *large_count) {
+    const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (m >= n) return;
+    const uint64_t c = cnt[m];
+    if (c == 0) { ucnt[m] = 0; return; }
+    if (c > PGI_TAG_SMALL) { large_list[atomicAdd(large_count, 1ull)] = m; return; }
+    uint64_t v[PGI_TAG_SMALL];
+    uint32_t k = 0;                                     // sorted unique prefix v[0..k)
+    uint64_t loc = first_item[m]; const uint32_t sk = skip[m];
+    if (t.layout != 0) for (uint32_t i = 0; i < sk; ++i) (void) tag_bytecode_next(t, loc);
+    else loc += sk;
+    for (uint32_t i = 0; i < (uint32_t) c; ++i) {
+        const uint64_t x = t.layout == 0 ? tag_item_compact(t, loc++) : tag_value_bytecode(tag_bytecode_next(t, loc));
+        uint32_t p = k;                                  // insert keeping v sorted, dropping duplicates
+        while (p > 0 && v[p - 1] > x) --p;
+        if (p > 0 && v[p - 1] == x) continue;
+        for (uint32_t q = k; q > p; --q) v[q] = v[q - 1];
+        v[p] = x; ++k;
+    }
+    uint64_t *dst = raw + raw_off[m];
+    for (uint32_t i = 0; i < k; ++i) dst[i] = v[i];
+    ucnt[m] = k;
+}
+
+// K2b (long lists). One warp per queued MEM: decode its runs into raw (lane-strided for the bit-packed
+// layout; the ByteCode stream is inherently serial and is walked by lane 0).
+__global__ void tag_large_decode_kernel(TagDev t, uint64_t n_large, const uint64_t *large_list, const uint64_t *cnt,
+                                        const uint64_t *raw_off, const uint64_t *first_item, const uint32_t *skip,
+                                        uint64_t *raw, uint64_t *seg_begin, uint64_t *seg_end) {
+    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31u;
+    if (w >= n_large) return;
+    const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
+    if (lane == 0) { seg_begin[w] = o; seg_end[w] = o + c; }
+    if (t.layout == 0) {
+        const uint64_t f = first_item[m] + skip[m];
+        for (uint64_t i = lane; i < c; i += 32) raw[o + i] = tag_item_compact(t, f + i);
+    } else if (lane == 0) {
+        uint64_t loc = first_item[m];
+        for (uint32_t i = 0, sk = skip[m]; i < sk; ++i) (void) tag_bytecode_next(t, loc);
+        for (uint64_t i = 0; i < c; ++i) raw[o + i] = tag_value_bytecode(tag_bytecode_next(t, loc));
+    }
+}
+
+// K3 (long lists). One warp per queued MEM: unique of the sorted segment in `sorted`, written back to raw.
+__global__ void tag_large_unique_kernel(uint64_t n_large, const uint64_t *large_list, const uint64_t *cnt, const uint64_t *raw_off,
+                                        const uint64_t *sorted, uint64_t *raw, uint64_t *ucnt) {
+    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31u;
+    if (w >= n_large) return;
+    const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
+    uint64_t k = 0;
+    for (uint64_t b = 0; b < c; b += 32) {
+        const uint64_t i = b + lane;
+        bool keep = false; uint64_t x = 0;
+        if (i < c) { x = sorted[o + i]; keep = i == 0 || sorted[o + i - 1] != x; }
+        const unsigned mask = __ballot_sync(0xFFFFFFFFu, keep);
+        if (keep) raw[o + k + __popc(mask & ((1u << lane) - 1u))] = x;
+        k += __popc(mask);
+    }
+    if (lane == 0) ucnt[m] = k;
+}
+
+// K4. Compaction: unique lists -> tags[tag_off[m] ..). Short lists: one thread per MEM.
+__global__ void tag_copy_kernel(uint64_t n, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *tag_off,
+                                const uint64_t *raw, uint64_t *tags) {
+    const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (m >= n || cnt[m] > PGI_TAG_SMALL) return;
+    const uint64_t a = tag_off[m], k = tag_off[m + 1] - a; const uint64_t *src = raw + raw_off[m];
+    for (uint64_t i = 0; i < k; ++i) tags[a + i] = src[i];
+}
+__global__ void tag_large_copy_kernel(uint64_t n_large, const uint64_t *large_list, const uint64_t *raw_off, const uint64_t *tag_off,
+                                      const uint64_t *raw, uint64_t *tags) {
+    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31u;
+    if (w >= n_large) return;
+    const uint64_t m = large_list[w], a = tag_off[m], k = tag_off[m + 1] - a, o = raw_off[m];
+    for (uint64_t i = lane; i < k; i += 32) tags[a + i] = raw[o + i];
+}
+
+// M1. Random-access roofline: every thread walks `chain` dependent hops through a buffer of `n_slots`
+// slots of BYTES bytes, reading the whole slot each hop (BYTES = 32: one sector; 64: one run block).
+template <int BYTES>
+__global__ void gather_kernel(const uint4 *buf, uint64_t n_slots, uint64_t n_threads, int chain, unsigned long long *sink) {
+    const uint64_t tid = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (tid >= n_threads) return;
+    uint64_t x = tid * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull, acc = 0;
+    for (int h = 0; h < chain; ++h) {
+        x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+        const uint64_t slot = x % n_slots;
+        const uint4 *p = buf + slot * (BYTES / 16);
+        uint64_t s = 0;
+#pragma unroll
+        for (int q = 0; q < BYTES / 16; ++q) { const uint4 v = __ldg(p + q); s += v.x + v.y + v.z + v.w; }
+        acc += s; x += s;                                // next address depends on the loaded data
+    }
+    if (acc == 0x1234567ull) atomicAdd(sink, 1ull);
+}
+
+} // namespace pgi

@@ -1,0 +1,132 @@
+"""GPU parity: the CUDA path (through the C ABI of include/pgi.h) against the CPU oracle, bit-exact."""
+import numpy as np, pytest
+import orc, datasets
+from conftest import load_package
+
+pytestmark = pytest.mark.gpu
+
+@pytest.fixture(scope="module")
+def capi():
+    c = load_package().capi
+    assert c.lib().pgi_device_count() > 0, "no CUDA device visible: the product has no CPU path"
+    return c
+
+def cases():
+    xy = dict(ri=datasets.gold("xy.ri"), tags=datasets.gold("xy_bidirectional_compressed.tags"), layout=1, text=datasets.gold("contigs_xy"))
+    two = dict(ri=datasets.gold("two_contig_xy.ri"), tags=None, layout=0, text=datasets.gold("contigs_XY.txt"))
+    out = {"xy_legacy_bytecode": xy, "two_contig_legacy": two}
+    for enc in (True, False):
+        s = datasets.synth_index(encoded=enc)
+        out["synth_%s_compact" % ("enc" if enc else "leg")] = dict(ri=s["ri"], tags=s["tags0"], layout=0, text=s["text"])
+    s = datasets.synth_index(encoded=True)
+    out["synth_enc_bytecode"] = dict(ri=s["ri"], tags=s["tags1"], layout=1, text=s["text"])
+    return out
+
+CASES = None
+def get_case(name):
+    global CASES
+    if CASES is None: CASES = cases()
+    return CASES[name]
+NAMES = ["xy_legacy_bytecode", "two_contig_legacy", "synth_enc_compact", "synth_leg_compact", "synth_enc_bytecode"]
+
+def compare(g, o, with_tags):
+    assert g["n_mems"] == o["n_mems"]
+    assert np.array_equal(g["mem_off"], o["mem_off"])
+    assert np.array_equal(g["mems"], o["mems"])
+    if with_tags:
+        assert np.array_equal(g["n_runs"], o["n_runs"])
+        assert np.array_equal(g["tag_off"], o["tag_off"])
+        assert np.array_equal(g["tags"], o["tags"])
+    assert g["text"] == o["text"]
+
+@pytest.mark.parametrize("name", NAMES)
+def test_extend_and_rank(capi, name):
+    c = get_case(name)
+    o = orc.Index(c["ri"]); g = capi.Index(c["ri"])
+    rng = np.random.default_rng(3); N = 50000; n = o.n
+    iv = np.zeros((N, 3), dtype=np.uint64)
+    k = rng.integers(0, n, N); sz = np.minimum(rng.integers(0, 300, N), n - k)
+    iv[:, 0] = k; iv[:, 1] = rng.integers(0, n, N); iv[:, 2] = sz
+    iv[:200] = [0, 0, n]
+    iv[200:300, 0] = rng.integers(0, 2 * n, 100)             # positions beyond n (defined UB: read as n)
+    sym = rng.choice(np.frombuffer(b"ACGTN\n\0acgtnX\xff", dtype=np.uint8), N); d = rng.integers(0, 2, N).astype(np.uint8)
+    assert np.array_equal(g.extend_batch(iv, sym, d), o.extend_batch(iv, sym, d))
+    pos = np.concatenate([rng.integers(0, n + 1, 20000), [0, n, n - 1, 1]]).astype(np.uint64)
+    assert np.array_equal(g.rank_batch(pos), o.rank_batch(pos))
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("params", [(20, 1), (5, 1), (1, 1), (10, 3), (31, 2)])
+def test_find_mems(capi, name, params):
+    c = get_case(name); ml, mo = params
+    o = orc.Index(c["ri"], c["tags"], c["layout"]); g = capi.Index(c["ri"], c["tags"], c["layout"])
+    nreads = 3000 if ml >= 10 else 400
+    reads, off = datasets.sample_reads(c["text"], nreads, 150, 0.01, seed=ml * 7 + mo)
+    R = o.find_mems(reads, off, ml, mo, count_work=True); G = g.find_mems(reads, off, ml, mo)
+    compare(G, R, c["tags"] is not None)
+    assert G["extensions"] == R["counters"]["E"]
+
+@pytest.mark.parametrize("name", ["xy_legacy_bytecode", "synth_enc_compact"])
+def test_ragged_and_edge_reads(capi, name):
+    c = get_case(name)
+    o = orc.Index(c["ri"], c["tags"], c["layout"]); g = capi.Index(c["ri"], c["tags"], c["layout"])
+    rs = datasets.ragged_reads(c["text"], seed=5)
+    reads, off = orc.pack_reads(rs)
+    for ml, mo in [(20, 1), (3, 1), (1, 2)]:
+        compare(g.find_mems(reads, off, ml, mo), o.find_mems(reads, off, ml, mo), True)
+    e = np.zeros(0, dtype=np.uint8)                           # empty batch
+    G = g.find_mems(e, np.zeros(1, dtype=np.uint64), 20, 1)
+    assert G["n_mems"] == 0 and G["n_reads"] == 0
+
+@pytest.mark.parametrize("name", ["xy_legacy_bytecode", "synth_enc_compact", "synth_enc_bytecode"])
+def test_tag_query_batch(capi, name):
+    c = get_case(name)
+    o = orc.Index(c["ri"], c["tags"], c["layout"]); g = capi.Index(c["ri"], c["tags"], c["layout"])
+    rng = np.random.default_rng(11); N = 4000; n = o.n
+    st = rng.integers(0, n, N).astype(np.uint64)
+    ln = np.where(rng.random(N) < 0.9, rng.integers(1, 40, N), rng.integers(40, 3000, N)).astype(np.uint64)
+    en = np.minimum(st + ln - 1, np.uint64(n + 40))          # a few intervals run past the end of the array
+    G = g.tag_query_batch(st, en)
+    for i in range(N):
+        nr, tv = o.tag_query(int(st[i]), int(en[i]))
+        assert G["n_runs"][i] == nr, i
+        a, b = G["tag_off"][i], G["tag_off"][i + 1]
+        assert np.array_equal(G["tags"][a:b], tv), i
+
+def test_first_mod_10_quirk(capi):
+    """intervals whose first run index is a multiple of 10 start one run late."""
+    c = get_case("synth_enc_compact"); o = orc.Index(c["ri"], c["tags"], 0); g = capi.Index(c["ri"], c["tags"], 0)
+    st = np.arange(0, min(o.n, 4000), dtype=np.uint64); en = st + np.uint64(3)
+    G = g.tag_query_batch(st, en)
+    for i in range(len(st)):
+        nr, tv = o.tag_query(int(st[i]), int(en[i]))
+        a, b = G["tag_off"][i], G["tag_off"][i + 1]
+        assert G["n_runs"][i] == nr and np.array_equal(G["tags"][a:b], tv)
+
+def test_clone_and_batch_api(capi):
+    c = get_case("synth_enc_compact"); o = orc.Index(c["ri"], c["tags"], 0); g = capi.Index(c["ri"], c["tags"], 0)
+    g2 = g.clone_to(0)
+    reads, off = datasets.sample_reads(c["text"], 2000, 150, 0.02, seed=9)
+    R = o.find_mems(reads, off, 20, 1)
+    compare(g2.find_mems(reads, off, 20, 1), R, True)
+    b = capi.Batch(g2)
+    for _ in range(2):                                        # context reuse
+        b.upload(reads.ctypes.data, off.ctypes.data, len(off) - 1); b.run(20, 1)
+        G = b.fetch(text=True); compare(G, R, True)
+    ms = b.stage_ms(); assert ms[6] >= 5 and ms[5] > 0
+
+def test_large_batch_properties(capi):
+    """Many reads; size-independent checks (every MEM is >= min_len, intervals non-empty, offsets monotone,
+    tags sorted unique) plus oracle equality on a slice."""
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    g = capi.Index(s["ri"], s["tags0"], 0); o = orc.Index(s["ri"], s["tags0"], 0)
+    reads, off = datasets.sample_reads(s["text"], 200000, 150, 0.01, seed=4)
+    G = g.find_mems(reads, off, 20, 1, text=False)
+    m = G["mems"]
+    assert (m[:, 1] - m[:, 0] >= 20).all() and (m[:, 3].astype(np.int64) > 0).all() and (m[:, 1] <= 150).all()
+    assert (np.diff(G["mem_off"].astype(np.int64)) >= 0).all() and (np.diff(G["tag_off"].astype(np.int64)) >= 0).all()
+    for i in np.random.default_rng(0).integers(0, G["n_mems"], 2000):
+        t = G["tags"][G["tag_off"][i]:G["tag_off"][i + 1]]
+        assert (np.diff(t.astype(np.int64)) > 0).all()
+    k = 5000
+    R = o.find_mems(reads[: k * 150], off[: k + 1], 20, 1)
+    assert np.array_equal(G["mems"][: R["n_mems"]], R["mems"]) and np.array_equal(G["tags"][: R["n_tags"]], R["tags"])
