@@ -129,7 +129,7 @@ int pgi_batch_device_result(pgi_batch *, pgi_result *out);
 int pgi_batch_fetch(pgi_batch *, pgi_result *out);
 /* Device time of the stages of the last run, from CUDA events on the batch's stream, in milliseconds:
  * [0] MEM kernel (fmd_mem_kernel), [1] MEM ordering (scan + scatter), [2] tag sizing, [3] tag decode + sort,
- * [4] tag unique + compaction, [5] whole run, [6] number of kernel launches in the run, [7] MEM kernel re-runs. */
+ * [4] tag unique + compaction, [5] whole run, [6] number of this library's own kernel launches in the run (CUB scans / sorts excluded), [7] MEM kernel re-runs. */
 int pgi_batch_stage_ms(pgi_batch *, double ms[8]);
 
 /* Text of src/find_mems.cpp:115-139 (+ tag lines of src/tag_arrays.cpp:885-889) for a host result;

@@ -69,3 +69,22 @@ def sample_reads(text: bytes, n_reads: int, read_len: int, sub=0.0, indel=0.0, s
                                     ctypes.c_double, ctypes.c_double, ctypes.c_uint64, ctypes.c_void_p]
     if L.prep_sample_reads(text, len(text), n_reads, read_len, float(sub), float(indel), seed, out.ctypes.data): _err(L)
     return out
+
+def tags_from_runs(value: np.ndarray, length: np.ndarray, layout=0):
+    """(value, length) tag runs -> (tags file bytes, number of runs after splitting at 511)."""
+    L = lib(); p = ctypes.c_void_p(); n = ctypes.c_uint64(); nr = ctypes.c_uint64()
+    v = np.ascontiguousarray(value, dtype=np.uint64); l = np.ascontiguousarray(length, dtype=np.uint64)
+    if L.prep_tags_from_runs(v.ctypes.data_as(ctypes.c_void_p), l.ctypes.data_as(ctypes.c_void_p), ctypes.c_uint64(len(v)), int(layout),
+                             ctypes.byref(p), ctypes.byref(n), ctypes.byref(nr)): _err(L)
+    return _take(L, p, n), nr.value
+
+def rlbwt_from_runs(sym: np.ndarray, length: np.ndarray) -> bytes:
+    """(symbol byte, length) BWT runs -> .rl_bwt file bytes (deps/grlBWT/include/bwt_io.h:40-58)."""
+    length = np.ascontiguousarray(length, dtype=np.uint64); sym = np.ascontiguousarray(sym, dtype=np.uint8)
+    mx = int(length.max()) if len(length) else 1
+    fb = max(1, (mx.bit_length() + 7) // 8)
+    rec = np.zeros((len(sym), 1 + fb), dtype=np.uint8)
+    rec[:, 0] = sym
+    for i in range(fb):
+        rec[:, 1 + i] = ((length >> np.uint64(8 * i)) & np.uint64(0xFF)).astype(np.uint8)
+    return np.array([1, fb], dtype=np.uint64).tobytes() + rec.tobytes()

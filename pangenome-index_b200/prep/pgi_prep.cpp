@@ -343,6 +343,21 @@ int prep_tags_from_rows(const uint64_t *row_value, uint64_t n, int layout, uint8
     } catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
+// (value, length) tag runs -> tags file bytes; runs longer than 511 are split (tag_arrays.cpp:942-957).
+int prep_tags_from_runs(const uint64_t *value, const uint64_t *len, uint64_t n_in, int layout, uint8_t **out, uint64_t *out_len, uint64_t *n_runs) {
+    try {
+        TagRuns t; t.value.reserve(n_in + n_in / 16); t.len.reserve(n_in + n_in / 16);
+        for (uint64_t i = 0; i < n_in; ++i) {
+            uint64_t l = len[i];
+            while (l >= 512) { t.value.push_back(value[i]); t.len.push_back(511); l -= 511; }
+            if (l > 0) { t.value.push_back(value[i]); t.len.push_back(l); }
+        }
+        std::vector<uint8_t> f = serialize_tags(t, layout);
+        *out = dup_out(f, out_len); if (n_runs) *n_runs = t.value.size();
+        return 0;
+    } catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+
 // Sample n_reads reads of read_len from newline-terminated sequences, uniform over valid start positions,
 // with i.i.d. substitution rate `sub` and 1-bp indel rate `indel` (each split evenly insert/delete).
 // Output: fixed-stride buffer reads[n_reads*read_len] (reads never span a newline).

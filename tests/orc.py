@@ -58,8 +58,11 @@ class Index:
         self.info = list(info); self.n = info[0]; self.sigma = info[1]
         self.C = list(C)[: self.sigma]; self.sym_map = bytes(sm)
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().orc_index_free(self.h); self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().orc_index_free(self.h); self.h = None
+        except Exception:
+            pass
     def extend_batch(self, iv3, sym, direction):
         iv3 = np.ascontiguousarray(iv3, dtype=np.uint64); sym = np.ascontiguousarray(sym, dtype=np.uint8)
         direction = np.ascontiguousarray(direction, dtype=np.uint8); out = np.zeros_like(iv3)
@@ -78,22 +81,25 @@ class Index:
         out = np.zeros(cap, dtype=np.uint64); n = ctypes.c_uint64()
         nr = lib().orc_tag_query(self.h, start, end, out.ctypes.data, cap, ctypes.byref(n))
         return nr, out[: n.value].copy()
-    def find_mems(self, reads, read_off, min_len, min_occ, with_tags=None, threads=0, count_work=False):
+    def find_mems(self, reads, read_off, min_len, min_occ, with_tags=None, threads=0, count_work=False, text=True):
         """reads: uint8 array (concatenated), read_off: uint64 [n+1] -> dict of numpy arrays."""
         reads = np.ascontiguousarray(reads, dtype=np.uint8); read_off = np.ascontiguousarray(read_off, dtype=np.uint64)
         if with_tags is None:
             with_tags = self.has_tags
-        res = OrcResult()
+        import time
+        res = OrcResult(); t0 = time.perf_counter()
         if lib().orc_find_mems(self.h, reads.ctypes.data, read_off.ctypes.data, len(read_off) - 1, min_len, min_occ,
                                int(with_tags), threads, int(count_work), ctypes.byref(res)):
             raise RuntimeError(lib().orc_last_error().decode())
-        out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags,
+        seconds = time.perf_counter() - t0          # the C call only: MEMs + tags into binary arrays, no text
+        out = dict(seconds=seconds, n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags,
                    mem_off=_np(res.mem_off, res.n_reads + 1), mems=_np(res.mems, 4 * res.n_mems).reshape(-1, 4),
                    tag_off=_np(res.tag_off, res.n_mems + 1), tags=_np(res.tags, res.n_tags), n_runs=_np(res.n_runs, res.n_mems),
                    counters=dict(zip(["E", "D", "M", "tag_runs", "tag_skipped", "tag_item_sectors"], list(res.counters)[:6])))
-        ln = ctypes.c_uint64()
-        p = lib().orc_format_text(ctypes.byref(res), 1, int(with_tags), ctypes.byref(ln))
-        out["text"] = ctypes.string_at(p, ln.value); lib().orc_free(p)
+        if text:
+            ln = ctypes.c_uint64()
+            p = lib().orc_format_text(ctypes.byref(res), 1, int(with_tags), ctypes.byref(ln))
+            out["text"] = ctypes.string_at(p, ln.value); lib().orc_free(p)
         lib().orc_result_free(ctypes.byref(res))
         return out
 

@@ -36,8 +36,11 @@ class Index:
                 "tag_m", "tag_shift", "tag_low_bytes", "starts_regular"]
         self.info = dict(zip(keys, list(info)))
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().sim_free(self.h); self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().sim_free(self.h); self.h = None
+        except Exception:
+            pass
     def extend_batch(self, iv3, sym, direction):
         iv3 = np.ascontiguousarray(iv3, dtype=np.uint64); sym = np.ascontiguousarray(sym, dtype=np.uint8)
         direction = np.ascontiguousarray(direction, dtype=np.uint8); out = np.zeros_like(iv3)

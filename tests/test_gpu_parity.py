@@ -112,7 +112,7 @@ def test_clone_and_batch_api(capi):
     for _ in range(2):                                        # context reuse
         b.upload(reads.ctypes.data, off.ctypes.data, len(off) - 1); b.run(20, 1)
         G = b.fetch(text=True); compare(G, R, True)
-    ms = b.stage_ms(); assert ms[6] >= 5 and ms[5] > 0
+    ms = b.stage_ms(); assert ms[6] >= 4 and ms[5] > 0
 
 def test_large_batch_properties(capi):
     """Many reads; size-independent checks (every MEM is >= min_len, intervals non-empty, offsets monotone,
