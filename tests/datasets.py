@@ -73,7 +73,7 @@ def synth_index(ref_len=3000, n_hap=4, seed=7, encoded=True):
     val[(off >= lens[seq_id])] = 0            # endmarker rows (merge_tags.cpp:619-622)
     tags0, nr0 = prep.tags_from_rows(val, 0)
     tags1, nr1 = prep.tags_from_rows(val, 1)
-    return dict(text=text, seqs=seqs, ri=ri, tags0=tags0, tags1=tags1, info=info, rl_bwt=rl, n_tag_runs=nr0)
+    return dict(text=text, seqs=seqs, ri=ri, tags0=tags0, tags1=tags1, info=info, rl_bwt=rl, n_tag_runs=nr0, row_val=val)
 
 def sample_reads(text, n_reads, read_len, sub, seed, indel=0.0):
     prep = load_package().prep

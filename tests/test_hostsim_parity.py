@@ -1,0 +1,74 @@
+"""CPU: the PRODUCT's device arithmetic (csrc/pgi_core.cuh: block locate, packed run scan, FMD extension, MEM lane
+state machine, tag plan / item decoders) and host flattener (csrc/pgi_flatten.hpp), compiled as plain C++ by
+tests/hostsim (test-only), against the oracle. This is the GPU-less safety net for kernel changes; the same
+comparisons run on the GPU through the C ABI in test_gpu_parity.py."""
+import numpy as np, pytest
+import orc, sim, datasets
+
+def case(name):
+    if name == "xy_legacy_bytecode":
+        return dict(ri=datasets.gold("xy.ri"), tags=datasets.gold("xy_bidirectional_compressed.tags"), layout=1, text=datasets.gold("contigs_xy"))
+    if name == "two_contig_legacy":
+        return dict(ri=datasets.gold("two_contig_xy.ri"), tags=None, layout=0, text=datasets.gold("contigs_XY.txt"))
+    enc = name != "synth_leg_compact"
+    s = datasets.synth_index(encoded=enc)
+    if name == "synth_enc_bytecode":
+        return dict(ri=s["ri"], tags=s["tags1"], layout=1, text=s["text"])
+    return dict(ri=s["ri"], tags=s["tags0"], layout=0, text=s["text"])
+
+NAMES = ["xy_legacy_bytecode", "two_contig_legacy", "synth_enc_compact", "synth_leg_compact", "synth_enc_bytecode"]
+
+@pytest.mark.parametrize("name", NAMES)
+def test_flatten_facts(name):
+    c = case(name); o = orc.Index(c["ri"], c["tags"], c["layout"]); g = sim.Index(c["ri"], c["tags"], c["layout"])
+    assert g.info["n"] == o.n and g.info["sigma"] == o.sigma and g.info["encoded"] == o.info[2]
+    assert g.info["n_ref_blocks"] == o.info[4]
+    assert g.info["has_quirk"] == (1 if name in ("xy_legacy_bytecode", "two_contig_legacy") else 0)   # legacy + sigma 5
+    if c["tags"]:
+        assert g.info["tag_m"] == o.info[12]
+
+@pytest.mark.parametrize("name", NAMES)
+def test_extend_matches_oracle(name):
+    c = case(name); o = orc.Index(c["ri"]); g = sim.Index(c["ri"])
+    rng = np.random.default_rng(3); N = 40000; n = o.n
+    iv = np.zeros((N, 3), dtype=np.uint64)
+    k = rng.integers(0, n, N); sz = np.minimum(rng.integers(0, 400, N), n - k)
+    iv[:, 0] = k; iv[:, 1] = rng.integers(0, n, N); iv[:, 2] = sz
+    iv[:300] = [0, 0, n]
+    iv[300:400, 0] = rng.integers(0, 2 * n, 100)             # positions beyond n (defined UB: read as n)
+    iv[400:500, 2] = rng.integers(0, n, 100)                 # long intervals
+    iv[400:500, 0] = np.minimum(iv[400:500, 0], n - iv[400:500, 2])
+    sym = rng.choice(np.frombuffer(b"ACGTN\n\0acgtnX\xff", dtype=np.uint8), N); d = rng.integers(0, 2, N).astype(np.uint8)
+    assert np.array_equal(g.extend_batch(iv, sym, d), o.extend_batch(iv, sym, d))
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("params", [(20, 1), (5, 1), (1, 1), (10, 3)])
+def test_lane_machine_matches_find_all_mems(name, params):
+    c = case(name); ml, mo = params
+    o = orc.Index(c["ri"]); g = sim.Index(c["ri"])
+    nreads = 300 if ml >= 10 else 60
+    reads, off = datasets.sample_reads(c["text"], nreads, 150, 0.02, seed=ml + 3 * mo)
+    R = o.find_mems(reads, off, ml, mo, with_tags=False, count_work=True, threads=1)
+    tot_ext = 0
+    for i in range(nreads):
+        rd = reads[int(off[i]):int(off[i + 1])].tobytes()
+        mems, ne = g.find_mems(rd, ml, mo); tot_ext += ne
+        assert np.array_equal(mems, R["mems"][int(R["mem_off"][i]):int(R["mem_off"][i + 1])]), i
+    assert tot_ext == R["counters"]["E"]
+    for rd in datasets.ragged_reads(c["text"], seed=2, n=40):
+        buf, o2 = orc.pack_reads([rd])
+        want = o.find_mems(buf, o2, ml, mo, with_tags=False)["mems"]
+        got, _ = g.find_mems(rd, ml, mo)
+        assert np.array_equal(got, want), rd
+
+@pytest.mark.parametrize("name", ["xy_legacy_bytecode", "synth_enc_compact", "synth_enc_bytecode"])
+def test_tag_plan_matches_oracle(name):
+    c = case(name); o = orc.Index(c["ri"], c["tags"], c["layout"]); g = sim.Index(c["ri"], c["tags"], c["layout"])
+    rng = np.random.default_rng(11); n = o.n
+    for _ in range(3000):
+        a = int(rng.integers(0, n)); b = min(n + 30, a + int(rng.integers(0, 50 if rng.random() < 0.9 else 2500)))
+        nr, tv = o.tag_query(a, b); nr2, tv2 = g.tag_query(a, b)
+        assert nr == nr2 and np.array_equal(tv, tv2), (a, b)
+    for a in range(0, min(n, 1500)):                          # every alignment of the first % 10 rule
+        nr, tv = o.tag_query(a, a + 2); nr2, tv2 = g.tag_query(a, a + 2)
+        assert nr == nr2 and np.array_equal(tv, tv2), a
