@@ -55,82 +55,95 @@ PGI_HD uint64_t ld64(const uint64_t *p) {
     return *p;
 #endif
 }
-PGI_HD void ld_block(const uint64_t *blk, uint64_t w[8]) {
+// One 64-byte run block as sixteen u32 words (four 128-bit loads of one aligned 64 B line).
+PGI_HD void ld_block(const uint64_t *blk, uint32_t w[16]) {
 #if defined(__CUDA_ARCH__)
-    const uint4 *q = reinterpret_cast<const uint4 *>(blk);      // four 128-bit loads: one 64-byte block
-    uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
-    w[0] = a.x | ((uint64_t) a.y << 32); w[1] = a.z | ((uint64_t) a.w << 32);
-    w[2] = b.x | ((uint64_t) b.y << 32); w[3] = b.z | ((uint64_t) b.w << 32);
-    w[4] = c.x | ((uint64_t) c.y << 32); w[5] = c.z | ((uint64_t) c.w << 32);
-    w[6] = d.x | ((uint64_t) d.y << 32); w[7] = d.z | ((uint64_t) d.w << 32);
+    const uint4 *q = reinterpret_cast<const uint4 *>(blk);
+    const uint4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2), d = __ldg(q + 3);
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+    w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
 #else
-    for (int i = 0; i < 8; ++i) w[i] = blk[i];
+    for (int i = 0; i < 8; ++i) { w[2 * i] = (uint32_t) blk[i]; w[2 * i + 1] = (uint32_t) (blk[i] >> 32); }
 #endif
+}
+PGI_HD uint64_t block_start(const uint32_t w[16]) { return (uint64_t) w[0] | (uint64_t) (w[7] & 0xFFu) << 32; }
+PGI_HD uint64_t block_start_at(const uint64_t *blocks, uint64_t idx) {      // start of block idx, from memory
+    const uint64_t a = ld64(blocks + idx * PGI_BLOCK_WORDS), b = ld64(blocks + idx * PGI_BLOCK_WORDS + 3);
+    return (a & 0xFFFFFFFFull) | ((b >> 32) & 0xFFull) << 32;
 }
 
 // ------------------------------------------------------------------------------------ block locate
 // Index of the run block containing BWT position pos (pos <= n): last block whose start <= pos.
-// Replaces blocks_start_pos.predecessor(pos) (src/r-index.cpp:594,621): one directory word, and a
-// second one only when pos lies behind the first block boundary of its bucket.
-PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
-    const uint64_t b = pos >> ix.dir_shift;
-    const uint64_t e = ld64(ix.dir + b);
-    uint64_t idx = e & 0xFFFFFFFFull;
-    const uint64_t rel = pos - (b << ix.dir_shift);
-    if (rel >= (e >> 32)) {
-        const uint64_t hi = ld64(ix.dir + b + 1) & 0xFFFFFFFFull;
-        if (hi == idx + 1) idx = hi;
-        else {                                      // several boundaries in this bucket: search block starts in (idx, hi]
-            uint64_t lo = idx + 1, up = hi;          // invariant: start(lo) <= pos
-            while (lo < up) {
-                uint64_t mid = (lo + up + 1) >> 1;
-                uint64_t st = ld64(ix.blocks + mid * PGI_BLOCK_WORDS) & 0xFFFFFFFFFFull;
-                if (st <= pos) lo = mid; else up = mid - 1;
-            }
-            idx = lo;
+// Replaces blocks_start_pos.predecessor(pos) (src/r-index.cpp:594,621): ONE directory word holds the block
+// index at the bucket start and the offsets of the first two block boundaries inside the bucket
+// (pgi_layout.h); only buckets with more than two boundaries fall into the search below.
+PGI_HD uint64_t locate_from_dir(const RiDev &ix, uint64_t pos, uint64_t e) {
+    const uint32_t rel = (uint32_t) pos & ((1u << ix.dir_shift) - 1u);
+    const uint32_t t1 = (uint32_t) (e >> 32) & 0xFFFFu, t2 = (uint32_t) (e >> 48) & 0x7FFFu;
+    uint64_t idx = (e & 0xFFFFFFFFull) + (rel >= t1) + (rel >= t2);
+    if ((e >> 63) && rel >= t2) {                     // rare: more boundaries; search block starts in (idx, hi]
+        const uint64_t hi = ld64(ix.dir + (pos >> ix.dir_shift) + 1) & 0xFFFFFFFFull;
+        uint64_t lo = idx, up = hi;                    // invariant: start(lo) <= pos
+        while (lo < up) {
+            const uint64_t mid = (lo + up + 1) >> 1;
+            if (block_start_at(ix.blocks, mid) <= pos) lo = mid; else up = mid - 1;
         }
+        idx = lo;
     }
     return idx;
 }
-
-// Symbol counts before a block, per nuc code, from its header words.
-PGI_HD void block_cums(const uint64_t w[8], uint64_t cum[6]) {
-    cum[1] = (w[0] >> 40) | ((w[1] & 0xFFFFull) << 24);
-    cum[2] = (w[1] >> 16) & 0xFFFFFFFFFFull;
-    cum[3] = w[2] & 0xFFFFFFFFFFull;
-    cum[5] = (w[2] >> 40) | ((w[3] & 0xFFFFull) << 24);
-    cum[0] = (w[3] >> 16) & 0xFFFFFFFFull;
-    cum[4] = (w[3] >> 48) | ((w[4] & 0xFFFFull) << 16);
+PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
+    return locate_from_dir(ix, pos, ld64(ix.dir + (pos >> ix.dir_shift)));
 }
 
-// 16-bit run entry i (0..14) of a block.
-PGI_HD uint32_t block_entry(const uint64_t w[8], int i) {
-    const int bit = 16 + 16 * i;                    // relative to word 4
-    return (uint32_t) (w[4 + (bit >> 6)] >> (bit & 63)) & 0xFFFFu;
-}
+// ------------------------------------------------------------------------------------ in-block rank
+// Weighted rank of one position. tbl = six 4-bit fields (bits 0..2 weight w[c], bit 3 "main symbol"), the low
+// 24 bits of an extension descriptor. Returns, for the first `rel` positions of the block plus the block's
+// cumulative header:   W = sum_c w[c] * rank_c(pos)      M = rank_main(pos)   (0 when no field has bit 3).
+// Per run entry: one table shift indexed by the raw entry (code4 sits in its low 5 bits), min, subtract and one
+// 32x32->64 multiply-add whose multiplier carries the weight in bits 0..2 and the main flag in bit 21
+// (sum of weight * count < 7 * 15 * 2047 < 2^21, so the two partial sums never meet).
+struct PosRank { uint64_t W, M; };
 
-// In-block counts of the six codes among the first rel1 and the first rel2 positions of a block.
-// Packed accumulators: codes 0..2 in lo, 3..5 in hi, 21 bits per field (a block covers < 2^17 positions).
-struct Packed6 { uint64_t lo, hi; };
-PGI_HD void block_scan2(const uint64_t w[8], uint64_t rel1, uint64_t rel2, Packed6 &c1, Packed6 &c2) {
-    c1.lo = c1.hi = c2.lo = c2.hi = 0;
-    // a block covers at most 15 * 8191 positions; clamp so the 32-bit arithmetic below is exact
-    uint32_t r1 = rel1 > 0x3FFFFull ? 0x3FFFFu : (uint32_t) rel1;
-    uint32_t r2 = rel2 > 0x3FFFFull ? 0x3FFFFu : (uint32_t) rel2;
-#pragma unroll
-    for (int i = 0; i < PGI_RUNS_PER_BLOCK; ++i) {
-        const uint32_t e = block_entry(w, i);
-        const uint32_t len = e >> 3, code = e & 7;
-        const uint32_t t1 = len < r1 ? len : r1, t2 = len < r2 ? len : r2;
-        r1 -= t1; r2 -= t2;
-        const bool up = code >= 3;
-        const uint32_t sh = (code - (up ? 3u : 0u)) * 21u;
-        const uint64_t v1 = (uint64_t) t1 << sh, v2 = (uint64_t) t2 << sh;
-        if (up) { c1.hi += v1; c2.hi += v2; } else { c1.lo += v1; c2.lo += v2; }
+#define PGI_SCAN_ENTRY(ENT, LEN)                                                     \
+    {                                                                                  \
+        const uint32_t v_ = tbl >> ((ENT) & 31u);                                     \
+        const uint32_t l_ = (LEN);                                                     \
+        const uint32_t t_ = l_ < r ? l_ : r;                                           \
+        r -= t_;                                                                       \
+        acc += (uint64_t) t_ * (uint64_t) (((v_ << 18) | v_) & 0x200007u);             \
     }
+
+PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) {
+    const uint64_t d = pos - block_start(w);
+    uint32_t r = d > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t) d;
+    uint64_t acc = 0;
+    { const uint32_t h = w[8] >> 16; PGI_SCAN_ENTRY(h, w[8] >> 21) }
+#pragma unroll
+    for (int j = 9; j < 16; ++j) {
+        const uint32_t x = w[j], h = x >> 16;
+        PGI_SCAN_ENTRY(x, (x >> 5) & 0x7FFu)
+        PGI_SCAN_ENTRY(h, x >> 21)
+    }
+    // header: cumulative counts before the block; code c lives in word {5,1,2,3,6,4}[c], high byte as in pgi_layout.h
+    const uint32_t wNL = tbl & 7u, wA = (tbl >> 4) & 7u, wC = (tbl >> 8) & 7u, wG = (tbl >> 12) & 7u, wN = (tbl >> 16) & 7u, wT = (tbl >> 20) & 7u;
+    const uint32_t mNL = (tbl >> 3) & 1u, mA = (tbl >> 7) & 1u, mC = (tbl >> 11) & 1u, mG = (tbl >> 15) & 1u, mN = (tbl >> 19) & 1u, mT = (tbl >> 23) & 1u;
+    const uint32_t hA = (w[7] >> 8) & 0xFFu, hC = (w[7] >> 16) & 0xFFu, hG = w[7] >> 24, hT = w[8] & 0xFFu;
+    uint64_t Wl = (uint64_t) w[5] * wNL + (uint64_t) w[1] * wA + (uint64_t) w[2] * wC + (uint64_t) w[3] * wG + (uint64_t) w[6] * wN + (uint64_t) w[4] * wT;
+    uint64_t Ml = (uint64_t) w[5] * mNL + (uint64_t) w[1] * mA + (uint64_t) w[2] * mC + (uint64_t) w[3] * mG + (uint64_t) w[6] * mN + (uint64_t) w[4] * mT;
+    const uint32_t Wh = hA * wA + hC * wC + hG * wG + hT * wT, Mh = hA * mA + hC * mC + hG * mG + hT * mT;
+    PosRank o;
+    o.W = Wl + ((uint64_t) Wh << 32) + (acc & 0x1FFFFFull);
+    o.M = Ml + ((uint64_t) Mh << 32) + (acc >> 21);
+    return o;
 }
-PGI_HD uint64_t packed_get(const Packed6 &p, int c) {
-    return ((c >= 3 ? p.hi : p.lo) >> (21 * (c >= 3 ? c - 3 : c))) & 0x1FFFFFull;
+
+// True ranks of the six nuc codes at pos (batched rank API and tests; not on the MEM path).
+PGI_HD void rank_all(const RiDev &ix, uint64_t pos, uint64_t tr[6]) {
+    uint32_t w[16];
+    ld_block(ix.blocks + locate_block(ix, pos) * PGI_BLOCK_WORDS, w);
+#pragma unroll
+    for (int c = 0; c < 6; ++c) tr[c] = pos_rank(w, pos, 8u << (4 * c)).M;
 }
 
 // Quirk slot value Q(pos): column-0 cumulative of the reference's own 10-run block containing pos
@@ -146,92 +159,37 @@ PGI_HD uint64_t quirk_at(const RiDev &ix, uint64_t pos) {
     return ld64(ix.q_val + lo);
 }
 
-// True ranks of the six nuc codes at pos1 <= n and pos2 <= n (either order).
-// Both positions usually share a block once the interval is short: one 64-byte load serves both.
-PGI_HD void rank_pair(const RiDev &ix, uint64_t pos1, uint64_t pos2, uint64_t tr1[6], uint64_t tr2[6]) {
-    const uint64_t b1 = locate_block(ix, pos1), b2 = locate_block(ix, pos2);
-    uint64_t w[8], cum[6]; Packed6 c1, c2;
-    ld_block(ix.blocks + b1 * PGI_BLOCK_WORDS, w);
-    const uint64_t st1 = w[0] & 0xFFFFFFFFFFull;
-    if (b1 == b2) {
-        block_scan2(w, pos1 - st1, pos2 - st1, c1, c2);
-        block_cums(w, cum);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) { tr1[c] = cum[c] + packed_get(c1, c); tr2[c] = cum[c] + packed_get(c2, c); }
-    } else {
-        uint64_t v[8];
-        ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);
-        Packed6 d;
-        block_scan2(w, pos1 - st1, 0, c1, d);
-        block_cums(w, cum);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) tr1[c] = cum[c] + packed_get(c1, c);
-        const uint64_t st2 = v[0] & 0xFFFFFFFFFFull;
-        block_scan2(v, pos2 - st2, 0, c2, d);
-        block_cums(v, cum);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) tr2[c] = cum[c] + packed_get(c2, c);
-    }
-}
-
 // ------------------------------------------------------------------------------------ FMD extension
 struct BiInt { uint64_t k, kp; int64_t s; };      // FastLocate::bi_interval {forward, reverse, size}
 
 // One backward extension with the per-byte descriptor d (desc_b[a]); forward extension = the same on
 // the swapped interval with desc_f[a] (src/r-index.cpp:758-764). All arithmetic mod 2^64, like the
 // reference's size_t. Positions beyond n read as n (defined UB).
+// Both positions (k and k+s) go through the same straight-line code, whether or not they share a block: the
+// 32 lanes of a warp stay converged, and both directory words and both blocks are requested before any is used.
 PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
     uint64_t p2 = in.k + (uint64_t) in.s, p1 = in.k;
     if (p2 > ix.n) p2 = ix.n;
     if (p1 > ix.n) p1 = ix.n;
-    const uint64_t b1 = locate_block(ix, p1), b2 = locate_block(ix, p2);
-    uint64_t w[8], v[8];
+    const uint64_t e1 = ld64(ix.dir + (p1 >> ix.dir_shift)), e2 = ld64(ix.dir + (p2 >> ix.dir_shift));
+    const uint64_t b1 = locate_from_dir(ix, p1, e1), b2 = locate_from_dir(ix, p2, e2);
+    uint32_t w[16], v[16];
     ld_block(ix.blocks + b1 * PGI_BLOCK_WORDS, w);
-    const bool same = b1 == b2;
-    if (!same) ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);     // both block loads are in flight together
-    const uint32_t ms = (d >> 21) & 7;
-    uint64_t kp = in.kp, x = 0, y = 0;
-    {
-        const uint64_t st = w[0] & 0xFFFFFFFFFFull;
-        Packed6 c1, c2; uint64_t cum[6];
-        block_scan2(w, p1 - st, same ? p2 - st : 0, c1, c2);
-        block_cums(w, cum);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-            const uint64_t wt = (d >> (3 * c)) & 7;
-            const uint64_t r1 = cum[c] + packed_get(c1, c);
-            kp -= wt * r1;
-            if (ms == (uint32_t) c) y = r1;
-            if (same) {
-                const uint64_t r2 = cum[c] + packed_get(c2, c);
-                kp += wt * r2;
-                if (ms == (uint32_t) c) x = r2;
-            }
-        }
-    }
-    if (!same) {
-        const uint64_t st = v[0] & 0xFFFFFFFFFFull;
-        Packed6 c2, dd; uint64_t cum[6];
-        block_scan2(v, p2 - st, 0, c2, dd);
-        block_cums(v, cum);
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-            const uint64_t r2 = cum[c] + packed_get(c2, c);
-            kp += (uint64_t) ((d >> (3 * c)) & 7) * r2;
-            if (ms == (uint32_t) c) x = r2;
-        }
-    }
+    ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);
+    const uint32_t tbl = d & 0xFFFFFFu;
+    const PosRank r1 = pos_rank(w, p1, tbl), r2 = pos_rank(v, p2, tbl);
+    uint64_t kp = in.kp + (r2.W - r1.W), x = r2.M, y = r1.M;
     if (ix.has_quirk) {
-        const uint32_t wq = (d >> 18) & 7;
-        if (wq || ms == PGI_SRC_QUIRK) {
+        const uint32_t wq = (d >> 24) & 7u;
+        if (wq || (d & PGI_DESC_MAIN_QUIRK)) {
             const uint64_t q2 = quirk_at(ix, p2), q1 = quirk_at(ix, p1);
             kp += (uint64_t) wq * (q2 - q1);
-            if (ms == PGI_SRC_QUIRK) { x = q2; y = q1; }
+            if (d & PGI_DESC_MAIN_QUIRK) { x = q2; y = q1; }
         }
     }
     BiInt out;
     if (y >= x) { out.k = 0; out.kp = 0; out.s = 0; return out; }
-    out.k = y + ix.C[(d >> 24) & 7]; out.kp = kp; out.s = (int64_t) (x - y);
+    out.k = y + ix.C[d >> 29]; out.kp = kp; out.s = (int64_t) (x - y);
     return out;
 }
 

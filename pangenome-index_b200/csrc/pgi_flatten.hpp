@@ -146,12 +146,12 @@ public:
     void finish() { flush_pending(); if (ne_) emit(); }
 private:
     std::vector<uint64_t> &out_; unsigned pcode_ = 8; uint64_t plen_ = 0;
-    uint64_t bstart_ = 0, bcum_[6]; uint16_t ent_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
+    uint64_t bstart_ = 0, bcum_[6]; uint32_t ent_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
     void flush_pending() {
         while (plen_) {
             uint64_t t = plen_ < PGI_MAX_RUN_ENTRY ? plen_ : PGI_MAX_RUN_ENTRY;
             if (!ne_) { bstart_ = pos; std::memcpy(bcum_, cum, sizeof(cum)); }
-            ent_[ne_++] = (uint16_t) (pcode_ | (t << 3));
+            ent_[ne_++] = (uint16_t) ((pcode_ << 2) | (t << 5));        // code4 | length << 5
             cum[pcode_] += t; pos += t; plen_ -= t;
             if (ne_ == PGI_RUNS_PER_BLOCK) emit();
         }
@@ -161,20 +161,15 @@ private:
             throw FormatError("index longer than 2^40 positions is not supported by the device layout");
         if (bcum_[0] >> 32 || bcum_[4] >> 32)
             throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
-        uint64_t r[4] = {0, 0, 0, 0};   // 15 x 16-bit entries = 240 bits, starting at bit 16 of word 4
-        for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) {
-            uint64_t e = i < ne_ ? ent_[i] : 0; unsigned bit = 16 + 16 * i;
-            r[bit >> 6] |= e << (bit & 63);
-        }
         const uint64_t A = bcum_[1], C = bcum_[2], G = bcum_[3], T = bcum_[5], NL = bcum_[0], N = bcum_[4];
-        uint64_t w[PGI_BLOCK_WORDS];
-        w[0] = bstart_ | (A << 40);                       // start(40) | A[0..24)
-        w[1] = (A >> 24) | (C << 16);                     // A[24..40) | C(40) | 8 spare bits
-        w[2] = G | (T << 40);                             // G(40) | T[0..24)
-        w[3] = (T >> 24) | (NL << 16) | (N << 48);        // T[24..40) | NL(32) | N[0..16)
-        w[4] = (N >> 16) | r[0];                          // N[16..32) | runs 0..2
-        w[5] = r[1]; w[6] = r[2]; w[7] = r[3];
-        out_.insert(out_.end(), w, w + PGI_BLOCK_WORDS);
+        uint32_t w[PGI_BLOCK_U32];
+        w[0] = (uint32_t) bstart_; w[1] = (uint32_t) A; w[2] = (uint32_t) C; w[3] = (uint32_t) G; w[4] = (uint32_t) T;
+        w[5] = (uint32_t) NL; w[6] = (uint32_t) N;
+        w[7] = (uint32_t) (bstart_ >> 32) | (uint32_t) (A >> 32) << 8 | (uint32_t) (C >> 32) << 16 | (uint32_t) (G >> 32) << 24;
+        auto ent = [&](unsigned i) -> uint32_t { return i < ne_ ? ent_[i] : 0u; };
+        w[8] = (uint32_t) (T >> 32) | ent(0) << 16;
+        for (unsigned j = 0; j < 7; ++j) w[9 + j] = ent(1 + 2 * j) | ent(2 + 2 * j) << 16;
+        for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) out_.push_back((uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32);
         starts.push_back(bstart_);
         ne_ = 0;
     }
@@ -184,19 +179,21 @@ inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, ui
     const uint64_t nb = starts.size();
     if (nb == 0) throw FormatError("r-index has no runs");
     if (nb >> 32) throw FormatError("too many run blocks for the 32-bit block directory");
-    // about two directory buckets per block: most buckets then hold at most one block boundary
+    // about two directory buckets per block: most buckets then hold at most one block boundary (pgi_layout.h)
     unsigned S = 0;
-    while (S < 31 && (n >> (S + 1)) >= 2 * nb) ++S;
+    while (S < PGI_DIR_MAX_SHIFT && (n >> (S + 1)) >= 2 * nb) ++S;
     const uint64_t nbuckets = (n >> S) + 1;
     im.k.dir_shift = S; im.k.n_blocks = nb;
     im.dir.assign(nbuckets + 1, 0);
     uint64_t idx = 0;
     for (uint64_t b = 0; b <= nbuckets; ++b) {
-        const uint64_t lo = b << S;
+        const uint64_t lo = b << S, hi = lo + (1ULL << S);
         while (idx + 1 < nb && starts[idx + 1] <= lo) ++idx;
-        uint64_t off = 0xFFFFFFFFull;
-        if (idx + 1 < nb && starts[idx + 1] - lo < (1ULL << S)) off = starts[idx + 1] - lo;
-        im.dir[b] = idx | (off << 32);
+        uint64_t t1 = PGI_DIR_NONE1, t2 = PGI_DIR_NONE2, more = 0;
+        if (idx + 1 < nb && starts[idx + 1] < hi) t1 = starts[idx + 1] - lo;
+        if (idx + 2 < nb && starts[idx + 2] < hi) t2 = starts[idx + 2] - lo;
+        if (idx + 3 < nb && starts[idx + 3] < hi) more = 1;
+        im.dir[b] = idx | (t1 << 32) | (t2 << 48) | (more << 63);
     }
 }
 
@@ -231,10 +228,12 @@ inline void build_descriptors(RiImage &im, const bool present[6], bool legacy) {
             w[slot[k.sym_map[comp[kNuc[b]]]]]++;
         const unsigned mi = k.sym_map[a];
         uint32_t d = 0;
-        for (unsigned c = 0; c < 6; ++c) d |= (uint32_t) w[c] << (3 * c);
-        d |= (uint32_t) w[PGI_SRC_QUIRK] << 18;
-        d |= (uint32_t) slot[mi] << 21;
-        d |= (uint32_t) mi << 24;
+        for (unsigned c = 0; c < 6; ++c) d |= (uint32_t) w[c] << (4 * c);    // at most 6 increments in total: fits 3 bits
+        d |= (uint32_t) w[PGI_SRC_QUIRK] << 24;
+        if (slot[mi] < 6) d |= 8u << (4 * slot[mi]);
+        else if (slot[mi] == PGI_SRC_QUIRK) d |= PGI_DESC_MAIN_QUIRK;
+        else d |= PGI_DESC_MAIN_ZERO;
+        d |= (uint32_t) mi << 29;
         desc[a] = d;
     }
     for (int a = 0; a < 256; ++a) { k.desc_b[a] = desc[a]; k.desc_f[a] = desc[comp[a]]; }

@@ -96,13 +96,12 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS) fmd_mem_kernel(const MemArgs 
                 if ((o >> 3) != cwi) { cwi = o >> 3; cw = __ldg(a.reads64 + cwi); }
                 sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
             }
-            if (L.phase == PH_P2) {
-                BiInt t; t.k = L.b.kp; t.kp = L.b.k; t.s = L.b.s;
-                t = extend_desc(a.ix, t, s_desc[256 + sym]);
-                L.b.k = t.kp; L.b.kp = t.k; L.b.s = t.s;
-            } else {
-                L.b = extend_desc(a.ix, L.b, s_desc[sym]);
-            }
+            // forward extension = backward extension of the swapped interval with the complement's descriptor
+            // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
+            const bool fwd = L.phase == PH_P2;
+            BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
+            t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
+            L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
             ++n_ext;
             lane_after_ext(L, a.min_len, a.min_occ, a.ix.n);
         }
@@ -141,8 +140,8 @@ __global__ void rank_kernel(RiDev ix, SlotTable st, uint64_t n, const uint64_t *
     const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint64_t p = pos[i]; if (p > ix.n) p = ix.n;
-    uint64_t t1[6], t2[6];
-    rank_pair(ix, p, p, t1, t2);
+    uint64_t t1[6];
+    rank_all(ix, p, t1);
     const uint64_t q = ix.has_quirk ? quirk_at(ix, p) : 0;
     for (uint32_t j = 0; j < 8; ++j) {
         uint64_t v = 0;

@@ -3,28 +3,44 @@
 #pragma once
 #include <stdint.h>
 
-// One run block = 64 bytes = 8 little-endian u64 words (two 32-byte DRAM sectors, one aligned 64 B burst):
-//   w0 = start(40) | A[0..24)           start = first BWT position covered by the block
-//   w1 = A[24..40) | C(40) | spare(8)   A,C,G,T = symbol counts before the block (40 bits)
-//   w2 = G(40) | T[0..24)
-//   w3 = T[24..40) | NL(32) | N[0..16)  NL = endmarker count, N = 'N' count (32 bits)
-//   w4 = N[16..32) | e0 e1 e2           e_i = 16-bit run entries: code(3) | length(13), length 0 = unused
-//   w5 = e3..e6, w6 = e7..e10, w7 = e11..e14
-// code = index into nuc = {'\n','A','C','G','N','T'} (include/pangenome_index/utils.hpp:11).
-#define PGI_BLOCK_WORDS 8
+// One run block = 64 bytes = 16 little-endian u32 words (two 32-byte DRAM sectors, one aligned 64 B burst):
+//   w0      start, low 32 bits          start = first BWT position covered by the block (40 bits)
+//   w1..w4  A, C, G, T, low 32 bits     symbol counts before the block (40 bits each)
+//   w5, w6  NL, N                       endmarker / 'N' counts before the block (32 bits each)
+//   w7      start_hi | A_hi << 8 | C_hi << 16 | G_hi << 24      (bits 32..39 of the 40-bit fields)
+//   w8      T_hi | spare << 8 | e0 << 16
+//   w9..w15 e1..e14, two per word (odd entry in the low half)
+// Run entry e_i (16 bits) = code4 | length << 5: code4 = 4 * code (5 bits), length 1..2047 (0 = unused entry).
+// code = index into nuc = {'\n','A','C','G','N','T'} (include/pangenome_index/utils.hpp:11). code4 is stored
+// pre-multiplied so that a 32-bit shift by the raw entry (which uses the low 5 bits only) indexes a table of
+// 4-bit fields without extracting the code first. A block covers at most 15 * 2047 < 2^15 positions.
+#define PGI_BLOCK_U32 16
+#define PGI_BLOCK_WORDS 8            /* the same block counted in u64 words (host vectors are u64) */
 #define PGI_RUNS_PER_BLOCK 15
-#define PGI_MAX_RUN_ENTRY 8191ull
+#define PGI_MAX_RUN_ENTRY 2047ull
+
+// Block directory entry (u64), one per bucket of 2^dir_shift positions (dir_shift <= 14):
+//   bits 0..31  index of the block containing the first position of the bucket
+//   bits 32..47 offset inside the bucket of the 1st block boundary (0xFFFF: none)
+//   bits 48..62 offset of the 2nd block boundary (0x7FFF: none)
+//   bit 63      the bucket holds more than two boundaries (binary search over block starts past the 2nd)
+#define PGI_DIR_NONE1 0xFFFFull
+#define PGI_DIR_NONE2 0x7FFFull
+#define PGI_DIR_MAX_SHIFT 14
 
 // Sources of one rank-vector slot R(pos)[i]: true rank of nuc code 0..5,
 // the legacy "column-0 cumulative at the reference block start" quirk, or constant zero.
 #define PGI_SRC_QUIRK 6u
 #define PGI_SRC_ZERO 7u
 
-// Per-byte extension descriptor (desc_b for backward, desc_f = desc_b[complement] for forward):
-//   bits 0..17  w[c], c = 0..5 : how many times (true rank delta of code c) is added to k'
-//   bits 18..20 wq             : how many times the quirk delta is added to k'
-//   bits 21..23 main source    : where R[sym_map[a]] comes from (0..5, PGI_SRC_QUIRK, PGI_SRC_ZERO)
-//   bits 24..26 sym_map[a]     : index into C
+// Per-byte extension descriptor (desc_b for backward, desc_f = desc_b[complement] for forward), 32 bits:
+//   bits 0..23  six 4-bit fields, field c (code c): bits 0..2 = w[c], how many times the true rank delta of code c
+//               is added to k'; bit 3 = "R[sym_map[a]] is the true rank of code c" (at most one field has it)
+//   bits 24..26 wq: how many times the quirk delta is added to k'
+//   bit 27      R[sym_map[a]] comes from the quirk slot;  bit 28: it is constant zero
+//   bits 29..31 sym_map[a]: index into C
+#define PGI_DESC_MAIN_QUIRK (1u << 27)
+#define PGI_DESC_MAIN_ZERO (1u << 28)
 typedef struct {
     uint64_t n, sigma, n_blocks, n_quirk, mem_tail;
     uint32_t dir_shift, has_quirk;
