@@ -128,6 +128,16 @@ class Index:
         out = _result_to_dict(res, L, self.has_tags, text=text); L.pgi_result_free(ctypes.byref(res))
         return out
 
+    def find_mems_raw(self, reads_ptr, off_ptr, n_reads, min_len, min_occ):
+        """pgi_find_mems on raw host pointers (pinned recommended); returns the Result struct whose arrays live in
+        library-owned pinned memory until result_free(res). No numpy copies: this is what bench.py times end to end."""
+        res = Result()
+        _ck(lib().pgi_find_mems(self.h, reads_ptr, off_ptr, n_reads, min_len, min_occ, None, ctypes.byref(res)))
+        return res
+    @staticmethod
+    def result_free(res):
+        lib().pgi_result_free(ctypes.byref(res))
+
 class Batch:
     """Reusable batch context (stream + work buffers) for pipelined or device-resident runs."""
     def __init__(self, index: Index, stream=None):

@@ -319,7 +319,7 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
         CK(cudaMemsetAsync(b->d_nmems.p, 0, (n + 1) * 8, b->stream));
         MemArgs a;
         a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
-        a.n_reads = n; a.min_len = min_len; a.min_occ = min_occ;
+        a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
         a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
         if (n) { fmd_mem_kernel<<<grid, PGI_MEM_THREADS, 0, b->stream>>>(a); ++launches; }
@@ -488,7 +488,7 @@ static void pool_give(pgi_index *ix, pgi_batch *b) { std::lock_guard<std::mutex>
 
 extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
                              uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out) {
-    if (!ix || !read_off || !out) return fail(PGI_EINVAL, "null argument");
+    if (!ix || !read_off || !out || (!reads && n_reads)) return fail(PGI_EINVAL, "null argument");
     pgi_batch *b = pool_take(ix);
     if (!b) return PGI_ECUDA;
     cudaStream_t own = b->stream;

@@ -196,13 +196,15 @@ PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
 // ------------------------------------------------------------------------------------ MEM state machine
 // One lane walks one read through find_all_mems as a loop whose every trip performs exactly one FMD
 // extension (so the 32 lanes of a warp stay convergent although they are in different phases).
-enum { PH_P1 = 1, PH_P2 = 2, PH_P3 = 3, PH_DONE = 0 };
+enum { PH_DONE = 0, PH_P1 = 1, PH_P2 = 2, PH_P3 = 3, PH_EMIT = 4 };
+enum { LANE_DONE = 0, LANE_EXTEND = 1, LANE_EMIT = 2 };
 
+// Read positions are 32-bit: a single read is limited to 2^31 - 16 bytes (longer reads are truncated).
+#define PGI_MAX_READ_LEN 0x7FFFFFF0ull
 struct MemLane {
-    uint64_t len, x, j, e;
+    uint32_t len, x, j, phase;
     BiInt b;                    // interval being extended (bint in P1/P2, back in P3)
     uint64_t k2; int64_t s2;    // bint2.forward / bint2.size
-    uint32_t phase, emit;       // emit = 1: a MEM {x, e, k2, s2} is ready to be written
 };
 
 PGI_HD bool ext_failed(const BiInt &b, uint64_t min_occ) {
@@ -211,62 +213,56 @@ PGI_HD bool ext_failed(const BiInt &b, uint64_t min_occ) {
 
 // `return v` of find_mems_function followed by the `while (x < len)` of find_all_mems and the entry
 // checks of the next call (algorithm.hpp:658-666, 745-748).
-PGI_HD void lane_return(MemLane &L, uint64_t v, uint64_t min_len, uint64_t n) {
+PGI_HD void lane_return(MemLane &L, uint32_t v, uint32_t min_len, uint64_t n) {
     L.x = v;
-    if (L.x >= L.len) { L.phase = PH_DONE; return; }
-    if (L.len - L.x < min_len) { L.x = L.len; L.phase = PH_DONE; return; }
+    if (L.x >= L.len || L.len - L.x < min_len) { L.x = L.len; L.phase = PH_DONE; return; }
     L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n;
     L.j = L.x + min_len - 1; L.phase = PH_P1;
 }
-PGI_HD void lane_begin(MemLane &L, uint64_t len, uint64_t min_len, uint64_t n) {
-    L.len = len; L.emit = 0; L.e = 0; L.k2 = 0; L.s2 = 0;
+PGI_HD void lane_begin(MemLane &L, uint64_t len, uint32_t min_len, uint64_t n) {
+    L.len = (uint32_t) (len < PGI_MAX_READ_LEN ? len : PGI_MAX_READ_LEN); L.k2 = 0; L.s2 = 0;
     L.b.k = L.b.kp = 0; L.b.s = 0; L.j = 0;
     lane_return(L, 0, min_len, n);
 }
 
-// Advance through loop heads until the lane needs an extension (returns true; symbol position = L.j,
-// forward iff phase == PH_P2), has a MEM to emit (L.emit set; call again afterwards) or is done.
-PGI_HD bool lane_settle(MemLane &L, uint64_t min_len, uint64_t n) {
+// Advance through loop heads until the lane needs an extension (LANE_EXTEND; symbol position = L.j, forward iff
+// phase == PH_P2), has the MEM {x, j, k2, s2} to write (LANE_EMIT; call lane_emitted, then settle again) or is done.
+PGI_HD int lane_settle(MemLane &L, uint32_t min_len, uint64_t n) {
     for (;;) {
-        if (L.emit) return false;
         switch (L.phase) {
         case PH_P1:
-            if ((int64_t) L.j >= (int64_t) L.x) return true;
+            if ((int32_t) L.j >= (int32_t) L.x) return LANE_EXTEND;
             L.k2 = L.b.k; L.s2 = L.b.s; L.j = L.x + min_len; L.phase = PH_P2;        // bint2 = bint
             break;
         case PH_P2:
-            if (L.j < L.len) return true;
-            L.e = L.j; L.emit = 1;                                                     // output.push_back
-            L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n; L.phase = PH_P3;               // back = full; j = e
-            return false;
+            if (L.j < L.len) return LANE_EXTEND;
+            L.phase = PH_EMIT;
+            break;
+        case PH_EMIT:
+            return LANE_EMIT;                                                          // output.push_back({x, e = j, bint2})
         case PH_P3:
-            if (L.j > L.x) return true;
+            if (L.j > L.x) return LANE_EXTEND;
             lane_return(L, L.j + 1, min_len, n);
             break;
         default:
-            return false;
+            return LANE_DONE;
         }
     }
 }
+PGI_HD void lane_emitted(MemLane &L, uint64_t n) {
+    L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n; L.phase = PH_P3;                       // back = full interval; j = e
+}
 
 // Bookkeeping after the extension requested by lane_settle produced L.b.
-PGI_HD void lane_after_ext(MemLane &L, uint64_t min_len, uint64_t min_occ, uint64_t n) {
+PGI_HD void lane_after_ext(MemLane &L, uint32_t min_len, uint64_t min_occ, uint64_t n) {
     const bool fail = ext_failed(L.b, min_occ);
-    switch (L.phase) {
-    case PH_P1:
-        if (fail) lane_return(L, L.j + 1, min_len, n);
-        else if (L.j == 0) { L.k2 = L.b.k; L.s2 = L.b.s; L.j = L.x + min_len; L.phase = PH_P2; }
-        else --L.j;
-        break;
-    case PH_P2:
-        if (fail) { L.e = L.j; L.emit = 1; L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n; L.phase = PH_P3; }
+    if (L.phase == PH_P2) {
+        if (fail) L.phase = PH_EMIT;
         else { L.k2 = L.b.k; L.s2 = L.b.s; ++L.j; }
-        break;
-    case PH_P3:
+    } else {                                                                           // PH_P1 / PH_P3: walking left
         if (fail) lane_return(L, L.j + 1, min_len, n);
+        else if (L.phase == PH_P1 && L.j == 0) { L.k2 = L.b.k; L.s2 = L.b.s; L.j = L.x + min_len; L.phase = PH_P2; }
         else --L.j;
-        break;
-    default: break;
     }
 }
 

@@ -16,6 +16,7 @@
 namespace pgi {
 
 #define PGI_MEM_THREADS 256
+#define PGI_MEM_BLOCKS_PER_SM 4     // 64 registers per thread: 32 resident warps per SM hide the two dependent loads per position
 #define PGI_TAG_SMALL 32u          // lists up to this many runs are handled by one thread
 
 struct MemArgs {
@@ -33,20 +34,23 @@ struct MemArgs {
     uint64_t *read_nmems;          // n_reads (+1) MEM counts per read
 };
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // K1. One lane = one read at a time; every trip of the loop performs exactly one FMD extension per
 // active lane, so a warp stays convergent while its 32 reads sit in different phases of
 // find_mems_function. Lanes that finish a read pull the next one from a warp-local queue that is
 // refilled 32 reads at a time from a global cursor (persistent grid: no tail of idle lanes inside a warp).
-__global__ void __launch_bounds__(PGI_MEM_THREADS) fmd_mem_kernel(const MemArgs a) {
+// Read bytes and MEM records are streamed (evict-first) so that they do not push the index out of L2.
+__global__ void __launch_bounds__(PGI_MEM_THREADS, PGI_MEM_BLOCKS_PER_SM) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
     for (int i = threadIdx.x; i < 512; i += blockDim.x) s_desc[i] = a.desc[i];
     __syncthreads();
     const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
     const unsigned lt_mask = (1u << lane) - 1u;
-    MemLane L; L.phase = PH_DONE; L.emit = 0; L.len = 0; L.x = 0; L.j = 0; L.e = 0; L.k2 = 0; L.s2 = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
-    uint64_t rd = ~0ull, base = 0, wq_next = 0, wq_end = 0, n_ext = 0;
-    uint64_t cw = 0, cwi = ~0ull;      // cached 8-byte window of the read
-    uint32_t nm = 0;
+    const uint32_t n_reads = (uint32_t) a.n_reads, min_len = (uint32_t) a.min_len;
+    MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.k2 = 0; L.s2 = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
+    uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
+    uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0;
     bool exhausted = false, have = false;
     for (;;) {
         // ---- hand out reads to idle lanes
@@ -57,57 +61,65 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS) fmd_mem_kernel(const MemArgs 
                 unsigned long long got = 0;
                 if (lane == 0) got = atomicAdd(a.cursor, 32ull);
                 got = __shfl_sync(FULL, got, 0);
-                wq_next = got; wq_end = got + 32 < a.n_reads ? got + 32 : a.n_reads;
-                if (wq_next >= a.n_reads) { wq_next = wq_end = a.n_reads; exhausted = true; }
+                if (got >= n_reads) { wq_next = wq_end = n_reads; exhausted = true; }
+                else { wq_next = (uint32_t) got; wq_end = got + 32 < n_reads ? (uint32_t) got + 32 : n_reads; }
             }
             if (want && !exhausted) {
-                const uint64_t id = wq_next + __popc(m & lt_mask);
+                const uint32_t id = wq_next + __popc(m & lt_mask);
                 if (id < wq_end) {
                     rd = id; have = true; nm = 0;
-                    base = a.read_off[id];
-                    lane_begin(L, a.read_off[id + 1] - base, a.min_len, a.ix.n);
+                    const uint64_t o0 = __ldcs(a.read_off + id), o1 = __ldcs(a.read_off + id + 1);
+                    base = o0;
+                    lane_begin(L, o1 - o0, min_len, a.ix.n);
+                    const char *rp = reinterpret_cast<const char *>(a.reads64) + base;      // pull the read towards L2
+                    for (uint32_t o = 0; o < L.len && o < 512; o += 128) prefetch_l2(rp + o);
                 }
             }
-            const uint64_t adv = wq_next + __popc(m);
+            const uint32_t adv = wq_next + __popc(m);
             wq_next = adv < wq_end ? adv : wq_end;
         }
         // ---- run to the next extension, writing out MEMs on the way
         bool need = false;
         if (have) {
-            for (;;) {
-                need = lane_settle(L, a.min_len, a.ix.n);
-                if (!L.emit) break;
+            int st;
+            while ((st = lane_settle(L, min_len, a.ix.n)) == LANE_EMIT) {
                 const unsigned long long slot = atomicAdd(a.mem_count, 1ull);
                 if (slot < a.mem_cap) {
-                    a.mem_buf[2 * slot] = make_uint4((uint32_t) L.x, (uint32_t) (L.x >> 32), (uint32_t) L.e, (uint32_t) (L.e >> 32));
-                    a.mem_buf[2 * slot + 1] = make_uint4((uint32_t) L.k2, (uint32_t) (L.k2 >> 32), (uint32_t) (uint64_t) L.s2, (uint32_t) ((uint64_t) L.s2 >> 32));
-                    a.mem_key[slot] = (rd << 32) | nm;
+                    __stcs(a.mem_buf + 2 * slot, make_uint4(L.x, 0u, L.j, 0u));
+                    __stcs(a.mem_buf + 2 * slot + 1, make_uint4((uint32_t) L.k2, (uint32_t) (L.k2 >> 32), (uint32_t) (uint64_t) L.s2, (uint32_t) ((uint64_t) L.s2 >> 32)));
+                    __stcs(a.mem_key + slot, ((uint64_t) rd << 32) | nm);
                 }
-                ++nm; L.emit = 0;
+                ++nm;
+                lane_emitted(L, a.ix.n);
             }
+            need = st == LANE_EXTEND;
             if (!need) { a.read_nmems[rd] = nm; have = false; }
         }
         if (__all_sync(FULL, !have && exhausted)) break;
         // ---- one FMD extension
         if (need) {
             uint32_t sym = 0;
+            const bool fwd = L.phase == PH_P2;
             if (L.j < L.len) {
                 const uint64_t o = base + L.j;
-                if ((o >> 3) != cwi) { cwi = o >> 3; cw = __ldg(a.reads64 + cwi); }
+                if ((o >> 3) != cwi) {
+                    cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
+                    if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
+                }
                 sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
             }
             // forward extension = backward extension of the swapped interval with the complement's descriptor
             // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
-            const bool fwd = L.phase == PH_P2;
             BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
             t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
             L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
             ++n_ext;
-            lane_after_ext(L, a.min_len, a.min_occ, a.ix.n);
+            lane_after_ext(L, min_len, a.min_occ, a.ix.n);
         }
     }
-    for (int o = 16; o; o >>= 1) n_ext += __shfl_xor_sync(FULL, n_ext, o);
-    if (lane == 0 && n_ext) atomicAdd(a.ext_count, (unsigned long long) n_ext);
+    unsigned long long tot = n_ext;
+    for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
+    if (lane == 0 && tot) atomicAdd(a.ext_count, tot);
 }
 
 // K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read.

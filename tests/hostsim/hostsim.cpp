@@ -60,20 +60,20 @@ void sim_extend_batch(const sim_index *s, uint64_t n, const uint64_t *in3, const
 }
 // find_all_mems of one read through the lane state machine; returns the MEM count (records of 4 u64 into out, up to cap).
 uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint64_t min_len, uint64_t min_occ, uint64_t *out, uint64_t cap, uint64_t *n_ext) {
-    MemLane L; lane_begin(L, len, min_len, s->rd.n);
+    MemLane L; lane_begin(L, len, (uint32_t) min_len, s->rd.n);
     uint64_t nm = 0, ext = 0;
     for (;;) {
-        bool need = lane_settle(L, min_len, s->rd.n);
-        if (L.emit) {
-            if (nm < cap) { out[4 * nm] = L.x; out[4 * nm + 1] = L.e; out[4 * nm + 2] = L.k2; out[4 * nm + 3] = (uint64_t) L.s2; }
-            ++nm; L.emit = 0; continue;
+        const int st = lane_settle(L, (uint32_t) min_len, s->rd.n);
+        if (st == LANE_EMIT) {
+            if (nm < cap) { out[4 * nm] = L.x; out[4 * nm + 1] = L.j; out[4 * nm + 2] = L.k2; out[4 * nm + 3] = (uint64_t) L.s2; }
+            ++nm; lane_emitted(L, s->rd.n); continue;
         }
-        if (!need) break;
+        if (st != LANE_EXTEND) break;
         const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
         if (L.phase == PH_P2) { std::swap(L.b.k, L.b.kp); L.b = extend_desc(s->rd, L.b, s->ri.k.desc_f[a]); std::swap(L.b.k, L.b.kp); }
         else L.b = extend_desc(s->rd, L.b, s->ri.k.desc_b[a]);
         ++ext;
-        lane_after_ext(L, min_len, min_occ, s->rd.n);
+        lane_after_ext(L, (uint32_t) min_len, min_occ, s->rd.n);
     }
     if (n_ext) *n_ext = ext;
     return nm;

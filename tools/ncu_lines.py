@@ -18,6 +18,6 @@ for r in rows:
         out.append((cur, int(r[0]), r[1].strip()[:100], s, i, t))
 ts = sum(o[3] for o in out); ti = sum(o[4] for o in out); tt = sum(o[5] for o in out)
 print("total: samples %d  warp-inst %d  thread-inst %d  avg threads/inst %.2f" % (ts, ti, tt, tt / max(1, ti)))
-out.sort(key=lambda o: -o[4])
+out.sort(key=lambda o: -o[3 if (len(sys.argv) > 3 and sys.argv[3] == "samples") else 4])
 for o in out[:top]:
     print("%-20s %4d  smp %5.1f%%  inst %5.1f%%  thr %5.1f  %s" % (o[0], o[1], 100 * o[3] / max(1, ts), 100 * o[4] / max(1, ti), o[5] / max(1, o[4]), o[2]))
