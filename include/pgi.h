@@ -83,7 +83,8 @@ int pgi_device_count(void);   /* number of CUDA devices (0 when none / no driver
 /* Replaces FastLocate::load_encoded (src/r-index.cpp:406-459; falls back to the legacy layout of
  * FastLocate::load :378-404 when flag bit 0 is clear) + TagArray::load_compressed_tags_compact /
  * load_compressed_tags, and flattens both into the device layout on GPU `device`.
- * tag_bytes may be NULL (MEM finding only). The input buffers are not retained. */
+ * tag_bytes may be NULL (MEM finding only); ri_bytes may be NULL when tag_bytes is given (a tags-only index, the
+ * TagArray facade: only pgi_tag_query_batch works on it). The input buffers are not retained. */
 int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
                      int tag_layout, int device, pgi_index **out);
 /* Replica of an index on another GPU (device-to-device copy over NVLink; no host round trip). */
@@ -135,6 +136,11 @@ int pgi_batch_stage_ms(pgi_batch *, double ms[8]);
 /* Text of src/find_mems.cpp:115-139 (+ tag lines of src/tag_arrays.cpp:885-889) for a host result;
  * sequence numbers start at first_seq. Host-side formatting (no GPU work). Returns a malloc'd buffer
  * (free with pgi_free), length in *len. with_tags = 0 omits the two tag lines per MEM. */
+/* Pinned (page-locked) host memory for read / offset staging buffers: copies from it run at full PCIe rate and
+ * asynchronously. Returns NULL on failure. Free with pgi_host_free. */
+void *pgi_host_alloc(size_t bytes);
+void pgi_host_free(void *);
+
 char *pgi_format_text(const pgi_result *, uint64_t first_seq, int with_tags, uint64_t *len);
 void pgi_free(void *);
 

@@ -10,7 +10,7 @@ _lib = None
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
-           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_random_access_gbs"]
+           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -57,6 +57,7 @@ def lib():
         L.pgi_batch_stage_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_double * 8)]
         L.pgi_format_text.argtypes = [ctypes.POINTER(Result), u64, i32, ctypes.POINTER(u64)]
         L.pgi_free.argtypes = [vp]
+        L.pgi_host_alloc.restype = vp; L.pgi_host_alloc.argtypes = [ctypes.c_size_t]; L.pgi_host_free.argtypes = [vp]
         L.pgi_random_access_gbs.argtypes = [i32, u64, ctypes.c_uint32, u64, i32, ctypes.POINTER(ctypes.c_double)]
         _lib = L
     return _lib
@@ -90,7 +91,7 @@ class Index:
             self.h = _handle
         else:
             h = ctypes.c_void_p()
-            _ck(L.pgi_index_create(ri, len(ri), tags, len(tags) if tags else 0, tag_layout, device, ctypes.byref(h)))
+            _ck(L.pgi_index_create(ri, len(ri) if ri else 0, tags, len(tags) if tags else 0, tag_layout, device, ctypes.byref(h)))
             self.h = h
         info = IndexInfo(); _ck(L.pgi_index_info(self.h, ctypes.byref(info)))
         self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:15]}

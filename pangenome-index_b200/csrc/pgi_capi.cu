@@ -69,7 +69,7 @@ template <typename T> T *upload(const std::vector<T> &v, std::vector<void *> &ow
 
 struct pgi_index {
     int device = 0;
-    RiDev ri; TagDev tg; bool has_tags = false;
+    RiDev ri; TagDev tg; bool has_tags = false, has_ri = true;
     RiConsts consts; SparseRankConsts ivk;
     uint32_t *d_desc = nullptr;
     std::vector<void *> owned;
@@ -110,15 +110,16 @@ static void fill_info(pgi_index *ix, const RiImage &ri, const TagImage *tg, uint
 
 extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
                                 int tag_layout, int device, pgi_index **out) {
-    if (!ri_bytes || !out) return fail(PGI_EINVAL, "null argument");
+    if ((!ri_bytes && !tag_bytes) || !out) return fail(PGI_EINVAL, "null argument");
     if (int rc = check_device(device)) return rc;
     pgi_index *ix = nullptr;
     try {
         RiImage ri; TagImage tg; bool has_tags = tag_bytes && tag_len;
-        flatten_ri(ri_bytes, ri_len, ri);
+        std::memset(&ri.k, 0, sizeof(ri.k));
+        if (ri_bytes) flatten_ri(ri_bytes, ri_len, ri);
         if (has_tags) flatten_tags(tag_bytes, tag_len, tag_layout, tg);
         DeviceGuard g(device);
-        ix = new pgi_index(); ix->device = device; ix->consts = ri.k;
+        ix = new pgi_index(); ix->device = device; ix->consts = ri.k; ix->has_ri = ri_bytes != nullptr;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         uint64_t bytes = 0;
         RiDev &d = ix->ri;
@@ -174,7 +175,7 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         DeviceGuard g(device);
         ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
-        ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags;
+        ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags; ix->has_ri = src->has_ri;
         ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
         ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
         const int sd = src->device;
@@ -416,6 +417,7 @@ extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) {
     if (!b) return fail(PGI_EINVAL, "null argument");
     if (!b->read_off) return fail(PGI_EINVAL, "no reads staged: call pgi_batch_upload or pgi_batch_set_device_reads first");
     if (b->n_reads >> 32) return fail(PGI_EINVAL, "more than 2^32 reads in one batch");
+    if (!b->ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
     try {
         DeviceGuard g(b->ix->device);
         int launches = 0, reruns = 0;
@@ -535,6 +537,7 @@ extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *st
 
 extern "C" int pgi_extend_batch(pgi_index *ix, uint64_t n, const pgi_bi_interval *in, const uint8_t *sym, const uint8_t *dir, pgi_bi_interval *out) {
     if (!ix || ((!in || !sym || !dir || !out) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
     if (!n) return PGI_OK;
     try {
         DeviceGuard g(ix->device);
@@ -552,6 +555,7 @@ extern "C" int pgi_extend_batch(pgi_index *ix, uint64_t n, const pgi_bi_interval
 
 extern "C" int pgi_rank_batch(pgi_index *ix, uint64_t n, const uint64_t *pos, uint64_t *out8) {
     if (!ix || ((!pos || !out8) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
     if (!n) return PGI_OK;
     try {
         DeviceGuard g(ix->device);
@@ -602,6 +606,13 @@ extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int wi
     return buf;
 }
 extern "C" void pgi_free(void *p) { std::free(p); }
+
+extern "C" void *pgi_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); fail(PGI_ENOMEM, "cudaHostAlloc failed"); return nullptr; }
+    return p;
+}
+extern "C" void pgi_host_free(void *p) { if (p) cudaFreeHost(p); }
 
 extern "C" int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t bytes_per_access, uint64_t n_access, int chain, double *gbs) {
     if (!gbs || chain < 1 || (bytes_per_access != 32 && bytes_per_access != 64 && bytes_per_access != 128)) return fail(PGI_EINVAL, "bad argument");

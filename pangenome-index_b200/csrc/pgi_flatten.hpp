@@ -374,6 +374,7 @@ inline void flatten_tags(const void *bytes, size_t len, int layout, TagImage &im
     im.starts_regular = layout == 0;
     starts.for_each_one([&](uint64_t j, uint64_t p) { im.starts.push_back(p); if (p != 10 * j) im.starts_regular = false; });
     SdVectorView iv; iv.parse(r);
+    if (r.remaining()) throw FormatError("trailing bytes after the tag arrays (wrong tag layout?)");
     build_sparse_rank(iv, im.intervals);
 }
 

@@ -1,0 +1,63 @@
+"""The find_mems command line (host/find_mems.cpp: batched multi-GPU driver; host/find_mems_serial.cpp: the reference's
+per-read loop written against the facade header). stdout must equal the oracle's rendering of src/find_mems.cpp:115-139,
+byte for byte, minus the two trailing timing lines (whose values are run dependent in the reference too)."""
+import os, subprocess, sys
+import numpy as np, pytest
+import orc, datasets
+from conftest import ROOT
+
+HOST = os.path.join(ROOT, "pangenome-index_b200", "host")
+CLI = os.path.join(HOST, "find_mems"); SERIAL = os.path.join(HOST, "find_mems_serial")
+
+def strip_timing(out: bytes) -> bytes:
+    i = out.rfind(b"\nTotal time for finding all MEMs:")
+    assert i >= 0 and out.count(b"Total time for") == 2
+    return out[:i]
+
+def test_cli_fails_loudly_without_gpu(tmp_path):
+    from conftest import load_package
+    if load_package().capi.lib().pgi_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    p = subprocess.run([CLI, os.path.join(datasets.GOLD, "xy.ri"), os.path.join(datasets.GOLD, "xy_bidirectional_compressed.tags"),
+                        os.path.join(datasets.GOLD, "reads.txt"), "5", "1"], capture_output=True)
+    assert p.returncode != 0 and b"no CUDA device" in p.stderr and p.stdout == b""
+    p = subprocess.run([CLI], capture_output=True)
+    assert p.returncode != 0 and b"usage" in p.stderr
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["xy_bytecode", "synth_compact"])
+def test_cli_stdout_equals_oracle(tmp_path, case):
+    if case == "xy_bytecode":
+        ri, tg, layout, text = datasets.gold("xy.ri"), datasets.gold("xy_bidirectional_compressed.tags"), 1, datasets.gold("contigs_xy")
+    else:
+        s = datasets.synth_index(); ri, tg, layout, text = s["ri"], s["tags0"], 0, s["text"]
+    rs = datasets.ragged_reads(text, seed=9, n=300)
+    rs = [r for r in rs if b"\n" not in r and b"\0" not in r]          # one read per text line
+    reads, off = datasets.sample_reads(text, 500, 150, 0.02, seed=3)
+    rs += [reads[int(off[i]):int(off[i + 1])].tobytes() for i in range(500)]
+    (tmp_path / "x.ri").write_bytes(ri); (tmp_path / "x.tags").write_bytes(tg)
+    body = b"\n".join(rs) + b"\n"
+    body = b"\n\n" + body.replace(b"\n", b"\n\n", 5)                   # empty lines are skipped and not numbered
+    (tmp_path / "reads.txt").write_bytes(body)
+    nonempty = [r for r in rs if r]
+    buf, o = orc.pack_reads(nonempty)
+    for ml, mo in [(20, 1), (5, 2)]:
+        want = orc.Index(ri, tg, layout).find_mems(buf, o, ml, mo)["text"]
+        for extra in (["--batch", "97"], ["--batch", "100000"], ["--tags-layout", "bytecode" if layout else "compact"]):
+            p = subprocess.run([CLI, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "reads.txt"), str(ml), str(mo)] + extra, capture_output=True)
+            assert p.returncode == 0, p.stderr.decode()
+            assert strip_timing(p.stdout) == want, extra
+    small = b"\n".join(nonempty[:60]) + b"\n"
+    (tmp_path / "small.txt").write_bytes(small)
+    sb, so = orc.pack_reads(nonempty[:60])
+    want = orc.Index(ri, tg, layout).find_mems(sb, so, 20, 1)["text"]
+    p = subprocess.run([SERIAL, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "small.txt"), "20", "1", "bytecode" if layout else "compact"], capture_output=True)
+    assert p.returncode == 0, p.stderr.decode()
+    assert p.stdout == want                                            # the facade loop prints no timing lines
+
+@pytest.mark.gpu
+def test_cli_rejects_wrong_tag_layout(tmp_path):
+    s = datasets.synth_index()
+    (tmp_path / "x.ri").write_bytes(s["ri"]); (tmp_path / "x.tags").write_bytes(s["tags0"]); (tmp_path / "r.txt").write_bytes(b"ACGT\n")
+    p = subprocess.run([CLI, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "r.txt"), "2", "1", "--tags-layout", "bytecode"], capture_output=True)
+    assert p.returncode != 0 and b"cannot load the index" in p.stderr
