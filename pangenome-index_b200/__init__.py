@@ -7,4 +7,4 @@ implementation of the query path: `capi.lib()` raises if the CUDA library is mis
 The directory name contains a hyphen, so import it through `__graft_entry__.load_package()` (or
 tests/conftest.py), which registers it as the module `pangenome_index_b200`.
 """
-from . import capi, prep  # noqa: F401
+from . import capi, prep, sharding  # noqa: F401

@@ -160,3 +160,20 @@ def test_large_ragged_batch_and_concurrent_callers(capi):
     R = o.find_mems(reads[: int(off[kk])], off[: kk + 1], 20, 1, text=False)
     assert np.array_equal(G["mems"][: R["n_mems"]], R["mems"]) and np.array_equal(G["tags"][: R["n_tags"]], R["tags"])
     assert np.array_equal(G["mem_off"][: kk + 1], R["mem_off"])
+
+def test_sharded_equals_unsharded(capi):
+    """The multi-GPU host logic (sharding.py) on the CUDA path: shards computed separately (as N ranks would, each on its
+    replica) and merged equal the unsharded batch; a clone of the index gives the same answers."""
+    sharding = load_package().sharding
+    c = get_case("synth_enc_compact"); g = capi.Index(c["ri"], c["tags"], 0); g2 = g.clone_to(0)
+    rs = datasets.ragged_reads(c["text"], seed=13, n=600); reads, off = orc.pack_reads(rs)
+    whole = g.find_mems(reads, off, 12, 1, text=False)
+    for world in (2, 8):
+        parts = []
+        for r in range(world):
+            rr, oo, lo, hi = sharding.shard_reads(reads, off, world, r)
+            parts.append((g if r % 2 == 0 else g2).find_mems(rr, oo, 12, 1, text=False))
+        m = sharding.merge_results(parts)
+        for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(m[k], whole[k]), (world, k)
+        assert m["extensions"] == whole["extensions"]
+    assert sharding.find_mems_sharded(lambda *a: g.find_mems(*a, text=False), reads, off, 12, 1)["n_mems"] == whole["n_mems"]
