@@ -27,8 +27,8 @@ def parse_args():
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--workload", default="synth", choices=["synth", "xy"])
-    p.add_argument("--ref-len", type=int, default=int(os.environ.get("PGI_BENCH_REF_LEN", 16_000_000)))
-    p.add_argument("--n-hap", type=int, default=int(os.environ.get("PGI_BENCH_N_HAP", 16)))
+    p.add_argument("--ref-len", type=int, default=int(os.environ.get("PGI_BENCH_REF_LEN", 50_000_000)))
+    p.add_argument("--n-hap", type=int, default=int(os.environ.get("PGI_BENCH_N_HAP", 20)))
     p.add_argument("--reads-per-step", type=int, default=int(os.environ.get("PGI_BENCH_READS", 2_000_000)))
     p.add_argument("--read-len", type=int, default=150)
     p.add_argument("--sub", type=float, default=0.01)
