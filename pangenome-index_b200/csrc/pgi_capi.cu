@@ -3,6 +3,7 @@
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_segmented_sort.cuh>
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
@@ -76,6 +77,7 @@ struct pgi_index {
     // sizes of the uploaded arrays, for clone
     uint64_t n_block_words = 0, n_dir = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
+    std::mutex compute_mu;                                  // see pgi_find_mems
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
     int sm_count = 0;
 };
@@ -495,9 +497,23 @@ extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *r
     if (!b) return PGI_ECUDA;
     cudaStream_t own = b->stream;
     if (cuda_stream) b->stream = (cudaStream_t) cuda_stream;
+    static const bool trace = std::getenv("PGI_TRACE") != nullptr;            // per-call timeline on stderr (host clock, ms)
+    static const auto t_origin = std::chrono::steady_clock::now();
+    auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_origin).count(); };
+    const double t0 = trace ? now_ms() : 0;
     int rc = pgi_batch_upload(b, reads, read_off, n_reads);
-    if (rc == PGI_OK) rc = pgi_batch_run(b, min_len, min_occ);
+    double t1 = 0;
+    // Concurrent callers pipeline instead of interleaving: the host->device copy is waited for OUTSIDE the compute token,
+    // the kernels of one call at a time own the GPU (a persistent grid fills every SM anyway; two of them interleaved only
+    // delay each other's short follow-up kernels), and the device->host copy again runs outside the token. In steady state
+    // call k+1 uploads and call k-1 downloads while call k computes.
+    if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
+    if (trace) t1 = now_ms();
+    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = pgi_batch_run(b, min_len, min_occ); }
+    const double t2 = trace ? now_ms() : 0;
     if (rc == PGI_OK) rc = pgi_batch_fetch(b, out);
+    if (trace) std::fprintf(stderr, "[pgi] ctx %p reads %llu: enter %.2f uploaded %.2f run_done %.2f (mem kernel %.2f, stages %.2f ms) fetched %.2f\n", (void *) b,
+                            (unsigned long long) n_reads, t0, t1, t2, b->stage_ms[0], b->stage_ms[5], now_ms());
     b->stream = own;
     if (rc != PGI_OK) { pool_give(ix, b); return rc; }
     out->owner = b;                                      // the result lives in the batch's pinned buffers
