@@ -75,7 +75,7 @@ struct pgi_index {
     uint32_t *d_desc = nullptr;
     std::vector<void *> owned;
     // sizes of the uploaded arrays, for clone
-    uint64_t n_block_words = 0, n_dir = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
+    uint64_t n_block_words = 0, n_dir = 0, n_sb = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
     std::mutex compute_mu;                                  // see pgi_find_mems
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
@@ -127,8 +127,9 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
         RiDev &d = ix->ri;
         d.blocks = upload(ri.blocks, ix->owned, bytes); ix->n_block_words = ri.blocks.size();
         d.dir = upload(ri.dir, ix->owned, bytes); ix->n_dir = ri.dir.size();
+        d.sb = upload(ri.sb, ix->owned, bytes); ix->n_sb = ri.sb.size();
         d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
-        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk;
+        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk; d.sb_shift = ri.k.sb_shift; d.pad_ = 0;
         for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
         std::vector<uint32_t> desc(512);
         for (int i = 0; i < 256; ++i) { desc[i] = ri.k.desc_b[i]; desc[256 + i] = ri.k.desc_f[i]; }
@@ -178,11 +179,12 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags; ix->has_ri = src->has_ri;
-        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
+        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_sb = src->n_sb; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
         ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
         const int sd = src->device;
         ix->ri.blocks = clone_arr(src->ri.blocks, sd, src->n_block_words, device, ix->owned);
         ix->ri.dir = clone_arr(src->ri.dir, sd, src->n_dir, device, ix->owned);
+        ix->ri.sb = clone_arr(src->ri.sb, sd, src->n_sb, device, ix->owned);
         ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, 512, device, ix->owned);
@@ -637,21 +639,31 @@ extern "C" int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t by
         DeviceGuard g(device);
         DevBuf buf, sink; buf.need(buf_bytes); sink.need(8);
         CK(cudaMemset(buf.p, 1, buf_bytes)); CK(cudaMemset(sink.p, 0, 8));
-        const uint64_t n_slots = buf_bytes / bytes_per_access, n_threads = std::max<uint64_t>(1, n_access / (uint64_t) chain);
+        const uint64_t n_slots = buf_bytes / bytes_per_access;
+        if (n_slots < 1 || (chain == 1 && n_slots >> 32)) return fail(PGI_EINVAL, "buffer too small or too large for the microbenchmark");
+        uint64_t n_threads = std::max<uint64_t>(1, n_access / (uint64_t) chain);
+        const uint32_t per_thread = 64;                   // independent form: 64 loads per thread
+        if (chain == 1) n_threads = std::max<uint64_t>(256, (n_access / per_thread + 255) / 256 * 256);
         cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
         float best = 1e30f;
         for (int rep = 0; rep < 4; ++rep) {              // rep 0 is the warm-up
             CK(cudaEventRecord(e0));
             const unsigned grid = grid_for(n_threads, 256);
-            if (bytes_per_access == 32) gather_kernel<32><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
-            else if (bytes_per_access == 64) gather_kernel<64><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
-            else gather_kernel<128><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sink.as<unsigned long long>());
+            unsigned long long *sk = sink.as<unsigned long long>();
+            if (chain == 1) {
+                if (bytes_per_access == 32) gather_indep_kernel<32><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, per_thread, sk);
+                else if (bytes_per_access == 64) gather_indep_kernel<64><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, per_thread, sk);
+                else gather_indep_kernel<128><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, per_thread, sk);
+            } else if (bytes_per_access == 32) gather_kernel<32><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sk);
+            else if (bytes_per_access == 64) gather_kernel<64><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sk);
+            else gather_kernel<128><<<grid, 256>>>(buf.as<uint4>(), n_slots, n_threads, chain, sk);
             CK(cudaGetLastError());
             CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
             float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
             if (rep > 0 && ms < best) best = ms;
         }
         cudaEventDestroy(e0); cudaEventDestroy(e1);
+        if (chain == 1) { *gbs = (double) n_threads * per_thread * bytes_per_access / (best * 1e-3) / 1e9; buf.release(); sink.release(); return PGI_OK; }
         *gbs = (double) n_threads * chain * bytes_per_access / (best * 1e-3) / 1e9;
         buf.release(); sink.release();
         return PGI_OK;

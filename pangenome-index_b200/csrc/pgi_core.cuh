@@ -25,11 +25,12 @@ namespace pgi {
 // Device view of the flattened r-index.
 struct RiDev {
     const uint64_t *blocks;     // 8 words per run block, 64-byte aligned
-    const uint64_t *dir;        // block directory
+    const uint32_t *dir;        // block directory, per bucket of 2^dir_shift positions (pgi_layout.h)
+    const uint32_t *sb;         // block index at every superbucket start
     const uint64_t *q_start;    // quirk tables (n_quirk entries) or nullptr
     const uint64_t *q_val;
     uint64_t n, n_blocks, n_quirk;
-    uint32_t dir_shift, has_quirk;
+    uint32_t dir_shift, has_quirk, sb_shift, pad_;
     uint64_t C[8];
 };
 
@@ -73,27 +74,34 @@ PGI_HD uint64_t block_start_at(const uint64_t *blocks, uint64_t idx) {      // s
 }
 
 // ------------------------------------------------------------------------------------ block locate
-// Index of the run block containing BWT position pos (pos <= n): last block whose start <= pos.
-// Replaces blocks_start_pos.predecessor(pos) (src/r-index.cpp:594,621): ONE directory word holds the block
-// index at the bucket start and the offsets of the first two block boundaries inside the bucket
-// (pgi_layout.h); only buckets with more than two boundaries fall into the search below.
-PGI_HD uint64_t locate_from_dir(const RiDev &ix, uint64_t pos, uint64_t e) {
-    const uint32_t rel = (uint32_t) pos & ((1u << ix.dir_shift) - 1u);
-    const uint32_t t1 = (uint32_t) (e >> 32) & 0xFFFFu, t2 = (uint32_t) (e >> 48) & 0x7FFFu;
-    uint64_t idx = (e & 0xFFFFFFFFull) + (rel >= t1) + (rel >= t2);
-    if ((e >> 63) && rel >= t2) {                     // rare: more boundaries; search block starts in (idx, hi]
-        const uint64_t hi = ld64(ix.dir + (pos >> ix.dir_shift) + 1) & 0xFFFFFFFFull;
-        uint64_t lo = idx, up = hi;                    // invariant: start(lo) <= pos
-        while (lo < up) {
-            const uint64_t mid = (lo + up + 1) >> 1;
-            if (block_start_at(ix.blocks, mid) <= pos) lo = mid; else up = mid - 1;
-        }
-        idx = lo;
-    }
-    return idx;
+// Replaces blocks_start_pos.predecessor(pos) (src/r-index.cpp:594,621; SDSL: 2-3 dependent cache lines).
+PGI_HD uint32_t ld32(const uint32_t *p) {
+#if defined(__CUDA_ARCH__)
+    return __ldg(p);
+#else
+    return *p;
+#endif
 }
+// Block guess from the two directory words of pos: exact unless the bucket holds more than two block boundaries and
+// pos lies behind the third, in which case the guess is SHORT (start(guess) <= pos always holds).
+PGI_HD uint64_t locate_guess(const RiDev &ix, uint64_t pos, uint32_t e, uint32_t base) {
+    const uint32_t rel = (uint32_t) pos & ((1u << ix.dir_shift) - 1u);
+    const uint32_t t1 = (e >> 16) & 0xFFu, t2 = e >> 24;                 // 0 = no boundary: (0 - 1) < rel is false
+    return (uint64_t) base + (e & 0xFFFFu) + ((t1 - 1u) < rel) + ((t2 - 1u) < rel);
+}
+// Index of the run block containing pos: last block whose start <= pos. Slow path and non-hot callers.
 PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
-    return locate_from_dir(ix, pos, ld64(ix.dir + (pos >> ix.dir_shift)));
+    const uint64_t b = pos >> ix.dir_shift;
+    uint64_t lo = locate_guess(ix, pos, ld32(ix.dir + b), ld32(ix.sb + (pos >> ix.sb_shift)));
+    uint64_t s1 = ((b + 1) << ix.dir_shift) >> ix.sb_shift; const uint64_t smax = ix.n >> ix.sb_shift;
+    if (s1 > smax) s1 = smax;                                             // the flattener clamps the same way
+    uint64_t up = (uint64_t) ld32(ix.sb + s1) + (ld32(ix.dir + b + 1) & 0xFFFFu);   // block at the next bucket start
+    if (up >= ix.n_blocks) up = ix.n_blocks - 1;
+    while (lo < up) {                                                     // invariant: start(lo) <= pos
+        const uint64_t mid = (lo + up + 1) >> 1;
+        if (block_start_at(ix.blocks, mid) <= pos) lo = mid; else up = mid - 1;
+    }
+    return lo;
 }
 
 // ------------------------------------------------------------------------------------ in-block rank
@@ -103,7 +111,7 @@ PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
 // Per run entry: one table shift indexed by the raw entry (code4 sits in its low 5 bits), min, subtract and one
 // 32x32->64 multiply-add whose multiplier carries the weight in bits 0..2 and the main flag in bit 21
 // (sum of weight * count < 7 * 15 * 2047 < 2^21, so the two partial sums never meet).
-struct PosRank { uint64_t W, M; };
+struct PosRank { uint64_t W, M; uint32_t left; };   // left: positions of pos beyond the end of the block (0 when the block is the right one)
 
 #define PGI_SCAN_ENTRY(ENT, LEN)                                                     \
     {                                                                                  \
@@ -135,9 +143,21 @@ PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) {
     PosRank o;
     o.W = Wl + ((uint64_t) Wh << 32) + (acc & 0x1FFFFFull);
     o.M = Ml + ((uint64_t) Mh << 32) + (acc >> 21);
+    o.left = r;
     return o;
 }
 
+// Exact but slow: search the block, then rank (the fallback of extend_desc; batched rank API).
+#if defined(__CUDA_ARCH__)
+__device__ __noinline__
+#else
+inline
+#endif
+PosRank rank_slow(const RiDev &ix, uint64_t pos, uint32_t tbl) {
+    uint32_t w[16];
+    ld_block(ix.blocks + locate_block(ix, pos) * PGI_BLOCK_WORDS, w);
+    return pos_rank(w, pos, tbl);
+}
 // True ranks of the six nuc codes at pos (batched rank API and tests; not on the MEM path).
 PGI_HD void rank_all(const RiDev &ix, uint64_t pos, uint64_t tr[6]) {
     uint32_t w[16];
@@ -171,13 +191,28 @@ PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
     uint64_t p2 = in.k + (uint64_t) in.s, p1 = in.k;
     if (p2 > ix.n) p2 = ix.n;
     if (p1 > ix.n) p1 = ix.n;
-    const uint64_t e1 = ld64(ix.dir + (p1 >> ix.dir_shift)), e2 = ld64(ix.dir + (p2 >> ix.dir_shift));
-    const uint64_t b1 = locate_from_dir(ix, p1, e1), b2 = locate_from_dir(ix, p2, e2);
+    // Every lane touches its own cache lines, so the L1 data pipe pays one wavefront per lane per load: a load whose
+    // address repeats the previous one (k and k+s in the same bucket / block: the common case once the interval is short)
+    // is predicated off and its value copied instead.
+    const uint64_t g1 = p1 >> ix.dir_shift, g2 = p2 >> ix.dir_shift, h1 = p1 >> ix.sb_shift, h2 = p2 >> ix.sb_shift;
+    const uint32_t e1 = ld32(ix.dir + g1), s1 = ld32(ix.sb + h1);
+    uint32_t e2 = e1, s2 = s1;
+    if (g2 != g1) e2 = ld32(ix.dir + g2);
+    if (h2 != h1) s2 = ld32(ix.sb + h2);
+    const uint64_t b1 = locate_guess(ix, p1, e1, s1), b2 = locate_guess(ix, p2, e2, s2);
     uint32_t w[16], v[16];
     ld_block(ix.blocks + b1 * PGI_BLOCK_WORDS, w);
-    ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);
+    if (b2 != b1) ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);
+    else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = w[i];
+    }
     const uint32_t tbl = d & 0xFFFFFFu;
-    const PosRank r1 = pos_rank(w, p1, tbl), r2 = pos_rank(v, p2, tbl);
+    PosRank r1 = pos_rank(w, p1, tbl), r2 = pos_rank(v, p2, tbl);
+    if (r1.left | r2.left) {                          // rare: a guess landed short (bucket with more than two boundaries)
+        if (r1.left) r1 = rank_slow(ix, p1, tbl);
+        if (r2.left) r2 = rank_slow(ix, p2, tbl);
+    }
     uint64_t kp = in.kp + (r2.W - r1.W), x = r2.M, y = r1.M;
     if (ix.has_quirk) {
         const uint32_t wq = (d >> 24) & 7u;

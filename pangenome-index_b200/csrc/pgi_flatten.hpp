@@ -111,7 +111,7 @@ inline uint64_t bytecode_next(const uint8_t *&p, const uint8_t *end) {
 struct RiImage {
     RiConsts k;                          // scalars + tables copied to the device as one struct
     std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte run block
-    std::vector<uint64_t> dir;           // block directory, (n >> dir_shift) + 2 entries
+    std::vector<uint32_t> dir, sb;       // two-level block directory (pgi_layout.h)
     std::vector<uint64_t> q_start, q_val;// quirk slot tables (legacy files with an absent nuc symbol)
     uint64_t n_file_runs = 0, n_ref_blocks = 0; bool encoded = false;
 };
@@ -179,21 +179,39 @@ inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, ui
     const uint64_t nb = starts.size();
     if (nb == 0) throw FormatError("r-index has no runs");
     if (nb >> 32) throw FormatError("too many run blocks for the 32-bit block directory");
-    // about two directory buckets per block: most buckets then hold at most one block boundary (pgi_layout.h)
+    // a bucket about as long as the average block (pgi_layout.h)
     unsigned S = 0;
-    while (S < PGI_DIR_MAX_SHIFT && (n >> (S + 1)) >= 2 * nb) ++S;
+    while (S < PGI_DIR_MAX_SHIFT && (n >> (S + 1)) >= nb) ++S;
     const uint64_t nbuckets = (n >> S) + 1;
     im.k.dir_shift = S; im.k.n_blocks = nb;
-    im.dir.assign(nbuckets + 1, 0);
+    // largest superbucket whose block count fits the 16-bit delta: blocks inside [q << sb, (q + 1) << sb) for every q
+    unsigned SB = PGI_SB_MAX_SHIFT;
+    for (; SB > PGI_SB_MIN_SHIFT; --SB) {
+        bool ok = true; uint64_t i = 0;
+        for (uint64_t q = 0; ok && (q << SB) <= n; ++q) {
+            const uint64_t end = (q + 1) << SB; uint64_t j = i;
+            while (j + 1 < nb && starts[j + 1] < end) ++j;              // j = last block starting inside the superbucket
+            if (j - i >= 0xFFFF) ok = false;
+            i = j;
+        }
+        if (ok) break;
+    }
+    im.k.sb_shift = SB;
+    const uint64_t nsb = (n >> SB) + 1, sb_mask = (1ULL << SB) - 1;
+    im.dir.assign(nbuckets + 1, 0); im.sb.assign(nsb, 0);
     uint64_t idx = 0;
     for (uint64_t b = 0; b <= nbuckets; ++b) {
         const uint64_t lo = b << S, hi = lo + (1ULL << S);
         while (idx + 1 < nb && starts[idx + 1] <= lo) ++idx;
-        uint64_t t1 = PGI_DIR_NONE1, t2 = PGI_DIR_NONE2, more = 0;
+        const uint64_t s = lo >> SB;
+        if (s < nsb && (lo & sb_mask) == 0) im.sb[s] = (uint32_t) idx;     // superbucket starts are bucket starts (S <= 8 < 19)
+        const uint64_t base = im.sb[s < nsb ? s : nsb - 1];
+        uint64_t t1 = 0, t2 = 0;
         if (idx + 1 < nb && starts[idx + 1] < hi) t1 = starts[idx + 1] - lo;
         if (idx + 2 < nb && starts[idx + 2] < hi) t2 = starts[idx + 2] - lo;
-        if (idx + 3 < nb && starts[idx + 3] < hi) more = 1;
-        im.dir[b] = idx | (t1 << 32) | (t2 << 48) | (more << 63);
+        const uint64_t delta = idx - base;
+        if (delta >> 16) throw FormatError("internal: block directory delta overflow");
+        im.dir[b] = (uint32_t) (delta | (t1 << 16) | (t2 << 24));
     }
 }
 

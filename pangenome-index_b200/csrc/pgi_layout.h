@@ -19,14 +19,19 @@
 #define PGI_RUNS_PER_BLOCK 15
 #define PGI_MAX_RUN_ENTRY 2047ull
 
-// Block directory entry (u64), one per bucket of 2^dir_shift positions (dir_shift <= 14):
-//   bits 0..31  index of the block containing the first position of the bucket
-//   bits 32..47 offset inside the bucket of the 1st block boundary (0xFFFF: none)
-//   bits 48..62 offset of the 2nd block boundary (0x7FFF: none)
-//   bit 63      the bucket holds more than two boundaries (binary search over block starts past the 2nd)
-#define PGI_DIR_NONE1 0xFFFFull
-#define PGI_DIR_NONE2 0x7FFFull
-#define PGI_DIR_MAX_SHIFT 14
+// Block directory: two levels, both read with independent loads (no dependent chain between them).
+//   sb[pos >> sb_shift]      (u32) index of the block containing the first position of the superbucket (2^19..2^30
+//                            positions: the table is a handful of cache lines, so 32 lanes' loads share wavefronts)
+//   dir[pos >> dir_shift]    (u32) bits 0..15  block index at the bucket start, relative to its superbucket's sb entry
+//                                  bits 16..23 offset inside the bucket of the 1st block boundary (0: none)
+//                                  bits 24..31 offset of the 2nd block boundary (0: none)
+// dir_shift <= 8, chosen so that a bucket is about one block long: 4 bytes per ~block instead of the 8 bytes per half
+// block of a one-level table, so the directory of a 2 G-position index is 31 MB and lives in L2 while the blocks stream
+// from HBM. A bucket with more than two boundaries makes the guess land short; the scan notices (positions left over
+// after the last run) and the rare slow path searches the block starts.
+#define PGI_SB_MIN_SHIFT 19           /* 2^19 / 15 < 2^16: the 16-bit delta always fits */
+#define PGI_SB_MAX_SHIFT 30           /* the flattener takes the largest shift whose deltas still fit: the sb table is then a few cache lines */
+#define PGI_DIR_MAX_SHIFT 8
 
 // Sources of one rank-vector slot R(pos)[i]: true rank of nuc code 0..5,
 // the legacy "column-0 cumulative at the reference block start" quirk, or constant zero.
@@ -43,7 +48,7 @@
 #define PGI_DESC_MAIN_ZERO (1u << 28)
 typedef struct {
     uint64_t n, sigma, n_blocks, n_quirk, mem_tail;
-    uint32_t dir_shift, has_quirk;
+    uint32_t dir_shift, has_quirk, sb_shift, pad_;
     uint32_t slot[8];          // source of R(pos)[i], i < sigma (0..5 true rank of that nuc code, PGI_SRC_QUIRK, PGI_SRC_ZERO)
     uint64_t C[8];
     uint8_t sym_map[256];

@@ -126,4 +126,28 @@ __global__ void gather_kernel(const uint4 *buf, uint64_t n_slots, uint64_t n_thr
     if (acc == 0x1234567ull) atomicAdd(sink, 1ull);
 }
 
+// M1, independent form (chain == 1): every thread issues `per_thread` random loads whose addresses do not depend on
+// loaded data (4 in flight per thread), over n_slots slots of BYTES bytes. This is the throughput ceiling of random
+// sector access for a given footprint; the chained form above adds the dependent-latency component.
+template <int BYTES>
+__global__ void gather_indep_kernel(const uint4 *buf, uint32_t n_slots, uint32_t per_thread, unsigned long long *sink) {
+    const uint64_t tid = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    uint64_t x = tid * (uint64_t) per_thread * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull; uint32_t acc = 0;   // a distinct counter per access
+    for (uint32_t i = 0; i < per_thread; i += 4) {
+        uint32_t slot[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            x += 0x9E3779B97F4A7C15ull; uint64_t z = x; z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull; z ^= z >> 27; z *= 0x94D049BB133111EBull; z ^= z >> 31;
+            slot[u] = (uint32_t) (((z >> 32) * (uint64_t) n_slots) >> 32);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint4 *p = buf + (uint64_t) slot[u] * (BYTES / 16);
+#pragma unroll
+            for (int q = 0; q < BYTES / 16; ++q) { const uint4 v = __ldg(p + q); acc += v.x ^ v.y ^ v.z ^ v.w; }
+        }
+    }
+    if (acc == 0x12345u) atomicAdd(sink, 1ull);
+}
+
 } // namespace pgi
