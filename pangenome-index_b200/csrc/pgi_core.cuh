@@ -182,6 +182,23 @@ PGI_HD uint64_t quirk_at(const RiDev &ix, uint64_t pos) {
 // ------------------------------------------------------------------------------------ FMD extension
 struct BiInt { uint64_t k, kp; int64_t s; };      // FastLocate::bi_interval {forward, reverse, size}
 
+// Second half of an extension: from the two weighted ranks to the new interval (src/r-index.cpp:733-755).
+PGI_HD BiInt extend_finish(const RiDev &ix, const BiInt &in, uint32_t d, const PosRank &r1, const PosRank &r2, uint64_t p1, uint64_t p2) {
+    uint64_t kp = in.kp + (r2.W - r1.W), x = r2.M, y = r1.M;
+    if (ix.has_quirk) {
+        const uint32_t wq = (d >> 24) & 7u;
+        if (wq || (d & PGI_DESC_MAIN_QUIRK)) {
+            const uint64_t q2 = quirk_at(ix, p2), q1 = quirk_at(ix, p1);
+            kp += (uint64_t) wq * (q2 - q1);
+            if (d & PGI_DESC_MAIN_QUIRK) { x = q2; y = q1; }
+        }
+    }
+    BiInt out;
+    if (y >= x) { out.k = 0; out.kp = 0; out.s = 0; return out; }
+    out.k = y + ix.C[d >> 29]; out.kp = kp; out.s = (int64_t) (x - y);
+    return out;
+}
+
 // One backward extension with the per-byte descriptor d (desc_b[a]); forward extension = the same on
 // the swapped interval with desc_f[a] (src/r-index.cpp:758-764). All arithmetic mod 2^64, like the
 // reference's size_t. Positions beyond n read as n (defined UB).
@@ -213,19 +230,7 @@ PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
         if (r1.left) r1 = rank_slow(ix, p1, tbl);
         if (r2.left) r2 = rank_slow(ix, p2, tbl);
     }
-    uint64_t kp = in.kp + (r2.W - r1.W), x = r2.M, y = r1.M;
-    if (ix.has_quirk) {
-        const uint32_t wq = (d >> 24) & 7u;
-        if (wq || (d & PGI_DESC_MAIN_QUIRK)) {
-            const uint64_t q2 = quirk_at(ix, p2), q1 = quirk_at(ix, p1);
-            kp += (uint64_t) wq * (q2 - q1);
-            if (d & PGI_DESC_MAIN_QUIRK) { x = q2; y = q1; }
-        }
-    }
-    BiInt out;
-    if (y >= x) { out.k = 0; out.kp = 0; out.s = 0; return out; }
-    out.k = y + ix.C[d >> 29]; out.kp = kp; out.s = (int64_t) (x - y);
-    return out;
+    return extend_finish(ix, in, d, r1, r2, p1, p2);
 }
 
 // ------------------------------------------------------------------------------------ MEM state machine

@@ -178,7 +178,7 @@ private:
 inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, uint64_t n) {
     const uint64_t nb = starts.size();
     if (nb == 0) throw FormatError("r-index has no runs");
-    if (nb >> 32) throw FormatError("too many run blocks for the 32-bit block directory");
+    if (nb >> 30) throw FormatError("too many run blocks (>= 2^30) for the 32-bit block directory / 16-byte-unit fetch indices");
     // a bucket about as long as the average block (pgi_layout.h)
     unsigned S = 0;
     while (S < PGI_DIR_MAX_SHIFT && (n >> (S + 1)) >= nb) ++S;

@@ -41,13 +41,47 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 // find_mems_function. Lanes that finish a read pull the next one from a warp-local queue that is
 // refilled 32 reads at a time from a global cursor (persistent grid: no tail of idle lanes inside a warp).
 // Read bytes and MEM records are streamed (evict-first) so that they do not push the index out of L2.
-__global__ void __launch_bounds__(PGI_MEM_THREADS, PGI_MEM_BLOCKS_PER_SM) fmd_mem_kernel(const MemArgs a) {
+//
+// Block fetch (MODE): every lane needs its own one or two 64-byte run blocks per extension.
+//   MODE 0  each lane loads its own blocks (4 x LDG.128 per block). 32 lanes = 32 distinct cache lines per load
+//           instruction: the L1 data pipe pays one wavefront per line, 4 x 32 per block and warp (ncu r01e: L1 wavefront
+//           throughput 79 % of peak, the limiter).
+//   MODE 1  cooperative: a quad of lanes fetches one block (4 x 16 B contiguous), so one instruction of the warp covers
+//           8 blocks = at most 8 lines; 4 rounds serve the 32 lanes. The 16-byte parts are copied global -> shared with
+//           cp.async (no registers, L1 bypassed) into a per-warp staging area, XOR-swizzled so that both the quad-wise
+//           writes and the per-lane 4 x LDS.128 reads are free of bank conflicts. 4x fewer L1 wavefronts per block.
+//   MODE 2  the same with LDG.128 + STS.128 instead of cp.async.
+#define PGI_NOBLK 0xFFFFFFFFu
+__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *g) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
+}
+// The same, skipped (predicated off inside the asm: no branch, no address re-derivation) when blk == PGI_NOBLK.
+__device__ __forceinline__ void cp_async16_if(uint32_t saddr, const void *g, uint32_t blk) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\t@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}" ::"r"(saddr), "l"(g), "r"(blk) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// Words of the lane's own staged block (slot = lane) of position `which`.
+__device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned which, unsigned lane, uint32_t w[16]) {
+    const uint4 *sl = warp_stage + which * 128u + lane * 4u;
+    const unsigned z = (lane >> 1) & 3u;
+    const uint4 a = sl[0u ^ z], b = sl[1u ^ z], c = sl[2u ^ z], d = sl[3u ^ z];
+    w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
+    w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
+}
+
+template <int MODE, int BPS>
+__global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
+    __shared__ uint4 s_stage[MODE ? (PGI_MEM_THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
     for (int i = threadIdx.x; i < 512; i += blockDim.x) s_desc[i] = a.desc[i];
     __syncthreads();
     const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
     const unsigned lt_mask = (1u << lane) - 1u;
     const uint32_t n_reads = (uint32_t) a.n_reads, min_len = (uint32_t) a.min_len;
+    uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 256u : 0u);
+    // loop-invariant half of the cooperative fetch (MODE 1): where this lane's part of round 0 / position 0 lands in the staging area
+    const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + ((lane >> 2) * 4u + ((lane & 3u) ^ ((lane >> 3) & 3u))) * 16u;
     MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.k2 = 0; L.s2 = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0;
@@ -97,24 +131,99 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, PGI_MEM_BLOCKS_PER_SM) fmd_me
         }
         if (__all_sync(FULL, !have && exhausted)) break;
         // ---- one FMD extension
-        if (need) {
-            uint32_t sym = 0;
-            const bool fwd = L.phase == PH_P2;
-            if (L.j < L.len) {
-                const uint64_t o = base + L.j;
-                if ((o >> 3) != cwi) {
-                    cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
-                    if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
-                }
-                sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
+        // forward extension = backward extension of the swapped interval with the complement's descriptor
+        // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
+        uint32_t sym = 0;
+        const bool fwd = L.phase == PH_P2;
+        if (need && L.j < L.len) {
+            const uint64_t o = base + L.j;
+            if ((o >> 3) != cwi) {
+                cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
+                if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
             }
-            // forward extension = backward extension of the swapped interval with the complement's descriptor
-            // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
-            BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
-            t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
-            L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
-            ++n_ext;
-            lane_after_ext(L, min_len, a.min_occ, a.ix.n);
+            sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
+        }
+        if (MODE == 0) {
+            if (need) {
+                BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
+                t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
+                L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
+                ++n_ext;
+                lane_after_ext(L, min_len, a.min_occ, a.ix.n);
+            }
+        } else {
+            // (1) every lane with work resolves its two block indices from the directory
+            uint32_t b1 = PGI_NOBLK, b2 = PGI_NOBLK;       // b2 stays PGI_NOBLK when k and k+s share a block
+            if (need) {
+                uint64_t p1 = fwd ? L.b.kp : L.b.k, p2 = p1 + (uint64_t) L.b.s;
+                if (p2 > a.ix.n) p2 = a.ix.n;
+                if (p1 > a.ix.n) p1 = a.ix.n;
+                const uint64_t g1 = p1 >> a.ix.dir_shift, g2 = p2 >> a.ix.dir_shift, h1 = p1 >> a.ix.sb_shift, h2 = p2 >> a.ix.sb_shift;
+                const uint32_t e1 = ld32(a.ix.dir + g1), s1 = ld32(a.ix.sb + h1);
+                uint32_t e2 = e1, s2 = s1;
+                if (g2 != g1) e2 = ld32(a.ix.dir + g2);
+                if (h2 != h1) s2 = ld32(a.ix.sb + h2);
+                b1 = (uint32_t) locate_guess(a.ix, p1, e1, s1);
+                const uint32_t bb = (uint32_t) locate_guess(a.ix, p2, e2, s2);
+                if (bb != b1) b2 = bb;
+            }
+            // (2) the warp fetches the blocks together: quad q of round r serves slot 8 r + q
+            const unsigned part = lane & 3u;
+            const char *const blk_bytes = reinterpret_cast<const char *>(a.ix.blocks);
+            if (MODE == 1) {
+                // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r
+#pragma unroll
+                // block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
+                // lane adds its part number and needs one multiply-add for the address
+                const uint32_t q1 = b1 == PGI_NOBLK ? PGI_NOBLK : b1 << 2, q2 = b2 == PGI_NOBLK ? PGI_NOBLK : b2 << 2;
+#pragma unroll
+                for (unsigned r = 0; r < 4; ++r) {
+                    const unsigned src = 8u * r + (lane >> 2);
+                    const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
+                    cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
+                    cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
+                }
+                cp_async_wait_all();
+            } else {
+                uint4 v1[4], v2[4];
+#pragma unroll
+                for (unsigned r = 0; r < 4; ++r) {
+                    const unsigned src = 8u * r + (lane >> 2);
+                    const uint32_t x1 = __shfl_sync(FULL, b1, src), x2 = __shfl_sync(FULL, b2, src);
+                    v1[r] = make_uint4(0, 0, 0, 0); v2[r] = v1[r];
+                    if (x1 != PGI_NOBLK) v1[r] = __ldg(reinterpret_cast<const uint4 *>(blk_bytes + (uint64_t) x1 * 64u + part * 16u));
+                    if (x2 != PGI_NOBLK) v2[r] = __ldg(reinterpret_cast<const uint4 *>(blk_bytes + (uint64_t) x2 * 64u + part * 16u));
+                }
+#pragma unroll
+                for (unsigned r = 0; r < 4; ++r) {
+                    const unsigned src = 8u * r + (lane >> 2);
+                    const unsigned so = src * 4u + (part ^ ((src >> 1) & 3u));
+                    wstage[so] = v1[r]; wstage[128u + so] = v2[r];
+                }
+            }
+            __syncwarp();
+            // (3) every lane with work scans its own blocks out of shared memory
+            if (need) {
+                BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
+                uint64_t p1 = t.k, p2 = p1 + (uint64_t) t.s;
+                if (p2 > a.ix.n) p2 = a.ix.n;
+                if (p1 > a.ix.n) p1 = a.ix.n;
+                const uint32_t d = s_desc[(fwd ? 256u : 0u) + sym], tbl = d & 0xFFFFFFu;
+                uint32_t w[16];
+                ld_staged(wstage, 0u, lane, w);
+                PosRank r1 = pos_rank(w, p1, tbl);
+                ld_staged(wstage, b2 != PGI_NOBLK ? 1u : 0u, lane, w);
+                PosRank r2 = pos_rank(w, p2, tbl);
+                if (r1.left | r2.left) {                      // rare: a guess landed short (bucket with more than two boundaries)
+                    if (r1.left) r1 = rank_slow(a.ix, p1, tbl);
+                    if (r2.left) r2 = rank_slow(a.ix, p2, tbl);
+                }
+                t = extend_finish(a.ix, t, d, r1, r2, p1, p2);
+                L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
+                ++n_ext;
+                lane_after_ext(L, min_len, a.min_occ, a.ix.n);
+            }
+            __syncwarp();                                     // the staging area is rewritten by the next trip
         }
     }
     unsigned long long tot = n_ext;
