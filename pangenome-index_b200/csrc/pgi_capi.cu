@@ -307,17 +307,17 @@ uint64_t read_back(pgi_batch *b, const void *dptr) {
     return *b->h_ctr.as<uint64_t>();
 }
 
-// K1 instantiations: block-fetch mode x resident CTAs per SM (pgi_kernels.cuh). PGI_K1="<mode><ctas>" picks one for
-// tuning runs (e.g. PGI_K1=04 is the lane-private fetch at 4 CTAs per SM); the default is the measured best.
-struct K1Variant { const char *name; void (*fn)(const MemArgs); };
+// K1 instantiations: block-fetch mode x CTA shape (pgi_kernels.cuh). PGI_K1=<name> picks one for tuning runs
+// (e.g. PGI_K1=04 is the lane-private fetch, 256 threads x 4 CTAs per SM); the default is the measured best.
+struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads; };
 const K1Variant &k1_variant() {
-    static const K1Variant table[] = {
-        {"04", fmd_mem_kernel<0, 4>}, {"14", fmd_mem_kernel<1, 4>}, {"15", fmd_mem_kernel<1, 5>}, {"16", fmd_mem_kernel<1, 6>},
-        {"24", fmd_mem_kernel<2, 4>}, {"25", fmd_mem_kernel<2, 5>},
+    static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
+        {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
+        {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process
     if (e) for (const K1Variant &v : table) if (!std::strcmp(v.name, e)) return v;
-    return table[1];
+    return table[0];
 }
 
 // MEM finding: K1 (+ re-run with a larger append buffer if it overflowed), scan, scatter.
@@ -327,9 +327,9 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     uint64_t cap = std::max<uint64_t>(1024, (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
     int blocks_per_sm = 0;
     const K1Variant &k1 = k1_variant();
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k1.fn, PGI_MEM_THREADS, 0));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k1.fn, (int) k1.threads, 0));
     if (blocks_per_sm < 1) blocks_per_sm = 1;
-    const uint64_t want_blocks = (n + PGI_MEM_THREADS - 1) / PGI_MEM_THREADS;
+    const uint64_t want_blocks = (n + k1.threads - 1) / k1.threads;
     const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, want_blocks));
     unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
     uint64_t total = 0;
@@ -342,7 +342,7 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
         a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
         a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
-        if (n) { k1.fn<<<grid, PGI_MEM_THREADS, 0, b->stream>>>(a); ++launches; }
+        if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(b->h_ctr.p, ctr, 32, cudaMemcpyDeviceToHost, b->stream));
         CK(cudaStreamSynchronize(b->stream));

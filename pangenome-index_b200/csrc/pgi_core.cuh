@@ -243,8 +243,8 @@ enum { LANE_DONE = 0, LANE_EXTEND = 1, LANE_EMIT = 2 };
 #define PGI_MAX_READ_LEN 0x7FFFFFF0ull
 struct MemLane {
     uint32_t len, x, j, phase;
-    BiInt b;                    // interval being extended (bint in P1/P2, back in P3)
-    uint64_t k2; int64_t s2;    // bint2.forward / bint2.size
+    BiInt b;                    // interval being extended (bint in P1/P2, back in P3). A failed forward extension is not
+                                // committed, so in P2 / EMIT b is also bint2, the last good interval (algorithm.hpp:684-699)
 };
 
 PGI_HD bool ext_failed(const BiInt &b, uint64_t min_occ) {
@@ -260,19 +260,19 @@ PGI_HD void lane_return(MemLane &L, uint32_t v, uint32_t min_len, uint64_t n) {
     L.j = L.x + min_len - 1; L.phase = PH_P1;
 }
 PGI_HD void lane_begin(MemLane &L, uint64_t len, uint32_t min_len, uint64_t n) {
-    L.len = (uint32_t) (len < PGI_MAX_READ_LEN ? len : PGI_MAX_READ_LEN); L.k2 = 0; L.s2 = 0;
+    L.len = (uint32_t) (len < PGI_MAX_READ_LEN ? len : PGI_MAX_READ_LEN);
     L.b.k = L.b.kp = 0; L.b.s = 0; L.j = 0;
     lane_return(L, 0, min_len, n);
 }
 
 // Advance through loop heads until the lane needs an extension (LANE_EXTEND; symbol position = L.j, forward iff
-// phase == PH_P2), has the MEM {x, j, k2, s2} to write (LANE_EMIT; call lane_emitted, then settle again) or is done.
+// phase == PH_P2), has the MEM {x, j, b.k, b.s} to write (LANE_EMIT; call lane_emitted, then settle again) or is done.
 PGI_HD int lane_settle(MemLane &L, uint32_t min_len, uint64_t n) {
     for (;;) {
         switch (L.phase) {
         case PH_P1:
             if ((int32_t) L.j >= (int32_t) L.x) return LANE_EXTEND;
-            L.k2 = L.b.k; L.s2 = L.b.s; L.j = L.x + min_len; L.phase = PH_P2;        // bint2 = bint
+            L.j = L.x + min_len; L.phase = PH_P2;                                    // bint2 = bint
             break;
         case PH_P2:
             if (L.j < L.len) return LANE_EXTEND;
@@ -293,15 +293,16 @@ PGI_HD void lane_emitted(MemLane &L, uint64_t n) {
     L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n; L.phase = PH_P3;                       // back = full interval; j = e
 }
 
-// Bookkeeping after the extension requested by lane_settle produced L.b.
-PGI_HD void lane_after_ext(MemLane &L, uint32_t min_len, uint64_t min_occ, uint64_t n) {
-    const bool fail = ext_failed(L.b, min_occ);
+// Bookkeeping after the extension requested by lane_settle produced t (in the orientation of L.b).
+PGI_HD void lane_after_ext(MemLane &L, const BiInt &t, uint32_t min_len, uint64_t min_occ, uint64_t n) {
+    const bool fail = ext_failed(t, min_occ);
     if (L.phase == PH_P2) {
-        if (fail) L.phase = PH_EMIT;
-        else { L.k2 = L.b.k; L.s2 = L.b.s; ++L.j; }
+        if (fail) L.phase = PH_EMIT;                                                   // b stays bint2
+        else { L.b = t; ++L.j; }
     } else {                                                                           // PH_P1 / PH_P3: walking left
+        L.b = t;
         if (fail) lane_return(L, L.j + 1, min_len, n);
-        else if (L.phase == PH_P1 && L.j == 0) { L.k2 = L.b.k; L.s2 = L.b.s; L.j = L.x + min_len; L.phase = PH_P2; }
+        else if (L.phase == PH_P1 && L.j == 0) { L.j = L.x + min_len; L.phase = PH_P2; }
         else --L.j;
     }
 }

@@ -15,8 +15,6 @@
 
 namespace pgi {
 
-#define PGI_MEM_THREADS 256
-#define PGI_MEM_BLOCKS_PER_SM 4     // 64 registers per thread: 32 resident warps per SM hide the two dependent loads per position
 #define PGI_TAG_SMALL 32u          // lists up to this many runs are handled by one thread
 
 struct MemArgs {
@@ -50,12 +48,9 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 //           8 blocks = at most 8 lines; 4 rounds serve the 32 lanes. The 16-byte parts are copied global -> shared with
 //           cp.async (no registers, L1 bypassed) into a per-warp staging area, XOR-swizzled so that both the quad-wise
 //           writes and the per-lane 4 x LDS.128 reads are free of bank conflicts. 4x fewer L1 wavefronts per block.
-//   MODE 2  the same with LDG.128 + STS.128 instead of cp.async.
+//           (LDG.128 + STS.128 instead of cp.async was measured as well: 17.8 ms against 16.6 ms per 2 M reads.)
 #define PGI_NOBLK 0xFFFFFFFFu
-__device__ __forceinline__ void cp_async16(uint32_t saddr, const void *g) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(saddr), "l"(g) : "memory");
-}
-// The same, skipped (predicated off inside the asm: no branch, no address re-derivation) when blk == PGI_NOBLK.
+// 16-byte global -> shared copy, skipped (predicated off inside the asm: no branch, no address re-derivation) when blk == PGI_NOBLK.
 __device__ __forceinline__ void cp_async16_if(uint32_t saddr, const void *g, uint32_t blk) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\t@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}" ::"r"(saddr), "l"(g), "r"(blk) : "memory");
 }
@@ -70,10 +65,10 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
 }
 
-template <int MODE, int BPS>
-__global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
+template <int MODE, int THREADS, int BPS>
+__global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
-    __shared__ uint4 s_stage[MODE ? (PGI_MEM_THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
+    __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
     for (int i = threadIdx.x; i < 512; i += blockDim.x) s_desc[i] = a.desc[i];
     __syncthreads();
     const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
@@ -82,7 +77,7 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const Mem
     uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 256u : 0u);
     // loop-invariant half of the cooperative fetch (MODE 1): where this lane's part of round 0 / position 0 lands in the staging area
     const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + ((lane >> 2) * 4u + ((lane & 3u) ^ ((lane >> 3) & 3u))) * 16u;
-    MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.k2 = 0; L.s2 = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
+    MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0;
     bool exhausted = false, have = false;
@@ -120,7 +115,7 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const Mem
                 const unsigned long long slot = atomicAdd(a.mem_count, 1ull);
                 if (slot < a.mem_cap) {
                     __stcs(a.mem_buf + 2 * slot, make_uint4(L.x, 0u, L.j, 0u));
-                    __stcs(a.mem_buf + 2 * slot + 1, make_uint4((uint32_t) L.k2, (uint32_t) (L.k2 >> 32), (uint32_t) (uint64_t) L.s2, (uint32_t) ((uint64_t) L.s2 >> 32)));
+                    __stcs(a.mem_buf + 2 * slot + 1, make_uint4((uint32_t) L.b.k, (uint32_t) (L.b.k >> 32), (uint32_t) (uint64_t) L.b.s, (uint32_t) ((uint64_t) L.b.s >> 32)));
                     __stcs(a.mem_key + slot, ((uint64_t) rd << 32) | nm);
                 }
                 ++nm;
@@ -147,9 +142,9 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const Mem
             if (need) {
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
                 t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
-                L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
+                BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
                 ++n_ext;
-                lane_after_ext(L, min_len, a.min_occ, a.ix.n);
+                lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
             }
         } else {
             // (1) every lane with work resolves its two block indices from the directory
@@ -170,37 +165,18 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const Mem
             // (2) the warp fetches the blocks together: quad q of round r serves slot 8 r + q
             const unsigned part = lane & 3u;
             const char *const blk_bytes = reinterpret_cast<const char *>(a.ix.blocks);
-            if (MODE == 1) {
-                // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r
+            // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r.
+            // Block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
+            // lane adds its part number and needs one multiply-add for the address.
+            const uint32_t q1 = b1 == PGI_NOBLK ? PGI_NOBLK : b1 << 2, q2 = b2 == PGI_NOBLK ? PGI_NOBLK : b2 << 2;
 #pragma unroll
-                // block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
-                // lane adds its part number and needs one multiply-add for the address
-                const uint32_t q1 = b1 == PGI_NOBLK ? PGI_NOBLK : b1 << 2, q2 = b2 == PGI_NOBLK ? PGI_NOBLK : b2 << 2;
-#pragma unroll
-                for (unsigned r = 0; r < 4; ++r) {
-                    const unsigned src = 8u * r + (lane >> 2);
-                    const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
-                    cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
-                    cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
-                }
-                cp_async_wait_all();
-            } else {
-                uint4 v1[4], v2[4];
-#pragma unroll
-                for (unsigned r = 0; r < 4; ++r) {
-                    const unsigned src = 8u * r + (lane >> 2);
-                    const uint32_t x1 = __shfl_sync(FULL, b1, src), x2 = __shfl_sync(FULL, b2, src);
-                    v1[r] = make_uint4(0, 0, 0, 0); v2[r] = v1[r];
-                    if (x1 != PGI_NOBLK) v1[r] = __ldg(reinterpret_cast<const uint4 *>(blk_bytes + (uint64_t) x1 * 64u + part * 16u));
-                    if (x2 != PGI_NOBLK) v2[r] = __ldg(reinterpret_cast<const uint4 *>(blk_bytes + (uint64_t) x2 * 64u + part * 16u));
-                }
-#pragma unroll
-                for (unsigned r = 0; r < 4; ++r) {
-                    const unsigned src = 8u * r + (lane >> 2);
-                    const unsigned so = src * 4u + (part ^ ((src >> 1) & 3u));
-                    wstage[so] = v1[r]; wstage[128u + so] = v2[r];
-                }
+            for (unsigned r = 0; r < 4; ++r) {
+                const unsigned src = 8u * r + (lane >> 2);
+                const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
+                cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
+                cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
             }
+            cp_async_wait_all();
             __syncwarp();
             // (3) every lane with work scans its own blocks out of shared memory
             if (need) {
@@ -219,9 +195,9 @@ __global__ void __launch_bounds__(PGI_MEM_THREADS, BPS) fmd_mem_kernel(const Mem
                     if (r2.left) r2 = rank_slow(a.ix, p2, tbl);
                 }
                 t = extend_finish(a.ix, t, d, r1, r2, p1, p2);
-                L.b.k = fwd ? t.kp : t.k; L.b.kp = fwd ? t.k : t.kp; L.b.s = t.s;
+                BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
                 ++n_ext;
-                lane_after_ext(L, min_len, a.min_occ, a.ix.n);
+                lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
             }
             __syncwarp();                                     // the staging area is rewritten by the next trip
         }

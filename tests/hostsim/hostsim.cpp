@@ -65,15 +65,16 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
     for (;;) {
         const int st = lane_settle(L, (uint32_t) min_len, s->rd.n);
         if (st == LANE_EMIT) {
-            if (nm < cap) { out[4 * nm] = L.x; out[4 * nm + 1] = L.j; out[4 * nm + 2] = L.k2; out[4 * nm + 3] = (uint64_t) L.s2; }
+            if (nm < cap) { out[4 * nm] = L.x; out[4 * nm + 1] = L.j; out[4 * nm + 2] = L.b.k; out[4 * nm + 3] = (uint64_t) L.b.s; }
             ++nm; lane_emitted(L, s->rd.n); continue;
         }
         if (st != LANE_EXTEND) break;
         const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
-        if (L.phase == PH_P2) { std::swap(L.b.k, L.b.kp); L.b = extend_desc(s->rd, L.b, s->ri.k.desc_f[a]); std::swap(L.b.k, L.b.kp); }
-        else L.b = extend_desc(s->rd, L.b, s->ri.k.desc_b[a]);
+        BiInt t = L.b;
+        if (L.phase == PH_P2) { std::swap(t.k, t.kp); t = extend_desc(s->rd, t, s->ri.k.desc_f[a]); std::swap(t.k, t.kp); }
+        else t = extend_desc(s->rd, t, s->ri.k.desc_b[a]);
         ++ext;
-        lane_after_ext(L, (uint32_t) min_len, min_occ, s->rd.n);
+        lane_after_ext(L, t, (uint32_t) min_len, min_occ, s->rd.n);
     }
     if (n_ext) *n_ext = ext;
     return nm;
