@@ -132,8 +132,12 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
         d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
         d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk; d.sb_shift = ri.k.sb_shift; d.pad_ = 0;
         for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
-        std::vector<uint32_t> desc(512);
+        std::vector<uint32_t> desc(PGI_DESC_WORDS);      // 512 descriptors, then their 512 x 4 scan tables (pos_rank)
         for (int i = 0; i < 256; ++i) { desc[i] = ri.k.desc_b[i]; desc[256 + i] = ri.k.desc_f[i]; }
+        for (int i = 0; i < 512; ++i) {
+            const ScanTab t = scan_tab(desc[i] & 0xFFFFFFu);
+            desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
+        }
         ix->d_desc = upload(desc, ix->owned, bytes);
         std::memset(&ix->tg, 0, sizeof(ix->tg));
         if (has_tags) {
@@ -188,7 +192,7 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix->ri.sb = clone_arr(src->ri.sb, sd, src->n_sb, device, ix->owned);
         ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
-        ix->d_desc = clone_arr(src->d_desc, sd, 512, device, ix->owned);
+        ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);
         if (src->has_tags) {
             ix->tg.iv.dir = clone_arr(src->tg.iv.dir, sd, src->n_iv_dir, device, ix->owned);
             ix->tg.iv.low = clone_arr(src->tg.iv.low, sd, src->n_iv_low, device, ix->owned);

@@ -105,33 +105,76 @@ PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
 }
 
 // ------------------------------------------------------------------------------------ in-block rank
-// Weighted rank of one position. tbl = six 4-bit fields (bits 0..2 weight w[c], bit 3 "main symbol"), the low
-// 24 bits of an extension descriptor. Returns, for the first `rel` positions of the block plus the block's
-// cumulative header:   W = sum_c w[c] * rank_c(pos)      M = rank_main(pos)   (0 when no field has bit 3).
-// Per run entry: one table shift indexed by the raw entry (code4 sits in its low 5 bits), min, subtract and one
-// 32x32->64 multiply-add whose multiplier carries the weight in bits 0..2 and the main flag in bit 21
-// (sum of weight * count < 7 * 15 * 2047 < 2^21, so the two partial sums never meet).
+// ---- SIMD primitives of the scan (one SASS instruction each on sm_100a; plain C++ for the test-only host build)
+PGI_HD uint32_t min_u16x2(uint32_t a, uint32_t b) {                 // VIMNMX.U16x2
+#if defined(__CUDA_ARCH__)
+    return __vminu2(a, b);
+#else
+    const uint32_t al = a & 0xFFFFu, bl = b & 0xFFFFu, ah = a >> 16, bh = b >> 16;
+    return (al < bl ? al : bl) | (ah < bh ? ah : bh) << 16;
+#endif
+}
+PGI_HD uint32_t byte_perm(uint32_t lo, uint32_t hi, uint32_t sel) { // PRMT: result byte i = byte (sel nibble i) of {hi:lo}
+#if defined(__CUDA_ARCH__)
+    return __byte_perm(lo, hi, sel);
+#else
+    const uint64_t t = (uint64_t) hi << 32 | lo; uint32_t r = 0;
+    for (int i = 0; i < 4; ++i) r |= (uint32_t) ((t >> (8 * ((sel >> (4 * i)) & 7u))) & 0xFFu) << (8 * i);
+    return r;
+#endif
+}
+PGI_HD uint32_t dp2a_lo(uint32_t a, uint32_t b, uint32_t c) {       // IDP.2A.LO.U16.U8: a.lo16 * b.byte0 + a.hi16 * b.byte1 + c
+#if defined(__CUDA_ARCH__)
+    return __dp2a_lo(a, b, c);
+#else
+    return (a & 0xFFFFu) * (b & 0xFFu) + (a >> 16) * ((b >> 8) & 0xFFu) + c;
+#endif
+}
+PGI_HD uint32_t dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {       // IDP.2A.HI.U16.U8: a.lo16 * b.byte2 + a.hi16 * b.byte3 + c
+#if defined(__CUDA_ARCH__)
+    return __dp2a_hi(a, b, c);
+#else
+    return (a & 0xFFFFu) * ((b >> 16) & 0xFFu) + (a >> 16) * (b >> 24) + c;
+#endif
+}
+
+// Byte tables of a descriptor's six 4-bit fields (bits 0..2 weight w[c], bit 3 "main symbol"), indexed by code through PRMT:
+// T.x / T.y = weights of codes 0..3 / 4..7, T.z / T.w = main flags of codes 0..3 / 4..7 (codes 6, 7: zero).
+struct ScanTab { uint32_t x, y, z, w; };
+PGI_HD ScanTab scan_tab(uint32_t tbl) {
+    ScanTab t;
+    t.x = (tbl & 7u) | ((tbl >> 4) & 7u) << 8 | ((tbl >> 8) & 7u) << 16 | ((tbl >> 12) & 7u) << 24;
+    t.y = ((tbl >> 16) & 7u) | ((tbl >> 20) & 7u) << 8;
+    t.z = ((tbl >> 3) & 1u) | ((tbl >> 7) & 1u) << 8 | ((tbl >> 11) & 1u) << 16 | ((tbl >> 15) & 1u) << 24;
+    t.w = ((tbl >> 19) & 1u) | ((tbl >> 23) & 1u) << 8;
+    return t;
+}
+
+// Weighted rank of one position. tbl = the low 24 bits of an extension descriptor, T = scan_tab(tbl). Returns, for the
+// first `rel` positions of the block plus the block's cumulative header:
+//     W = sum_c w[c] * rank_c(pos)      M = rank_main(pos)   (0 when no field has bit 3).
+// In-block part: with m_i = min(rel, E_i) (pgi_layout.h), run i contributes (m_i - m_{i-1}) * weight(c_i), so
+//     sum_i m_i * weight(c_i)  -  sum_i m_i * weight(c_{i+1})          (weight(c_12) = 0)
+// : per four runs two 16x2 mins, four PRMT table lookups (codes and next codes as selectors; weights and main flags) and
+// eight dp2a. No dependent chain over the runs, no per-run shifts and masks.
 struct PosRank { uint64_t W, M; uint32_t left; };   // left: positions of pos beyond the end of the block (0 when the block is the right one)
 
-#define PGI_SCAN_ENTRY(ENT, LEN)                                                     \
-    {                                                                                  \
-        const uint32_t v_ = tbl >> ((ENT) & 31u);                                     \
-        const uint32_t l_ = (LEN);                                                     \
-        const uint32_t t_ = l_ < r ? l_ : r;                                           \
-        r -= t_;                                                                       \
-        acc += (uint64_t) t_ * (uint64_t) (((v_ << 18) | v_) & 0x200007u);             \
-    }
-
-PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) {
+PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl, const ScanTab &T) {
     const uint64_t d = pos - block_start(w);
-    uint32_t r = d > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t) d;
-    uint64_t acc = 0;
-    { const uint32_t h = w[8] >> 16; PGI_SCAN_ENTRY(h, w[8] >> 21) }
+    const uint32_t r = d > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t) d;
+    const uint32_t rr = (r < 0xFFFFu ? r : 0xFFFFu) * 0x10001u;
+    const uint32_t c0 = w[9], c1 = w[8] >> 16;                          // codes 0..7, 8..11
+    const uint32_t n0 = c0 >> 4 | c1 << 28, n1 = c1 >> 4 | 0x7000u;     // next codes; behind the last run: unused (weight 0)
+    uint32_t aw = 0, an = 0, fw = 0, fn = 0, m1 = 0;
 #pragma unroll
-    for (int j = 9; j < 16; ++j) {
-        const uint32_t x = w[j], h = x >> 16;
-        PGI_SCAN_ENTRY(x, (x >> 5) & 0x7FFu)
-        PGI_SCAN_ENTRY(h, x >> 21)
+    for (int g = 0; g < 3; ++g) {
+        const uint32_t m0 = min_u16x2(rr, w[10 + 2 * g]);
+        m1 = min_u16x2(rr, w[11 + 2 * g]);
+        const uint32_t sc = g == 0 ? c0 : g == 1 ? c0 >> 16 : c1, sn = g == 0 ? n0 : g == 1 ? n0 >> 16 : n1;
+        const uint32_t bw = byte_perm(T.x, T.y, sc), bn = byte_perm(T.x, T.y, sn);
+        const uint32_t bf = byte_perm(T.z, T.w, sc), bg = byte_perm(T.z, T.w, sn);
+        aw = dp2a_hi(m1, bw, dp2a_lo(m0, bw, aw)); an = dp2a_hi(m1, bn, dp2a_lo(m0, bn, an));
+        fw = dp2a_hi(m1, bf, dp2a_lo(m0, bf, fw)); fn = dp2a_hi(m1, bg, dp2a_lo(m0, bg, fn));
     }
     // header: cumulative counts before the block; code c lives in word {5,1,2,3,6,4}[c], high byte as in pgi_layout.h
     const uint32_t wNL = tbl & 7u, wA = (tbl >> 4) & 7u, wC = (tbl >> 8) & 7u, wG = (tbl >> 12) & 7u, wN = (tbl >> 16) & 7u, wT = (tbl >> 20) & 7u;
@@ -141,11 +184,12 @@ PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) {
     uint64_t Ml = (uint64_t) w[5] * mNL + (uint64_t) w[1] * mA + (uint64_t) w[2] * mC + (uint64_t) w[3] * mG + (uint64_t) w[6] * mN + (uint64_t) w[4] * mT;
     const uint32_t Wh = hA * wA + hC * wC + hG * wG + hT * wT, Mh = hA * mA + hC * mC + hG * mG + hT * mT;
     PosRank o;
-    o.W = Wl + ((uint64_t) Wh << 32) + (acc & 0x1FFFFFull);
-    o.M = Ml + ((uint64_t) Mh << 32) + (acc >> 21);
-    o.left = r;
+    o.W = Wl + ((uint64_t) Wh << 32) + (uint64_t) (aw - an);
+    o.M = Ml + ((uint64_t) Mh << 32) + (uint64_t) (fw - fn);
+    o.left = r - (m1 >> 16);                                          // m_11 = min(rel, length of the block)
     return o;
 }
+PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) { return pos_rank(w, pos, tbl, scan_tab(tbl)); }
 
 // Exact but slow: search the block, then rank (the fallback of extend_desc; batched rank API).
 #if defined(__CUDA_ARCH__)

@@ -146,12 +146,12 @@ public:
     void finish() { flush_pending(); if (ne_) emit(); }
 private:
     std::vector<uint64_t> &out_; unsigned pcode_ = 8; uint64_t plen_ = 0;
-    uint64_t bstart_ = 0, bcum_[6]; uint32_t ent_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
+    uint64_t bstart_ = 0, bcum_[6]; uint32_t code_[PGI_RUNS_PER_BLOCK], end_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
     void flush_pending() {
         while (plen_) {
             uint64_t t = plen_ < PGI_MAX_RUN_ENTRY ? plen_ : PGI_MAX_RUN_ENTRY;
             if (!ne_) { bstart_ = pos; std::memcpy(bcum_, cum, sizeof(cum)); }
-            ent_[ne_++] = (uint16_t) ((pcode_ << 2) | (t << 5));        // code4 | length << 5
+            code_[ne_] = pcode_; end_[ne_] = (uint32_t) (pos + t - bstart_); ++ne_;
             cum[pcode_] += t; pos += t; plen_ -= t;
             if (ne_ == PGI_RUNS_PER_BLOCK) emit();
         }
@@ -166,9 +166,12 @@ private:
         w[0] = (uint32_t) bstart_; w[1] = (uint32_t) A; w[2] = (uint32_t) C; w[3] = (uint32_t) G; w[4] = (uint32_t) T;
         w[5] = (uint32_t) NL; w[6] = (uint32_t) N;
         w[7] = (uint32_t) (bstart_ >> 32) | (uint32_t) (A >> 32) << 8 | (uint32_t) (C >> 32) << 16 | (uint32_t) (G >> 32) << 24;
-        auto ent = [&](unsigned i) -> uint32_t { return i < ne_ ? ent_[i] : 0u; };
-        w[8] = (uint32_t) (T >> 32) | ent(0) << 16;
-        for (unsigned j = 0; j < 7; ++j) w[9 + j] = ent(1 + 2 * j) | ent(2 + 2 * j) << 16;
+        uint64_t codes = 0;
+        for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) codes |= (uint64_t) (i < ne_ ? code_[i] : PGI_CODE_UNUSED) << (4 * i);
+        auto end = [&](unsigned i) -> uint32_t { return end_[i < ne_ ? i : ne_ - 1]; };     // unused runs repeat the last end offset
+        w[8] = (uint32_t) (T >> 32) | (uint32_t) (codes >> 32) << 16;
+        w[9] = (uint32_t) codes;
+        for (unsigned j = 0; j < 6; ++j) w[10 + j] = end(2 * j) | end(2 * j + 1) << 16;
         for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) out_.push_back((uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32);
         starts.push_back(bstart_);
         ne_ = 0;

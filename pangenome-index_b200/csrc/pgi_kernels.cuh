@@ -19,7 +19,7 @@ namespace pgi {
 
 struct MemArgs {
     RiDev ix;
-    const uint32_t *desc;          // desc_b[256] followed by desc_f[256]
+    const uint32_t *desc;          // desc_b[256], desc_f[256], then the 512 x 4-word scan tables of those descriptors (PGI_DESC_WORDS)
     const uint64_t *reads64;       // read bytes viewed as aligned u64 words (buffer padded to 8 bytes)
     const uint64_t *read_off;      // n_reads + 1 byte offsets
     uint64_t n_reads, min_len, min_occ;
@@ -68,8 +68,12 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
 template <int MODE, int THREADS, int BPS>
 __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
+    __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
     __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
-    for (int i = threadIdx.x; i < 512; i += blockDim.x) s_desc[i] = a.desc[i];
+    for (int i = threadIdx.x; i < 512; i += blockDim.x) {
+        s_desc[i] = a.desc[i];
+        if (MODE) s_tab[i] = reinterpret_cast<const uint4 *>(a.desc + 512)[i];
+    }
     __syncthreads();
     const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -184,12 +188,14 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 uint64_t p1 = t.k, p2 = p1 + (uint64_t) t.s;
                 if (p2 > a.ix.n) p2 = a.ix.n;
                 if (p1 > a.ix.n) p1 = a.ix.n;
-                const uint32_t d = s_desc[(fwd ? 256u : 0u) + sym], tbl = d & 0xFFFFFFu;
+                const uint32_t di = (fwd ? 256u : 0u) + sym, d = s_desc[di], tbl = d & 0xFFFFFFu;
+                const uint4 tq = s_tab[di];
+                ScanTab T; T.x = tq.x; T.y = tq.y; T.z = tq.z; T.w = tq.w;
                 uint32_t w[16];
                 ld_staged(wstage, 0u, lane, w);
-                PosRank r1 = pos_rank(w, p1, tbl);
+                PosRank r1 = pos_rank(w, p1, tbl, T);
                 ld_staged(wstage, b2 != PGI_NOBLK ? 1u : 0u, lane, w);
-                PosRank r2 = pos_rank(w, p2, tbl);
+                PosRank r2 = pos_rank(w, p2, tbl, T);
                 if (r1.left | r2.left) {                      // rare: a guess landed short (bucket with more than two boundaries)
                     if (r1.left) r1 = rank_slow(a.ix, p1, tbl);
                     if (r2.left) r2 = rank_slow(a.ix, p2, tbl);

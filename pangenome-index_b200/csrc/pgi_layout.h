@@ -8,16 +8,21 @@
 //   w1..w4  A, C, G, T, low 32 bits     symbol counts before the block (40 bits each)
 //   w5, w6  NL, N                       endmarker / 'N' counts before the block (32 bits each)
 //   w7      start_hi | A_hi << 8 | C_hi << 16 | G_hi << 24      (bits 32..39 of the 40-bit fields)
-//   w8      T_hi | spare << 8 | e0 << 16
-//   w9..w15 e1..e14, two per word (odd entry in the low half)
-// Run entry e_i (16 bits) = code4 | length << 5: code4 = 4 * code (5 bits), length 1..2047 (0 = unused entry).
-// code = index into nuc = {'\n','A','C','G','N','T'} (include/pangenome_index/utils.hpp:11). code4 is stored
-// pre-multiplied so that a 32-bit shift by the raw entry (which uses the low 5 bits only) indexes a table of
-// 4-bit fields without extracting the code first. A block covers at most 15 * 2047 < 2^15 positions.
+//   w8      T_hi | spare << 8 | codes 8..11 << 16               (one nibble per run)
+//   w9      codes 0..7                                          (one nibble per run, run 0 in the low nibble)
+//   w10..w15 E_0..E_11, two per word (even run in the low half)
+// Run i of the block has symbol code c_i = index into nuc = {'\n','A','C','G','N','T'}
+// (include/pangenome_index/utils.hpp:11) and END OFFSET E_i = number of block positions up to and including run i
+// (16 bits, run lengths 1..4095: 12 * 4095 < 2^16). Unused runs have code 7 and repeat the last end offset, so E_11 is
+// always the length of the block. Storing ends instead of lengths makes the scan data-parallel: the positions of run i
+// that lie before block offset rel are min(rel, E_i) - min(rel, E_{i-1}), two runs per 16x2 SIMD min, and the weighted
+// sums are byte dot products (dp2a) against 8-byte weight tables looked up with the code nibbles as PRMT selectors
+// (pos_rank in pgi_core.cuh).
 #define PGI_BLOCK_U32 16
 #define PGI_BLOCK_WORDS 8            /* the same block counted in u64 words (host vectors are u64) */
-#define PGI_RUNS_PER_BLOCK 15
-#define PGI_MAX_RUN_ENTRY 2047ull
+#define PGI_RUNS_PER_BLOCK 12
+#define PGI_MAX_RUN_ENTRY 4095ull
+#define PGI_CODE_UNUSED 7u
 
 // Block directory: two levels, both read with independent loads (no dependent chain between them).
 //   sb[pos >> sb_shift]      (u32) index of the block containing the first position of the superbucket (2^19..2^30
@@ -29,7 +34,7 @@
 // block of a one-level table, so the directory of a 2 G-position index is 31 MB and lives in L2 while the blocks stream
 // from HBM. A bucket with more than two boundaries makes the guess land short; the scan notices (positions left over
 // after the last run) and the rare slow path searches the block starts.
-#define PGI_SB_MIN_SHIFT 19           /* 2^19 / 15 < 2^16: the 16-bit delta always fits */
+#define PGI_SB_MIN_SHIFT 19           /* 2^19 / 12 < 2^16: the 16-bit delta always fits */
 #define PGI_SB_MAX_SHIFT 30           /* the flattener takes the largest shift whose deltas still fit: the sb table is then a few cache lines */
 #define PGI_DIR_MAX_SHIFT 8
 
@@ -44,6 +49,7 @@
 //   bits 24..26 wq: how many times the quirk delta is added to k'
 //   bit 27      R[sym_map[a]] comes from the quirk slot;  bit 28: it is constant zero
 //   bits 29..31 sym_map[a]: index into C
+#define PGI_DESC_WORDS (512 + 512 * 4)  /* device copy: desc_b[256], desc_f[256], then a 4-word scan table per descriptor */
 #define PGI_DESC_MAIN_QUIRK (1u << 27)
 #define PGI_DESC_MAIN_ZERO (1u << 28)
 typedef struct {
