@@ -76,7 +76,7 @@ struct pgi_index {
     uint32_t *d_desc = nullptr;
     std::vector<void *> owned;
     // sizes of the uploaded arrays, for clone
-    uint64_t n_block_words = 0, n_dir = 0, n_sb = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
+    uint64_t n_block_words = 0, n_dir = 0, n_sb = 0, n_dense = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
     std::mutex compute_mu;                                  // see pgi_find_mems
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
@@ -129,6 +129,7 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
         d.blocks = upload(ri.blocks, ix->owned, bytes); ix->n_block_words = ri.blocks.size();
         d.dir = upload(ri.dir, ix->owned, bytes); ix->n_dir = ri.dir.size();
         d.sb = upload(ri.sb, ix->owned, bytes); ix->n_sb = ri.sb.size();
+        d.dense = upload(ri.dense, ix->owned, bytes); ix->n_dense = ri.dense.size();
         d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
         d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk; d.sb_shift = ri.k.sb_shift; d.pad_ = 0;
         for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
@@ -184,12 +185,13 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags; ix->has_ri = src->has_ri;
-        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_sb = src->n_sb; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
+        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_sb = src->n_sb; ix->n_dense = src->n_dense; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
         ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
         const int sd = src->device;
         ix->ri.blocks = clone_arr(src->ri.blocks, sd, src->n_block_words, device, ix->owned);
         ix->ri.dir = clone_arr(src->ri.dir, sd, src->n_dir, device, ix->owned);
         ix->ri.sb = clone_arr(src->ri.sb, sd, src->n_sb, device, ix->owned);
+        ix->ri.dense = clone_arr(src->ri.dense, sd, src->n_dense, device, ix->owned);
         ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);
@@ -316,7 +318,7 @@ uint64_t read_back(pgi_batch *b, const void *dptr) {
 struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads; };
 const K1Variant &k1_variant() {
     static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
-        {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
+        {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
         {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process

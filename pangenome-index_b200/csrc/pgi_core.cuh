@@ -27,6 +27,7 @@ struct RiDev {
     const uint64_t *blocks;     // 8 words per run block, 64-byte aligned
     const uint32_t *dir;        // block directory, per bucket of 2^dir_shift positions (pgi_layout.h)
     const uint32_t *sb;         // block index at every superbucket start
+    const uint32_t *dense;      // records of the dense buckets (pgi_layout.h)
     const uint64_t *q_start;    // quirk tables (n_quirk entries) or nullptr
     const uint64_t *q_val;
     uint64_t n, n_blocks, n_quirk;
@@ -82,10 +83,21 @@ PGI_HD uint32_t ld32(const uint32_t *p) {
     return *p;
 #endif
 }
-// Block guess from the two directory words of pos: exact unless the bucket holds more than two block boundaries and
-// pos lies behind the third, in which case the guess is SHORT (start(guess) <= pos always holds).
+// Block guess from the two directory words of pos: exact unless the bucket is one of the (never seen) dense buckets
+// beyond the 65535 that have a record, in which case the guess is SHORT (start(guess) <= pos always holds).
 PGI_HD uint64_t locate_guess(const RiDev &ix, uint64_t pos, uint32_t e, uint32_t base) {
     const uint32_t rel = (uint32_t) pos & ((1u << ix.dir_shift) - 1u);
+    if ((e & 0xFFFFu) == 0xFFFFu) {                                       // dense bucket: count the boundaries at or before rel
+        const uint32_t *rec = ix.dense + (uint64_t) (e >> 16) * PGI_DENSE_U32;
+        uint32_t cnt = 0;
+        for (uint32_t i = 1; i < PGI_DENSE_U32; ++i) {
+            const uint32_t x = ld32(rec + i);
+            const uint32_t c = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
+            cnt += c;
+            if (c < 4u) break;                                            // ascending: nothing further can count
+        }
+        return (uint64_t) ld32(rec) + cnt;
+    }
     const uint32_t t1 = (e >> 16) & 0xFFu, t2 = e >> 24;                 // 0 = no boundary: (0 - 1) < rel is false
     return (uint64_t) base + (e & 0xFFFFu) + ((t1 - 1u) < rel) + ((t2 - 1u) < rel);
 }
@@ -95,7 +107,9 @@ PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
     uint64_t lo = locate_guess(ix, pos, ld32(ix.dir + b), ld32(ix.sb + (pos >> ix.sb_shift)));
     uint64_t s1 = ((b + 1) << ix.dir_shift) >> ix.sb_shift; const uint64_t smax = ix.n >> ix.sb_shift;
     if (s1 > smax) s1 = smax;                                             // the flattener clamps the same way
-    uint64_t up = (uint64_t) ld32(ix.sb + s1) + (ld32(ix.dir + b + 1) & 0xFFFFu);   // block at the next bucket start
+    const uint32_t en = ld32(ix.dir + b + 1);
+    uint64_t up = (en & 0xFFFFu) == 0xFFFFu ? (uint64_t) ld32(ix.dense + (uint64_t) (en >> 16) * PGI_DENSE_U32)
+                                            : (uint64_t) ld32(ix.sb + s1) + (en & 0xFFFFu);      // block at the next bucket start
     if (up >= ix.n_blocks) up = ix.n_blocks - 1;
     while (lo < up) {                                                     // invariant: start(lo) <= pos
         const uint64_t mid = (lo + up + 1) >> 1;

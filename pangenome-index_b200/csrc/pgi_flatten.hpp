@@ -112,6 +112,7 @@ struct RiImage {
     RiConsts k;                          // scalars + tables copied to the device as one struct
     std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte run block
     std::vector<uint32_t> dir, sb;       // two-level block directory (pgi_layout.h)
+    std::vector<uint32_t> dense;         // records of the dense buckets (PGI_DENSE_U32 words each)
     std::vector<uint64_t> q_start, q_val;// quirk slot tables (legacy files with an absent nuc symbol)
     uint64_t n_file_runs = 0, n_ref_blocks = 0; bool encoded = false;
 };
@@ -213,9 +214,25 @@ inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, ui
         if (idx + 1 < nb && starts[idx + 1] < hi) t1 = starts[idx + 1] - lo;
         if (idx + 2 < nb && starts[idx + 2] < hi) t2 = starts[idx + 2] - lo;
         const uint64_t delta = idx - base;
-        if (delta >> 16) throw FormatError("internal: block directory delta overflow");
+        if (delta >= 0xFFFF) throw FormatError("internal: block directory delta overflow");
         im.dir[b] = (uint32_t) (delta | (t1 << 16) | (t2 << 24));
+        // dense bucket (more than two block boundaries inside): its own record with every boundary (pgi_layout.h)
+        if (idx + 3 < nb && starts[idx + 3] < hi && im.dense.size() / PGI_DENSE_U32 < 0xFFFF) {
+            uint32_t rec[PGI_DENSE_U32] = {0}; unsigned nbd = 0;
+            rec[0] = (uint32_t) idx;
+            for (uint64_t j = idx + 1; j < nb && starts[j] < hi; ++j) {
+                if (nbd == PGI_DENSE_BOUNDS) { nbd = PGI_DENSE_BOUNDS + 1; break; }
+                const uint32_t off = (uint32_t) (starts[j] - lo);
+                rec[1 + nbd / 4] |= off << (8 * (nbd % 4)); ++nbd;
+            }
+            if (nbd <= PGI_DENSE_BOUNDS) {               // (cannot overflow with >= 12-position blocks; kept as a guard)
+                const uint64_t id = im.dense.size() / PGI_DENSE_U32;
+                im.dense.insert(im.dense.end(), rec, rec + PGI_DENSE_U32);
+                im.dir[b] = (uint32_t) (0xFFFFu | id << 16);
+            }
+        }
     }
+    if (im.dense.empty()) im.dense.assign(PGI_DENSE_U32, 0);   // never a null table on the device
 }
 
 // Per-byte extension descriptors: SURVEY.md App. B2/B3 folded into weights over true ranks

@@ -34,6 +34,15 @@
 // block of a one-level table, so the directory of a 2 G-position index is 31 MB and lives in L2 while the blocks stream
 // from HBM. A bucket with more than two boundaries makes the guess land short; the scan notices (positions left over
 // after the last run) and the rare slow path searches the block starts.
+// Dense buckets: a bucket with MORE than two block boundaries inside (short runs: e.g. the first n_seq BWT rows, which
+// hold the last symbol of every sequence, next to C['A'] = n_seq where every search for an 'A' starts) gets the
+// reserved delta 0xFFFF and, in bits 16..31, the number of a 32-byte record in the dense table:
+//   word 0      (u32) absolute index of the block containing the first position of the bucket
+//   bytes 4..31 offsets inside the bucket of every block boundary, ascending (0: none)
+// so that the guess is exact there too (a bucket holds at most 256 / 12 boundaries). Only when more than 65535
+// buckets are dense do the rest keep the two-boundary form and fall back to the search.
+#define PGI_DENSE_U32 8
+#define PGI_DENSE_BOUNDS 28
 #define PGI_SB_MIN_SHIFT 19           /* 2^19 / 12 < 2^16: the 16-bit delta always fits */
 #define PGI_SB_MAX_SHIFT 30           /* the flattener takes the largest shift whose deltas still fit: the sb table is then a few cache lines */
 #define PGI_DIR_MAX_SHIFT 8

@@ -17,7 +17,7 @@ static thread_local std::string g_err;
 
 static void bind(sim_index *s) {
     RiDev &d = s->rd; const RiImage &im = s->ri;
-    d.blocks = im.blocks.data(); d.dir = im.dir.data(); d.sb = im.sb.data();
+    d.blocks = im.blocks.data(); d.dir = im.dir.data(); d.sb = im.sb.data(); d.dense = im.dense.data();
     d.q_start = im.q_start.empty() ? nullptr : im.q_start.data(); d.q_val = im.q_val.empty() ? nullptr : im.q_val.data();
     d.n = im.k.n; d.n_blocks = im.k.n_blocks; d.n_quirk = im.k.n_quirk; d.dir_shift = im.k.dir_shift; d.has_quirk = im.k.has_quirk; d.sb_shift = im.k.sb_shift; d.pad_ = 0;
     for (int i = 0; i < 8; ++i) d.C[i] = im.k.C[i];
