@@ -243,6 +243,19 @@ def main():
     k1_bytes_per_launch = 128.0 * d_per_e * ext_rank0 / args.steps
     k1_s = (k1_ms / args.steps) * 1e-3
     achieved = k1_bytes_per_launch / k1_s / 1e9
+    # DRAM traffic of the same kernel on the same default workload, from the committed ncu --set full capture (per launch)
+    traffic = None; traffic_src = None
+    if args.workload == "synth" and args.ref_len == 50_000_000 and args.n_hap == 20 and n == 2_000_000 and L == 150:
+        try:
+            import glob, re
+            f = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_fmd_mem_kernel_raw.txt")))[-1]
+            vals = {}
+            for ln in open(f):
+                m = re.match(r"(dram__bytes_(?:read|write)\.sum)\s+(\S+)\s+(\S+)", ln)
+                if m: vals[m.group(1)] = float(m.group(3)) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[m.group(2)]
+            traffic = vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"]; traffic_src = os.path.relpath(f, ROOT)
+        except Exception:
+            pass
     rnd = {}
     try:
         for b in (32, 64):
@@ -262,7 +275,7 @@ def main():
             "gpu_launches": int(cnt[0]),
             "stage_ms_per_step": {k: round(float(v) / args.steps, 3) for k, v in zip(["fmd_mem_kernel", "mem_order", "tag_plan", "tag_decode_sort", "tag_unique_compact", "run_total"], stage[:6])},
             "roofline": {"bound": "hbm", "kernel": "fmd_mem_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": k1_bytes_per_launch,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": k1_bytes_per_launch,
                          "bytes_model": "128 B x D, D = distinct reference 10-run blocks touched per extension (oracle: D/E = %.3f) x E = %d extensions per launch (counted by the kernel)" % (d_per_e, ext_rank0 // args.steps),
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
             "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",
