@@ -60,6 +60,12 @@ class ClockSampler(threading.Thread):
 
 E2E_CALLERS = 3
 
+def host_threads():
+    """Host threads the CPU legs use: every core this process may run on. Passed to the oracle explicitly, because
+    torchrun exports OMP_NUM_THREADS=1 to its workers and omp_get_max_threads() would then say 1."""
+    try: return max(1, len(os.sched_getaffinity(0)))
+    except Exception: return max(1, os.cpu_count() or 1)
+
 def make_workload(args, dev_index, rank):
     """-> dict(ri, tags, layout, reads (cuda uint8 [pool, n, L]), name, facts). Data prep only (not timed)."""
     import torch
@@ -94,6 +100,7 @@ def make_workload(args, dev_index, rank):
     return dict(ri=ri, tags=tags, layout=0, reads=reads, name=name, facts=facts)
 
 def cpu_oracle_rate(o, reads_np, L, min_len, min_occ, target_s, threads=0, count_work=True):
+    threads = threads or host_threads()
     """Time the oracle (all host threads) on a bounded sample sized for about target_s seconds. -> dict"""
     n_avail = len(reads_np) // L
     probe = min(n_avail, 20000)
@@ -113,15 +120,15 @@ def run_reference(args, rank, world):
     o = orc.Index(w["ri"], w["tags"], w["layout"])
     L = args.read_len
     reads_np = w["reads"][0].reshape(-1).cpu().numpy()
-    cores = orc.lib().orc_max_threads()
+    cores = host_threads()
     per_step_s = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     probe = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, per_step_s, count_work=False)
     n = probe["reads"]; off = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
     for _ in range(max(0, args.warmup - 1)):
-        o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, text=False)
+        o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores, text=False)
     t = 0.0
     for _ in range(args.steps):
-        t += o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, text=False)["seconds"]
+        t += o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores, text=False)["seconds"]
     rate = n * args.steps / t
     sample = "%d reads per step (bounded sample of the %d-read batch), %d OpenMP threads" % (n, args.reads_per_step, cores)
     line = {"impl": "reference", "metric": "find_mems reads/s (150bp, MEM + tag query)", "value": rate, "unit": "reads/s", "n_gpus": args.gpus,
@@ -233,7 +240,7 @@ def main():
                   and np.array_equal(G["n_runs"], R["n_runs"]) and G["extensions"] == R["counters"]["E"])
     c = R["counters"]; d_per_e = c["D"] / max(1, c["E"])
     cpu = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, args.cpu_seconds, count_work=False)
-    cores = orc.lib().orc_max_threads()
+    cores = host_threads()
     # ---- roofline of the dominant kernel (fmd_mem_kernel): algorithmic bytes = 128 B x D
     peaks = {}
     try: peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
