@@ -112,6 +112,25 @@ int pgi_find_mems(pgi_index *, const char *reads, const uint64_t *read_off, uint
                   uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out);
 void pgi_result_free(pgi_result *);
 
+/* The query_tags path: for every read the whole-read backward search FastLocate::count_encoded
+ * (include/pangenome_index/r-index.hpp:550-556; the legacy FastLocate::count :541-547 when the file has no encoded
+ * blocks, as src/query_tags.cpp:90-96 chooses) and, for reads with a match and an index with tags, the tag query of
+ * the final range (src/query_tags.cpp:97-102). Same buffer conventions as pgi_find_mems. Result: ONE record per read,
+ *   mems[i] = { start 0, end = read length, bwt_start = range.first, size = range.second - range.first + 1 },
+ * an empty range -- the reference's {1,0} -- being bwt_start 1, size 0 (no tags, n_runs 0); mem_off[i] = i;
+ * n_runs[i] = the reference's number_of_runs; extensions = LF steps executed. An empty read keeps the full range.
+ * PGI_EFORMAT on an encoded index without N (sigma 5): the reference reads a run header as a sixth cumulative there
+ * (src/r-index.cpp:577) and its results are garbage that this library does not reproduce. */
+int pgi_query_tags(pgi_index *, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                   void *cuda_stream, pgi_result *out);
+/* The same on a batch context (after pgi_batch_upload / pgi_batch_set_device_reads); results via
+ * pgi_batch_device_result / pgi_batch_fetch like pgi_batch_run. */
+int pgi_batch_run_query_tags(pgi_batch *);
+/* stdout of src/query_tags.cpp for such a result (the two lines TagArray::query_compressed_compact prints itself,
+ * src/tag_arrays.cpp:885-889, then the read_index summary line :103-108); read_index counts from first_index.
+ * malloc'd, free with pgi_free. */
+char *pgi_format_query_tags_text(const pgi_result *, uint64_t first_index, uint64_t *len);
+
 /* Explicit batch contexts, for callers that pipeline several batches per GPU (the find_mems driver)
  * or keep inputs / results resident in HBM (bench.py's device-resident figure). */
 int pgi_batch_create(pgi_index *, void *cuda_stream /* or NULL */, pgi_batch **out);

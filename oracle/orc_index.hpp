@@ -198,6 +198,72 @@ struct FastLocate {
         return bi_interval{k, k_prime, s};
     }
 
+    // ---- whole-read backward search: the query_tags path ----------------------
+    // symbol_to_code, r-index.hpp:664-667 (bytes outside nuc alias code 0, the endmarker)
+    static int symbol_to_code(uint64_t symbol) { for (int i = 0; i < 6; ++i) if ((uint64_t) NUC[i] == symbol) return i; return 0; }
+
+    // FastLocate::rankAt (4-argument form), r-index.cpp:558-568: true rank of byte `symbol` at pos
+    uint64_t rankAt(uint64_t pos, uint64_t symbol) const {
+        uint64_t bid, bstart; locate_block(pos, bid, bstart);
+        if (bid >= blocks.size()) return 0;
+        const RunBlock &b = blocks[bid];
+        uint64_t col = sym_map[symbol & 0xFF];
+        return block_rankAt(b, pos - bstart, symbol) + (col < b.cum.size() ? b.cum[col] : 0);
+    }
+
+    // EncodedBlock::rank_of_code, r-index.cpp:114-131
+    uint64_t rank_of_code(size_t &loc, size_t end_pos, int target_code, uint64_t rel) const {
+        uint64_t rank = 0, cur = 0;
+        while (loc < end_pos) {
+            uint8_t header = blocks_encoded_stream[loc++];
+            int code = (header >> 5) & 0x7; uint64_t prefix = header & 0x1F;
+            uint64_t run_length = prefix < 31 ? prefix + 1 : 32 + bytecode_read(blocks_encoded_stream.data(), blocks_encoded_stream.size(), loc);
+            if (code == target_code) {
+                if (cur + run_length > rel) { rank += rel - cur; break; }
+                rank += run_length;
+            }
+            cur += run_length;
+            if (cur > rel) break;
+        }
+        return rank;
+    }
+
+    // FastLocate::rankAt_encoded, r-index.cpp:570-590. The reference constructs the block reader with SIX
+    // cumulatives whatever the file holds (:577): on an encoded file without N (five cumulatives) the sixth read
+    // swallows run-header bytes and the scan starts late. Restated literally; the product refuses that case.
+    uint64_t rankAt_encoded(uint64_t pos, uint64_t symbol) const {
+        if (!is_encoded()) return rankAt(pos, symbol);
+        uint64_t bid, bstart; locate_block(pos, bid, bstart);
+        uint64_t nb = blocks_encoded_start_bits.size();
+        if (bid >= nb) return 0;
+        size_t loc = (size_t) blocks_encoded_start_bits.get(bid);
+        size_t end_pos = (bid + 1 < nb) ? (size_t) blocks_encoded_start_bits.get(bid + 1) : blocks_encoded_stream.size();
+        uint64_t cum[6]; read_cumulative(loc, 6, cum);
+        int target_code = symbol_to_code(symbol);
+        return rank_of_code(loc, end_pos, target_code, pos - bstart) + cum[target_code];
+    }
+
+    // FastLocate::LF (range form), r-index.cpp:650-686, and LF_encoded, :689-711. A pattern byte reaches these as
+    // size_t(char); bytes >= 0x80 would index sym_map out of bounds there and are taken modulo 256 here.
+    std::pair<uint64_t, uint64_t> LF_encoded(std::pair<uint64_t, uint64_t> range, uint64_t sym) const {
+        sym &= 0xFF;
+        if (!is_encoded() && !sym_map[sym]) return {1, 0};                       // legacy LF only (:653)
+        if (range.first > range.second) return {1, 0};
+        range.first = rankAt_encoded(range.first, sym);
+        uint64_t sym_inside = rankAt_encoded(range.second + 1, sym) - range.first;
+        if (sym_inside == 0) return {1, 0};
+        range.first += C[sym_map[sym]];
+        range.second = range.first + sym_inside - 1;
+        return range;
+    }
+
+    // FastLocate::count_encoded, r-index.hpp:550-556 (count :541-547 is the same loop over the legacy LF)
+    std::pair<uint64_t, uint64_t> count_encoded(const char *pattern, size_t len) const {
+        std::pair<uint64_t, uint64_t> range{0, bwt_size() - 1};
+        for (size_t i = len; i > 0; --i) range = LF_encoded(range, (uint8_t) pattern[i - 1]);
+        return range;
+    }
+
     // r-index.cpp:758-764 / :1500-1509
     bi_interval forward_extend_encoded(const bi_interval &bint, uint64_t symbol, uint64_t *distinct_blocks = nullptr) const {
         bi_interval tmp{bint.reverse, bint.forward, bint.size};

@@ -172,6 +172,69 @@ int orc_find_mems(const orc_index *ix, const char *reads, const uint64_t *read_o
     } catch (const std::exception &e) { g_err = e.what(); return -1; }
 }
 
+// query_tags over a batch (src/query_tags.cpp:87-109): per read count_encoded / count, then -- for reads with a
+// match -- the tag query of the final range. One record per read: mems[i] = {0, len, range.first, range.second -
+// range.first + 1} (size 0 and bwt_start 1 = the reference's empty range {1,0}); mem_off[i] = i.
+int orc_query_tags(const orc_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                   int with_tags, int threads, orc_result *res) {
+    try {
+        if (with_tags && !ix->has_tags) throw std::runtime_error("oracle: tags not loaded");
+        std::memset(res, 0, sizeof(*res));
+#ifdef _OPENMP
+        if (threads <= 0) threads = omp_get_max_threads();
+#else
+        threads = 1;
+#endif
+        std::vector<MEM> recs(n_reads);
+        std::vector<std::vector<uint64_t>> tv(n_reads);
+        std::vector<uint64_t> nruns(n_reads, 0);
+#pragma omp parallel for schedule(dynamic, 64) num_threads(threads)
+        for (int64_t r = 0; r < (int64_t) n_reads; ++r) {
+            const uint64_t len = read_off[r + 1] - read_off[r];
+            auto range = ix->ri.count_encoded(reads + read_off[r], len);
+            const bool hit = range.first <= range.second;
+            recs[r] = MEM{0, len, hit ? range.first : 1, hit ? (int64_t) (range.second - range.first + 1) : 0};
+            if (hit && with_tags) nruns[r] = ix->tags.query(range.first, range.second, tv[r]);
+        }
+        uint64_t nt = 0; for (auto &v : tv) nt += v.size();
+        res->n_reads = n_reads; res->n_mems = n_reads; res->n_tags = nt;
+        res->mem_off = (uint64_t *) std::malloc((n_reads + 1) * 8);
+        res->mems = (MEM *) std::malloc((n_reads + 1) * sizeof(MEM));
+        res->tag_off = (uint64_t *) std::malloc((n_reads + 1) * 8);
+        res->tags = (uint64_t *) std::malloc((nt + 1) * 8);
+        res->n_runs = (uint64_t *) std::malloc((n_reads + 1) * 8);
+        uint64_t ti = 0;
+        for (uint64_t r = 0; r < n_reads; ++r) {
+            res->mem_off[r] = r; res->mems[r] = recs[r]; res->n_runs[r] = nruns[r]; res->tag_off[r] = ti;
+            if (!tv[r].empty()) std::memcpy(res->tags + ti, tv[r].data(), tv[r].size() * 8);
+            ti += tv[r].size();
+        }
+        res->mem_off[n_reads] = n_reads; res->tag_off[n_reads] = nt;
+        return 0;
+    } catch (const std::exception &e) { g_err = e.what(); return -1; }
+}
+
+// stdout of query_tags for such a result: for every read with a match the two lines query_compressed_compact prints
+// itself (tag_arrays.cpp:885-889) and the summary line of src/query_tags.cpp:103-108; read_index counts from first_index.
+char *orc_format_query_tags(const orc_result *r, uint64_t first_index, uint64_t *len) {
+    std::string out;
+    for (uint64_t i = 0; i < r->n_reads; ++i) {
+        const MEM &m = r->mems[i];
+        if (m.size == 0) continue;
+        uint64_t a = r->tag_off[i], b = r->tag_off[i + 1];
+        out += "Number of unique positions: "; out += std::to_string(b - a); out += '\n';
+        for (uint64_t t = a; t < b; ++t) { out += std::to_string(r->tags[t]); out += ", "; }
+        out += '\n';
+        out += "read_index="; out += std::to_string(first_index + i); out += "\tlen="; out += std::to_string(m.end);
+        out += "\tbwt_start="; out += std::to_string(m.bwt_start); out += "\tbwt_end="; out += std::to_string(m.bwt_start + (uint64_t) m.size - 1);
+        out += "\truns="; out += std::to_string(r->n_runs[i]); out += '\n';
+    }
+    char *buf = (char *) std::malloc(out.size() + 1);
+    std::memcpy(buf, out.data(), out.size()); buf[out.size()] = 0;
+    *len = out.size();
+    return buf;
+}
+
 void orc_result_free(orc_result *r) {
     std::free(r->mem_off); std::free(r->mems); std::free(r->tag_off); std::free(r->tags); std::free(r->n_runs);
     std::memset(r, 0, sizeof(*r));

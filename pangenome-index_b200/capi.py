@@ -10,7 +10,7 @@ _lib = None
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
-           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
+           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -57,6 +57,10 @@ def lib():
         L.pgi_batch_stage_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_double * 8)]
         L.pgi_format_text.argtypes = [ctypes.POINTER(Result), u64, i32, ctypes.POINTER(u64)]
         L.pgi_free.argtypes = [vp]
+        L.pgi_query_tags.argtypes = [vp, vp, vp, u64, vp, ctypes.POINTER(Result)]
+        L.pgi_batch_run_query_tags.argtypes = [vp]
+        L.pgi_format_query_tags_text.restype = ctypes.c_void_p
+        L.pgi_format_query_tags_text.argtypes = [ctypes.POINTER(Result), u64, ctypes.POINTER(u64)]
         L.pgi_host_alloc.restype = vp; L.pgi_host_alloc.argtypes = [ctypes.c_size_t]; L.pgi_host_free.argtypes = [vp]
         L.pgi_random_access_gbs.argtypes = [i32, u64, ctypes.c_uint32, u64, i32, ctypes.POINTER(ctypes.c_double)]
         _lib = L
@@ -129,6 +133,19 @@ class Index:
         out = _result_to_dict(res, L, self.has_tags, text=text); L.pgi_result_free(ctypes.byref(res))
         return out
 
+    def query_tags(self, reads, read_off, text=True):
+        """The query_tags path (src/query_tags.cpp:87-109): whole-read count + tag query; one record per read."""
+        reads = np.ascontiguousarray(reads, dtype=np.uint8); read_off = np.ascontiguousarray(read_off, dtype=np.uint64)
+        res = Result(); L = lib()
+        _ck(L.pgi_query_tags(self.h, reads.ctypes.data, read_off.ctypes.data, len(read_off) - 1, None, ctypes.byref(res)))
+        out = _result_to_dict(res, L, self.has_tags, text=False)
+        if text:
+            ln = ctypes.c_uint64()
+            p = L.pgi_format_query_tags_text(ctypes.byref(res), 0, ctypes.byref(ln))
+            out["text"] = ctypes.string_at(p, ln.value); L.pgi_free(p)
+        L.pgi_result_free(ctypes.byref(res))
+        return out
+
     def find_mems_raw(self, reads_ptr, off_ptr, n_reads, min_len, min_occ):
         """pgi_find_mems on raw host pointers (pinned recommended); returns the Result struct whose arrays live in
         library-owned pinned memory until result_free(res). No numpy copies: this is what bench.py times end to end."""
@@ -156,6 +173,8 @@ class Batch:
         _ck(lib().pgi_batch_set_device_reads(self.h, d_reads_ptr, d_off_ptr, n_reads, total_bytes))
     def run(self, min_len, min_occ):
         _ck(lib().pgi_batch_run(self.h, min_len, min_occ))
+    def run_query_tags(self):
+        _ck(lib().pgi_batch_run_query_tags(self.h))
     def stage_ms(self):
         ms = (ctypes.c_double * 8)(); _ck(lib().pgi_batch_stage_ms(self.h, ctypes.byref(ms)))
         return list(ms)

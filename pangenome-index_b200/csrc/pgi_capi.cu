@@ -73,7 +73,7 @@ struct pgi_index {
     int device = 0;
     RiDev ri; TagDev tg; bool has_tags = false, has_ri = true;
     RiConsts consts; SparseRankConsts ivk;
-    uint32_t *d_desc = nullptr;
+    uint32_t *d_desc = nullptr, *d_desc_c = nullptr;      // extension descriptors; LF-step descriptors of the whole-read search
     std::vector<void *> owned;
     // sizes of the uploaded arrays, for clone
     uint64_t n_block_words = 0, n_dir = 0, n_sb = 0, n_dense = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
@@ -140,6 +140,12 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
             desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
         }
         ix->d_desc = upload(desc, ix->owned, bytes);
+        for (int i = 0; i < 512; ++i) {                    // the count bank in the same shape (both halves: the kernel never asks for "forward")
+            desc[i] = ri.k.desc_c[i & 255];
+            const ScanTab t = scan_tab(desc[i] & 0xFFFFFFu);
+            desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
+        }
+        ix->d_desc_c = upload(desc, ix->owned, bytes);
         std::memset(&ix->tg, 0, sizeof(ix->tg));
         if (has_tags) {
             TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = tg.intervals.k;
@@ -195,6 +201,7 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);
+        ix->d_desc_c = clone_arr(src->d_desc_c, sd, PGI_DESC_WORDS, device, ix->owned);
         if (src->has_tags) {
             ix->tg.iv.dir = clone_arr(src->tg.iv.dir, sd, src->n_iv_dir, device, ix->owned);
             ix->tg.iv.low = clone_arr(src->tg.iv.low, sd, src->n_iv_low, device, ix->owned);
@@ -369,6 +376,34 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
 }
 
+// Whole-read backward search (query_tags path): the same persistent kernel in OP 1; one record per read, in read order.
+__global__ void iota_kernel(uint64_t n_plus_1, uint64_t *out) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i < n_plus_1) out[i] = i;
+}
+void run_count_stage(pgi_batch *b, int &launches) {
+    pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
+    b->d_mem_off.need((n + 1) * 8); b->d_mems.need(std::max<uint64_t>(1, n) * 32);
+    void (*fn)(const MemArgs) = fmd_mem_kernel<1, 256, 4, 1>; const unsigned threads = 256;
+    int blocks_per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fn, (int) threads, 0));
+    if (blocks_per_sm < 1) blocks_per_sm = 1;
+    const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, (n + threads - 1) / threads));
+    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
+    CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
+    MemArgs a;
+    a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
+    a.n_reads = n; a.min_len = 1; a.min_occ = 0;
+    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = n;
+    a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
+    if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
+    iota_kernel<<<grid_for(n + 1, 256), 256, 0, b->stream>>>(n + 1, b->d_mem_off.as<uint64_t>());
+    ++launches; CK(cudaGetLastError());
+    b->extensions = read_back(b, ctr + 2);
+    b->n_mems = n;
+    CK(cudaEventRecord(b->ev[EV_MEM], b->stream)); CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
+}
+
 // Tag lookup for nm intervals given either as ordered MEM records or as start/end arrays (device pointers).
 void run_tag_stage(pgi_batch *b, uint64_t nm, const uint4 *mems, const uint64_t *start, const uint64_t *end, int &launches) {
     pgi_index *ix = b->ix; cudaStream_t st = b->stream;
@@ -438,16 +473,20 @@ float ev_ms(pgi_batch *b, int from, int to) { float ms = 0; cudaEventElapsedTime
     catch (const std::bad_alloc &) { return fail(PGI_ENOMEM, "out of host memory"); } \
     catch (const std::exception &e) { return fail(PGI_EINVAL, e.what()); }
 
-extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) {
+static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t min_occ) {
     if (!b) return fail(PGI_EINVAL, "null argument");
     if (!b->read_off) return fail(PGI_EINVAL, "no reads staged: call pgi_batch_upload or pgi_batch_set_device_reads first");
     if (b->n_reads >> 32) return fail(PGI_EINVAL, "more than 2^32 reads in one batch");
     if (!b->ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
+    if (count_mode && !b->ix->consts.count_ok)
+        return fail(PGI_EFORMAT, "encoded r-index without N: the reference's rankAt_encoded reads a run header as a sixth cumulative on such a "
+                                 "file (src/r-index.cpp:577), its count_encoded results are not reproduced");
     try {
         DeviceGuard g(b->ix->device);
         int launches = 0, reruns = 0;
         CK(cudaEventRecord(b->ev[EV_START], b->stream));
-        run_mem_stage(b, min_len, min_occ, launches, reruns);
+        if (count_mode) run_count_stage(b, launches);
+        else run_mem_stage(b, min_len, min_occ, launches, reruns);
         const uint64_t nm = b->n_mems;
         if (b->ix->has_tags) run_tag_stage(b, nm, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
         else {
@@ -466,6 +505,9 @@ extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) {
         return PGI_OK;
     } PGI_CATCH
 }
+
+extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) { return batch_run(b, false, min_len, min_occ); }
+extern "C" int pgi_batch_run_query_tags(pgi_batch *b) { return batch_run(b, true, 0, 0); }
 
 extern "C" int pgi_batch_stage_ms(pgi_batch *b, double ms[8]) {
     if (!b || !ms) return fail(PGI_EINVAL, "null argument");
@@ -513,8 +555,8 @@ static pgi_batch *pool_take(pgi_index *ix) {
 }
 static void pool_give(pgi_index *ix, pgi_batch *b) { std::lock_guard<std::mutex> l(ix->pool_mu); ix->pool.push_back(b); }
 
-extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
-                             uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out) {
+static int one_call(pgi_index *ix, bool count_mode, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                    uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out) {
     if (!ix || !read_off || !out || (!reads && n_reads)) return fail(PGI_EINVAL, "null argument");
     pgi_batch *b = pool_take(ix);
     if (!b) return PGI_ECUDA;
@@ -532,7 +574,7 @@ extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *r
     // call k+1 uploads and call k-1 downloads while call k computes.
     if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
     if (trace) t1 = now_ms();
-    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = pgi_batch_run(b, min_len, min_occ); }
+    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = batch_run(b, count_mode, min_len, min_occ); }
     const double t2 = trace ? now_ms() : 0;
     if (rc == PGI_OK) rc = pgi_batch_fetch(b, out);
     if (trace) std::fprintf(stderr, "[pgi] ctx %p reads %llu: enter %.2f uploaded %.2f run_done %.2f (mem kernel %.2f, stages %.2f ms) fetched %.2f\n", (void *) b,
@@ -541,6 +583,15 @@ extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *r
     if (rc != PGI_OK) { pool_give(ix, b); return rc; }
     out->owner = b;                                      // the result lives in the batch's pinned buffers
     return PGI_OK;
+}
+
+extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                             uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out) {
+    return one_call(ix, false, reads, read_off, n_reads, min_len, min_occ, cuda_stream, out);
+}
+extern "C" int pgi_query_tags(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
+                              void *cuda_stream, pgi_result *out) {
+    return one_call(ix, true, reads, read_off, n_reads, 0, 0, cuda_stream, out);
 }
 
 extern "C" void pgi_result_free(pgi_result *r) {
@@ -638,6 +689,28 @@ extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int wi
             }
         }
         s.push_back('\n');
+    }
+    char *buf = (char *) std::malloc(s.size() + 1);
+    if (!buf) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
+    std::memcpy(buf, s.data(), s.size()); buf[s.size()] = 0; *len = s.size();
+    return buf;
+}
+// stdout of src/query_tags.cpp:87-109 for a pgi_query_tags result: for every read with a match the two lines that
+// query_compressed_compact prints itself (src/tag_arrays.cpp:885-889), then the summary line (:103-108).
+extern "C" char *pgi_format_query_tags_text(const pgi_result *r, uint64_t first_index, uint64_t *len) {
+    if (!r || !len) { fail(PGI_EINVAL, "null argument"); return nullptr; }
+    std::string s;
+    s.reserve((size_t) (r->n_reads * 96 + r->n_tags * 12));
+    for (uint64_t i = 0; i < r->n_reads; ++i) {
+        const pgi_mem &x = r->mems[i];
+        if (x.size == 0) continue;                       // "Read i has no matches" goes to stderr in the reference
+        const uint64_t a = r->tag_off[i], e = r->tag_off[i + 1];
+        s += "Number of unique positions: "; put_u64(s, e - a); s.push_back('\n');
+        for (uint64_t t = a; t < e; ++t) { put_u64(s, r->tags[t]); s += ", "; }
+        s.push_back('\n');
+        s += "read_index="; put_u64(s, first_index + i); s += "\tlen="; put_u64(s, x.end);
+        s += "\tbwt_start="; put_u64(s, x.bwt_start); s += "\tbwt_end="; put_u64(s, x.bwt_start + (uint64_t) x.size - 1);
+        s += "\truns="; put_u64(s, r->n_runs[i]); s.push_back('\n');
     }
     char *buf = (char *) std::malloc(s.size() + 1);
     if (!buf) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }

@@ -275,6 +275,23 @@ inline void build_descriptors(RiImage &im, const bool present[6], bool legacy) {
         desc[a] = d;
     }
     for (int a = 0; a < 256; ++a) { k.desc_b[a] = desc[a]; k.desc_f[a] = desc[comp[a]]; }
+    // LF-step descriptors of the whole-read search (pgi_layout.h: desc_c).
+    //   legacy  LF (r-index.cpp:650-686): a byte with sym_map 0 fails; otherwise rankAt = true rank of the byte
+    //   encoded LF_encoded (:689-711):    rankAt_encoded ranks code symbol_to_code(a) (bytes outside nuc alias code 0,
+    //                                     r-index.hpp:664-667) and adds cum[code]: the true rank when six cumulatives exist
+    k.count_ok = legacy || sigma == 6;
+    for (int a = 0; a < 256; ++a) {
+        unsigned code = 0; bool in_nuc = false;
+        for (unsigned c = 0; c < 6; ++c) if (kNuc[c] == (uint8_t) a) { code = c; in_nuc = true; }
+        const unsigned mi = k.sym_map[a];
+        uint32_t d = (uint32_t) mi << 29;
+        if (legacy) {
+            if (mi != 0 && in_nuc && present[code]) d |= 8u << (4 * code); else d |= PGI_DESC_MAIN_ZERO;
+        } else {
+            if (present[code]) d |= 8u << (4 * code); else d |= PGI_DESC_MAIN_ZERO;
+        }
+        k.desc_c[a] = d;
+    }
 }
 
 // ---------------------------------------------------------------------------------- .ri

@@ -65,7 +65,13 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
 }
 
-template <int MODE, int THREADS, int BPS>
+//
+// OP 1 turns the same kernel into the whole-read backward search of the query_tags path (FastLocate::count_encoded /
+// count, r-index.hpp:541-556; src/query_tags.cpp:87-109): every trip is one LF step = the k / s half of a backward
+// extension with the count descriptors (a.desc = the desc_c bank), a lane is done when its read is used up or the range
+// became empty, and its record {0, len, range.first, size} (empty range: bwt_start 1, size 0 = the reference's {1,0})
+// goes to mem_buf[read] directly: one record per read, already in read order.
+template <int MODE, int THREADS, int BPS, int OP = 0>
 __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
     __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
@@ -103,7 +109,12 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     rd = id; have = true; nm = 0;
                     const uint64_t o0 = __ldcs(a.read_off + id), o1 = __ldcs(a.read_off + id + 1);
                     base = o0;
-                    lane_begin(L, o1 - o0, min_len, a.ix.n);
+                    if (OP == 0) lane_begin(L, o1 - o0, min_len, a.ix.n);
+                    else {
+                        L.len = (uint32_t) (o1 - o0 < PGI_MAX_READ_LEN ? o1 - o0 : PGI_MAX_READ_LEN);
+                        L.x = 0; L.j = L.len - 1u; L.phase = PH_P1;                      // range = {0, n - 1}; walk i = len .. 1
+                        L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) a.ix.n;
+                    }
                     const char *rp = reinterpret_cast<const char *>(a.reads64) + base;      // pull the read towards L2
                     for (uint32_t o = 0; o < L.len && o < 512; o += 128) prefetch_l2(rp + o);
                 }
@@ -113,7 +124,16 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         }
         // ---- run to the next extension, writing out MEMs on the way
         bool need = false;
-        if (have) {
+        if (have && OP == 1) {
+            need = L.phase == PH_P1 && (int32_t) L.j >= 0;
+            if (!need) {
+                const bool hit = L.phase == PH_P1;
+                const uint64_t k = hit ? L.b.k : 1ull, sz = hit ? (uint64_t) L.b.s : 0ull;
+                __stcs(a.mem_buf + 2 * (uint64_t) rd, make_uint4(0u, 0u, L.len, 0u));
+                __stcs(a.mem_buf + 2 * (uint64_t) rd + 1, make_uint4((uint32_t) k, (uint32_t) (k >> 32), (uint32_t) sz, (uint32_t) (sz >> 32)));
+                have = false;
+            }
+        } else if (have) {
             int st;
             while ((st = lane_settle(L, min_len, a.ix.n)) == LANE_EMIT) {
                 const unsigned long long slot = atomicAdd(a.mem_count, 1ull);
@@ -133,7 +153,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         // forward extension = backward extension of the swapped interval with the complement's descriptor
         // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
         uint32_t sym = 0;
-        const bool fwd = L.phase == PH_P2;
+        const bool fwd = OP == 0 && L.phase == PH_P2;
         if (need && L.j < L.len) {
             const uint64_t o = base + L.j;
             if ((o >> 3) != cwi) {
@@ -148,7 +168,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
                 ++n_ext;
-                lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
+                if (OP == 0) lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
+                else if (ext_failed(u, 0)) L.phase = PH_DONE;                            // LF returned {1, 0}: stays empty
+                else { L.b = u; --L.j; }
             }
         } else {
             // (1) every lane with work resolves its two block indices from the directory
@@ -203,7 +225,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 t = extend_finish(a.ix, t, d, r1, r2, p1, p2);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
                 ++n_ext;
-                lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
+                if (OP == 0) lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
+                else if (ext_failed(u, 0)) L.phase = PH_DONE;                            // LF returned {1, 0}: stays empty
+                else { L.b = u; --L.j; }
             }
             __syncwarp();                                     // the staging area is rewritten by the next trip
         }

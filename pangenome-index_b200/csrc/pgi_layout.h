@@ -68,6 +68,13 @@ typedef struct {
     uint64_t C[8];
     uint8_t sym_map[256];
     uint32_t desc_b[256], desc_f[256];
+    // Whole-read backward search (FastLocate::count_encoded / count -> LF_encoded / LF -> rankAt_encoded / rankAt,
+    // r-index.hpp:541-556, r-index.cpp:558-590,650-711): one LF step is the k / s half of a backward extension whose
+    // "main" rank is the TRUE rank of the byte itself (no rank-vector slot aliasing), so it reuses the same descriptor
+    // format with all weights zero. count_ok = 0: encoded file without N, on which the reference reads a run header as
+    // a sixth cumulative (r-index.cpp:577) -- not reproduced, the count entry points refuse such an index.
+    uint32_t desc_c[256];
+    uint32_t count_ok, pad2_;
 } RiConsts;
 
 // Sorted set S of positions in [0,size): rank1(i) = |{p in S : p < i}|.

@@ -19,6 +19,7 @@ __global__ void tag_plan_kernel(TagDev t, uint64_t n, const uint4 *mems, const u
         s = r.x | ((uint64_t) r.y << 32);
         e = s + (r.z | ((uint64_t) r.w << 32)) - 1;
     } else { s = start[i]; e = end[i]; }
+    if (mems && e + 1 == s) { n_runs[i] = 0; cnt[i] = 0; first_item[i] = 0; skip[i] = 0; return; }   // size 0: a query_tags read without a match is not queried (src/query_tags.cpp:97-100); MEMs always have size > 0
     const TagPlan p = tag_plan(t, s, e);
     n_runs[i] = p.n_runs; cnt[i] = p.count; first_item[i] = p.first_item; skip[i] = (uint32_t) p.skip;
 }

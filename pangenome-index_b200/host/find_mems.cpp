@@ -8,6 +8,11 @@
 // copies of one overlap the kernels of the other), every batch goes through ONE pgi_find_mems call (MEMs + tags), the
 // text of src/find_mems.cpp:115-139 / src/tag_arrays.cpp:885-889 is produced by pgi_format_text and written in read
 // order. Sequence numbers count non-empty lines from 1, like the reference's `i`. No CPU query path exists here.
+//
+// Compiled with -DPGI_QUERY_TAGS the same driver is `query_tags <r_index.ri> <tags> <reads.txt> [options]`, replacing
+// src/query_tags.cpp:39-112: every batch goes through pgi_query_tags (whole-read count_encoded / count + the tag query
+// of the final range) and the text is that of src/query_tags.cpp:103-108 preceded by the two lines
+// query_compressed_compact prints itself; read_index counts non-empty lines from 0 (readSequencesFromFile :27-37).
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -71,14 +76,24 @@ std::string slurp_file(const std::string &path, const char *what) {
 } // namespace
 
 int main(int argc, char **argv) {
-    if (argc < 6) {
+#ifdef PGI_QUERY_TAGS
+    const int n_fixed = 4;
+    if (argc < n_fixed) {
+        std::fprintf(stderr, "Usage: %s <r_index.ri> <compressed_tags.tags> <reads.txt> [--gpus N] [--batch READS] [--tags-layout auto|compact|bytecode] [--no-text]\n", argv[0]);
+        return 1;
+    }
+    const uint64_t mem_length = 0, min_occ = 0;
+#else
+    const int n_fixed = 6;
+    if (argc < n_fixed) {
         std::fprintf(stderr, "usage: %s <r_index.ri> <tags> <reads.txt> <min_mem_length> <min_occ> [--gpus N] [--batch READS] [--tags-layout auto|compact|bytecode] [--no-text]\n", argv[0]);
         return EXIT_FAILURE;
     }
-    const std::string r_index_file = argv[1], tag_array_index = argv[2], reads_file = argv[3];
     const uint64_t mem_length = (uint64_t) std::stoi(argv[4]), min_occ = (uint64_t) std::stoi(argv[5]);   // src/find_mems.cpp:17-18
+#endif
+    const std::string r_index_file = argv[1], tag_array_index = argv[2], reads_file = argv[3];
     int gpus = 1; uint64_t batch_reads = 1u << 20; std::string layout = "auto"; bool text = true;
-    for (int i = 6; i < argc; ++i) {
+    for (int i = n_fixed; i < argc; ++i) {
         std::string a = argv[i];
         if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);
         else if (a == "--batch" && i + 1 < argc) batch_reads = std::strtoull(argv[++i], nullptr, 10);
@@ -153,12 +168,22 @@ int main(int argc, char **argv) {
         pgi_index *my = ix[w % gpus]; Batch *b;
         while (work_q.pop(b)) {
             pgi_result r; auto t0 = clk::now();
-            if (pgi_find_mems(my, b->reads, b->off, b->n, mem_length, min_occ, nullptr, &r) != PGI_OK) {
+#ifdef PGI_QUERY_TAGS
+            const int rc = pgi_query_tags(my, b->reads, b->off, b->n, nullptr, &r);
+#else
+            const int rc = pgi_find_mems(my, b->reads, b->off, b->n, mem_length, min_occ, nullptr, &r);
+#endif
+            if (rc != PGI_OK) {
                 std::fprintf(stderr, "find_mems: batch %llu failed: %s\n", (unsigned long long) b->id, pgi_last_error());
                 failed = true; out_cv.notify_all(); free_q.push(b); continue;
             }
             const double dt = std::chrono::duration<double>(clk::now() - t0).count();
-            uint64_t len = 0; char *txt = text ? pgi_format_text(&r, b->first_seq, 1, &len) : nullptr;
+            uint64_t len = 0;
+#ifdef PGI_QUERY_TAGS
+            char *txt = text ? pgi_format_query_tags_text(&r, b->first_seq - 1, &len) : nullptr;
+#else
+            char *txt = text ? pgi_format_text(&r, b->first_seq, 1, &len) : nullptr;
+#endif
             { std::lock_guard<std::mutex> l(stat_mu); gpu_seconds += dt; total_reads += r.n_reads; total_mems += r.n_mems; total_tags += r.n_tags; }
             pgi_result_free(&r);
             const uint64_t id = b->id;
@@ -186,8 +211,13 @@ int main(int argc, char **argv) {
     std::fclose(rf);
     const double wall = std::chrono::duration<double>(clk::now() - t_run).count();
     if (failed) return EXIT_FAILURE;
+#ifndef PGI_QUERY_TAGS
     // src/find_mems.cpp:143-146 (values are not comparable: MEM finding and tag lookup are one fused GPU pass here)
     std::printf("\nTotal time for finding all MEMs: %g seconds\nTotal time for all tag queries: %g seconds\n", gpu_seconds, 0.0);
+#else
+    (void) mem_length; (void) min_occ; (void) gpu_seconds;
+    if (total_reads == 0) { std::cerr << "No reads found in file." << std::endl; return 1; }     // src/query_tags.cpp:82-85
+#endif
     std::fflush(stdout);
     std::cerr << "[find_mems] " << total_reads << " reads, " << total_mems << " MEMs, " << total_tags << " tags on " << gpus << " GPU(s) in " << wall
               << " s (" << (wall > 0 ? total_reads / wall : 0) << " reads/s including parsing and text output)" << std::endl;

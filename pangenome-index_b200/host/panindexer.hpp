@@ -6,6 +6,7 @@
 //   panindexer::FastLocate            include/pangenome_index/r-index.hpp:44-714   (query side only)
 //     load / load_encoded             src/r-index.cpp:378-459
 //     backward/forward_extend[_encoded]   src/r-index.cpp:713-764, 1395-1428, 1500-1509
+//     count / count_encoded           include/pangenome_index/r-index.hpp:541-556 (LF / LF_encoded src/r-index.cpp:650-711)
 //     bwt_size, is_encoded, complement, sym_map, C
 //   panindexer::TagArray              include/pangenome_index/tag_arrays.hpp:27-128 (query side only)
 //     load_compressed_tags[_compact]  src/tag_arrays.cpp:739-776
@@ -25,6 +26,7 @@
 #include <iterator>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 #include "../../include/pgi.h"
 
@@ -68,6 +70,21 @@ public:
     bi_interval forward_extend_encoded(const bi_interval &bint, size_t symbol) { return extend(bint, symbol, 1); }
     bi_interval backward_extend(const bi_interval &bint, size_t symbol) { return extend(bint, symbol, 0); }
     bi_interval forward_extend(const bi_interval &bint, size_t symbol) { return extend(bint, symbol, 1); }
+
+    // Whole-read backward search, r-index.hpp:541-556: {first, second} of gbwt::range_type; no match = {1, 0}.
+    // (count and count_encoded resolve to the same call: the library follows the file's own layout, as
+    // src/query_tags.cpp:90-96 does by hand.)
+    typedef std::pair<size_t, size_t> range_type;
+    range_type count_encoded(std::string &pattern) const {
+        if (!ix_) throw std::runtime_error("FastLocate: no index loaded");
+        const uint64_t off[2] = {0, (uint64_t) pattern.size()};
+        pgi_result r;
+        pgi_check(pgi_query_tags(ix_, pattern.data(), off, 1, nullptr, &r));
+        range_type out((size_t) r.mems[0].bwt_start, (size_t) (r.mems[0].bwt_start + (uint64_t) r.mems[0].size - 1));
+        pgi_result_free(&r);
+        return out;
+    }
+    range_type count(std::string &pattern) const { return count_encoded(pattern); }
 
     pgi_index *handle() const { return ix_; }
     const std::string &file_bytes() const { return bytes_; }

@@ -51,10 +51,10 @@ def synth_haplotypes(ref_len, n_hap, seed, snp=1 / 200, indel=1 / 1000, n_N=2):
     return haps, maps
 
 @functools.lru_cache(maxsize=None)
-def synth_index(ref_len=3000, n_hap=4, seed=7, encoded=True):
+def synth_index(ref_len=3000, n_hap=4, seed=7, encoded=True, n_N=2):
     """-> dict(text, ri, tags0 (sdsl-compact), tags1 (ByteCode+len9), info)."""
     prep = load_package().prep
-    haps, maps = synth_haplotypes(ref_len, n_hap, seed)
+    haps, maps = synth_haplotypes(ref_len, n_hap, seed, n_N=n_N)
     seqs, smaps, srev = [], [], []
     for h, m in zip(haps, maps):
         seqs.append(h); smaps.append(m); srev.append(0)

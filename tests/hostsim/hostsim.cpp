@@ -79,6 +79,19 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
     if (n_ext) *n_ext = ext;
     return nm;
 }
+// Whole-read backward search through the count descriptors (desc_c) and extend_desc, as fmd_mem_kernel's OP 1 does:
+// out2 = {range.first, size} (no match: {1, 0}). Returns 0, or 1 when the index refuses counting (count_ok == 0).
+int sim_count(const sim_index *s, const char *read, uint64_t len, uint64_t *out2) {
+    if (!s->ri.k.count_ok) return 1;
+    BiInt b{0, 0, (int64_t) s->rd.n};
+    for (uint64_t i = len; i > 0; --i) {
+        const BiInt t = extend_desc(s->rd, b, s->ri.k.desc_c[(unsigned char) read[i - 1]]);
+        if (ext_failed(t, 0)) { out2[0] = 1; out2[1] = 0; return 0; }
+        b = t;
+    }
+    out2[0] = b.k; out2[1] = (uint64_t) b.s;
+    return 0;
+}
 // one tag query through tag_plan + item decoders; returns number_of_runs, *n_out sorted unique values written (<= cap)
 uint64_t sim_tag_query(const sim_index *s, uint64_t start, uint64_t end, uint64_t *out, uint64_t cap, uint64_t *n_out) {
     TagPlan p = tag_plan(s->td, start, end);

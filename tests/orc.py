@@ -32,6 +32,10 @@ def lib():
                                     ctypes.POINTER(ctypes.c_uint64)]
         L.orc_find_mems.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64,
                                     ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(OrcResult)]
+        L.orc_query_tags.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int, ctypes.c_int,
+                                     ctypes.POINTER(OrcResult)]
+        L.orc_format_query_tags.restype = ctypes.c_void_p
+        L.orc_format_query_tags.argtypes = [ctypes.POINTER(OrcResult), ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
         L.orc_result_free.argtypes = [ctypes.POINTER(OrcResult)]
         L.orc_format_text.restype = ctypes.c_void_p
         L.orc_format_text.argtypes = [ctypes.POINTER(OrcResult), ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
@@ -102,6 +106,27 @@ class Index:
             out["text"] = ctypes.string_at(p, ln.value); lib().orc_free(p)
         lib().orc_result_free(ctypes.byref(res))
         return out
+
+def _query_tags(self, reads, read_off, with_tags=None, threads=0, text=True):
+    """query_tags path (src/query_tags.cpp:87-109): one record per read {0, len, range.first, size}."""
+    reads = np.ascontiguousarray(reads, dtype=np.uint8); read_off = np.ascontiguousarray(read_off, dtype=np.uint64)
+    if with_tags is None:
+        with_tags = self.has_tags
+    import time
+    res = OrcResult(); t0 = time.perf_counter()
+    if lib().orc_query_tags(self.h, reads.ctypes.data, read_off.ctypes.data, len(read_off) - 1, int(with_tags), threads, ctypes.byref(res)):
+        raise RuntimeError(lib().orc_last_error().decode())
+    seconds = time.perf_counter() - t0
+    out = dict(seconds=seconds, n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags,
+               mem_off=_np(res.mem_off, res.n_reads + 1), mems=_np(res.mems, 4 * res.n_mems).reshape(-1, 4),
+               tag_off=_np(res.tag_off, res.n_mems + 1), tags=_np(res.tags, res.n_tags), n_runs=_np(res.n_runs, res.n_mems))
+    if text:
+        ln = ctypes.c_uint64()
+        p = lib().orc_format_query_tags(ctypes.byref(res), 0, ctypes.byref(ln))
+        out["text"] = ctypes.string_at(p, ln.value); lib().orc_free(p)
+    lib().orc_result_free(ctypes.byref(res))
+    return out
+Index.query_tags = _query_tags
 
 def pack_reads(reads):
     """list of bytes -> (uint8 concatenation, uint64 offsets)."""

@@ -22,6 +22,7 @@ def lib():
         L.sim_tag_query.restype = ctypes.c_uint64
         L.sim_tag_query.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64,
                                     ctypes.POINTER(ctypes.c_uint64)]
+        L.sim_count.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -50,6 +51,12 @@ class Index:
         out = np.zeros((cap, 4), dtype=np.uint64); ne = ctypes.c_uint64()
         n = lib().sim_find_mems(self.h, read, len(read), min_len, min_occ, out.ctypes.data, cap, ctypes.byref(ne))
         return out[:n].copy(), ne.value
+    def count(self, read: bytes):
+        """-> (range.first, size), (1, 0) without a match, or None when the index refuses counting."""
+        out = np.zeros(2, dtype=np.uint64)
+        if lib().sim_count(self.h, read, len(read), out.ctypes.data):
+            return None
+        return int(out[0]), int(out[1])
     def tag_query(self, start, end, cap=1 << 20):
         out = np.zeros(cap, dtype=np.uint64); n = ctypes.c_uint64()
         nr = lib().sim_tag_query(self.h, start, end, out.ctypes.data, cap, ctypes.byref(n))

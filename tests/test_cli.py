@@ -61,3 +61,28 @@ def test_cli_rejects_wrong_tag_layout(tmp_path):
     (tmp_path / "x.ri").write_bytes(s["ri"]); (tmp_path / "x.tags").write_bytes(s["tags0"]); (tmp_path / "r.txt").write_bytes(b"ACGT\n")
     p = subprocess.run([CLI, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "r.txt"), "2", "1", "--tags-layout", "bytecode"], capture_output=True)
     assert p.returncode != 0 and b"cannot load the index" in p.stderr
+
+@pytest.mark.gpu
+def test_query_tags_cli_stdout_equals_oracle(tmp_path):
+    """host/query_tags (the same driver built with -DPGI_QUERY_TAGS): stdout of src/query_tags.cpp:87-109, read_index
+    counting non-empty lines from 0; reads without a match print nothing on stdout."""
+    QT = os.path.join(HOST, "query_tags")
+    s = datasets.synth_index(); ri, tg, text = s["ri"], s["tags0"], s["text"]
+    rng = np.random.default_rng(4); lines = [l for l in text.split(b"\n") if len(l) > 100]; rs = []
+    for _ in range(700):
+        L = lines[int(rng.integers(len(lines)))]; ln = int(rng.integers(1, 90)); st = int(rng.integers(0, len(L) - ln))
+        r = bytearray(L[st:st + ln])
+        if rng.random() < 0.3: r[int(rng.integers(len(r)))] = b"ACGTNx"[int(rng.integers(6))]
+        rs.append(bytes(r))
+    (tmp_path / "x.ri").write_bytes(ri); (tmp_path / "x.tags").write_bytes(tg)
+    (tmp_path / "reads.txt").write_bytes(b"\n" + b"\n".join(rs[:5]) + b"\n\n\n" + b"\n".join(rs[5:]) + b"\n")
+    buf, o = orc.pack_reads(rs)
+    want = orc.Index(ri, tg, 0).query_tags(buf, o)["text"]
+    assert want.count(b"read_index=") > 300
+    for extra in ([], ["--batch", "53"]):
+        p = subprocess.run([QT, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "reads.txt")] + extra, capture_output=True)
+        assert p.returncode == 0, p.stderr.decode()
+        assert p.stdout == want, extra
+    (tmp_path / "empty.txt").write_bytes(b"\n\n")
+    p = subprocess.run([QT, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "empty.txt")], capture_output=True)
+    assert p.returncode == 1 and b"No reads found in file." in p.stderr

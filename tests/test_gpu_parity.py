@@ -177,3 +177,62 @@ def test_sharded_equals_unsharded(capi):
         for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(m[k], whole[k]), (world, k)
         assert m["extensions"] == whole["extensions"]
     assert sharding.find_mems_sharded(lambda *a: g.find_mems(*a, text=False), reads, off, 12, 1)["n_mems"] == whole["n_mems"]
+
+def query_reads(text, seed, n=3000):
+    """Reads for the whole-read search: substrings of every length (most match), a few with one changed base, edge cases."""
+    rng = np.random.default_rng(seed)
+    lines = [l for l in text.split(b"\n") if len(l) > 100]
+    rs = [b"", b"A", b"T", b"N", b"\n", b"a", b"ACGT", bytes([0, 200]), b"GATTACA"]
+    for _ in range(n):
+        L = lines[int(rng.integers(len(lines)))]; ln = int(rng.integers(1, 120)); st = int(rng.integers(0, len(L) - ln))
+        r = bytearray(L[st:st + ln])
+        if rng.random() < 0.3: r[int(rng.integers(len(r)))] = b"ACGTN\nx"[int(rng.integers(7))]
+        rs.append(bytes(r))
+    return rs
+
+def compare_query_tags(G, R, with_tags):
+    assert G["n_reads"] == R["n_reads"] and G["n_mems"] == R["n_mems"]
+    assert np.array_equal(G["mem_off"], R["mem_off"]) and np.array_equal(G["mems"], R["mems"])
+    if with_tags:
+        assert np.array_equal(G["n_runs"], R["n_runs"]) and np.array_equal(G["tag_off"], R["tag_off"]) and np.array_equal(G["tags"], R["tags"])
+        assert G["text"] == R["text"]
+
+@pytest.mark.parametrize("name", NAMES)
+def test_query_tags(capi, name):
+    """count_encoded / count + tag query of the final range (src/query_tags.cpp:87-109), bit-exact."""
+    c = get_case(name)
+    o = orc.Index(c["ri"], c["tags"], c["layout"]); g = capi.Index(c["ri"], c["tags"], c["layout"])
+    reads, off = orc.pack_reads(query_reads(c["text"], seed=17))
+    R = o.query_tags(reads, off); G = g.query_tags(reads, off)
+    compare_query_tags(G, R, c["tags"] is not None)
+    hit = R["mems"][:, 3] > 0
+    assert hit.sum() > 1000 and (~hit).sum() > 100
+    assert (R["mems"][~hit, 2] == 1).all()                         # the reference's empty range {1, 0}
+    assert G["extensions"] > 0
+    e = g.query_tags(np.zeros(0, dtype=np.uint8), np.zeros(1, dtype=np.uint64))     # empty batch
+    assert e["n_reads"] == 0 and e["n_mems"] == 0
+    b = capi.Batch(g)                                            # batch-context form
+    b.upload(reads.ctypes.data, off.ctypes.data, len(off) - 1); b.run_query_tags(); S = b.fetch()
+    for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(S[k], G[k]), k
+
+def test_query_tags_large_and_refusal(capi):
+    """Many reads against plain-text occurrence counts (size-independent property: interval size = number of
+    occurrences of the read in the text), the oracle on a slice, and the refusal on an encoded index without N."""
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    g = capi.Index(s["ri"], s["tags0"], 0); o = orc.Index(s["ri"], s["tags0"], 0)
+    reads, off = datasets.sample_reads(s["text"], 100000, 40, 0.01, seed=6)
+    G = g.query_tags(reads, off, text=False)
+    k = 4000
+    R = o.query_tags(reads[: k * 40], off[: k + 1], text=False)
+    assert np.array_equal(G["mems"][:k], R["mems"]) and np.array_equal(G["tags"][: R["n_tags"]], R["tags"])
+    text = s["text"]
+    for i in np.random.default_rng(1).integers(0, 100000, 300):
+        rd = reads[i * 40:(i + 1) * 40].tobytes(); cnt = 0; p = text.find(rd)
+        while p >= 0: cnt += 1; p = text.find(rd, p + 1)
+        assert int(G["mems"][i, 3]) == cnt, i
+    s5 = datasets.synth_index(ref_len=2000, n_hap=2, seed=3, encoded=True, n_N=0)       # sigma 5, encoded
+    g5 = capi.Index(s5["ri"])
+    with pytest.raises(capi.PgiError):
+        g5.query_tags(reads[:400], off[:11])
+    r5, o5 = datasets.sample_reads(s5["text"], 500, 150, 0.01, seed=2)                  # find_mems itself works on it
+    compare(g5.find_mems(r5, o5, 20, 1), orc.Index(s5["ri"]).find_mems(r5, o5, 20, 1), False)

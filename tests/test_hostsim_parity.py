@@ -72,3 +72,25 @@ def test_tag_plan_matches_oracle(name):
     for a in range(0, min(n, 1500)):                          # every alignment of the first % 10 rule
         nr, tv = o.tag_query(a, a + 2); nr2, tv2 = g.tag_query(a, a + 2)
         assert nr == nr2 and np.array_equal(tv, tv2), a
+
+@pytest.mark.parametrize("name", NAMES)
+def test_count_matches_oracle(name):
+    """query_tags path: whole-read LF chain (count descriptors) against the oracle's count_encoded / count restatement."""
+    c = case(name); o = orc.Index(c["ri"]); g = sim.Index(c["ri"])
+    rng = np.random.default_rng(5)
+    lines = [l for l in c["text"].split(b"\n") if len(l) > 100]
+    rs = [b"", b"A", b"T", b"N", b"\n", b"a", b"ACGT", bytes([0, 200]), b"GATTACA"]
+    for _ in range(400):
+        L = lines[int(rng.integers(len(lines)))]; ln = int(rng.integers(1, 60)); st = int(rng.integers(0, len(L) - ln))
+        r = bytearray(L[st:st + ln])
+        if rng.random() < 0.3: r[int(rng.integers(len(r)))] = b"ACGTN\nx"[int(rng.integers(7))]
+        rs.append(bytes(r))
+    buf, off = orc.pack_reads(rs)
+    R = o.query_tags(buf, off, with_tags=False, threads=1)
+    hits = 0
+    for i, rd in enumerate(rs):
+        got = g.count(rd)
+        assert got is not None
+        assert got == (int(R["mems"][i, 2]), int(R["mems"][i, 3])), (i, rd)
+        hits += got[1] > 0
+    assert hits > 100
