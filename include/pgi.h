@@ -68,11 +68,12 @@ typedef struct {
     uint64_t is_encoded;     /* file had ENCODED_BLOCKS (flag bit 0) */
     uint64_t n_ref_blocks;   /* ones in blocks_start_pos */
     uint64_t n_runs;         /* logical runs in the file */
-    uint64_t n_dev_blocks;   /* 64-byte device run blocks */
-    uint64_t dir_shift;      /* log2 of the positions covered by one block-directory bucket */
+    uint64_t n_dev_blocks;   /* 64-byte device run blocks (one per bucket of 2^bucket_shift BWT positions + chunk blocks) */
+    uint64_t bucket_shift;   /* log2 of the positions covered by one bucket = one 64-byte block */
     uint64_t has_quirk_slot; /* legacy file with an absent nuc symbol */
     uint64_t has_tags, tag_layout, tag_runs, tag_items, tag_item_width, tag_universe;
     uint64_t device_bytes;   /* bytes of HBM held by the index */
+    uint64_t n_crowded_buckets; /* buckets with more than 12 runs (directory block + chunk blocks: one more access) */
     uint64_t C[8];
     uint8_t  sym_map[256];
 } pgi_index_info_t;

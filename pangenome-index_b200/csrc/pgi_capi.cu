@@ -76,7 +76,7 @@ struct pgi_index {
     uint32_t *d_desc = nullptr, *d_desc_c = nullptr;      // extension descriptors; LF-step descriptors of the whole-read search
     std::vector<void *> owned;
     // sizes of the uploaded arrays, for clone
-    uint64_t n_block_words = 0, n_dir = 0, n_sb = 0, n_dense = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
+    uint64_t n_block_words = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
     std::mutex compute_mu;                                  // see pgi_find_mems
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
@@ -101,7 +101,7 @@ static int check_device(int device) {
 static void fill_info(pgi_index *ix, const RiImage &ri, const TagImage *tg, uint64_t bytes) {
     pgi_index_info_t &f = ix->info; std::memset(&f, 0, sizeof(f));
     f.n = ri.k.n; f.sigma = ri.k.sigma; f.is_encoded = ri.encoded; f.n_ref_blocks = ri.n_ref_blocks; f.n_runs = ri.n_file_runs;
-    f.n_dev_blocks = ri.k.n_blocks; f.dir_shift = ri.k.dir_shift; f.has_quirk_slot = ri.k.has_quirk;
+    f.n_dev_blocks = ri.k.n_blocks; f.bucket_shift = ri.k.bshift; f.n_crowded_buckets = ri.k.n_dir_blocks; f.has_quirk_slot = ri.k.has_quirk;
     if (tg) {
         f.has_tags = 1; f.tag_layout = (uint64_t) tg->layout; f.tag_runs = tg->intervals.k.m; f.tag_items = tg->n_items;
         f.tag_item_width = tg->width; f.tag_universe = tg->intervals.k.size;
@@ -127,11 +127,8 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
         uint64_t bytes = 0;
         RiDev &d = ix->ri;
         d.blocks = upload(ri.blocks, ix->owned, bytes); ix->n_block_words = ri.blocks.size();
-        d.dir = upload(ri.dir, ix->owned, bytes); ix->n_dir = ri.dir.size();
-        d.sb = upload(ri.sb, ix->owned, bytes); ix->n_sb = ri.sb.size();
-        d.dense = upload(ri.dense, ix->owned, bytes); ix->n_dense = ri.dense.size();
         d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
-        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.dir_shift = ri.k.dir_shift; d.has_quirk = ri.k.has_quirk; d.sb_shift = ri.k.sb_shift; d.pad_ = 0;
+        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.bshift = ri.k.bshift; d.has_quirk = ri.k.has_quirk;
         for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
         std::vector<uint32_t> desc(PGI_DESC_WORDS);      // 512 descriptors, then their 512 x 4 scan tables (pos_rank)
         for (int i = 0; i < 256; ++i) { desc[i] = ri.k.desc_b[i]; desc[256 + i] = ri.k.desc_f[i]; }
@@ -191,13 +188,10 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags; ix->has_ri = src->has_ri;
-        ix->n_block_words = src->n_block_words; ix->n_dir = src->n_dir; ix->n_sb = src->n_sb; ix->n_dense = src->n_dense; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
+        ix->n_block_words = src->n_block_words; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
         ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
         const int sd = src->device;
         ix->ri.blocks = clone_arr(src->ri.blocks, sd, src->n_block_words, device, ix->owned);
-        ix->ri.dir = clone_arr(src->ri.dir, sd, src->n_dir, device, ix->owned);
-        ix->ri.sb = clone_arr(src->ri.sb, sd, src->n_sb, device, ix->owned);
-        ix->ri.dense = clone_arr(src->ri.dense, sd, src->n_dense, device, ix->owned);
         ix->ri.q_start = clone_arr(src->ri.q_start, sd, src->n_quirk, device, ix->owned);
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);

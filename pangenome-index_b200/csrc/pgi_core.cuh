@@ -24,14 +24,11 @@ namespace pgi {
 
 // Device view of the flattened r-index.
 struct RiDev {
-    const uint64_t *blocks;     // 8 words per run block, 64-byte aligned
-    const uint32_t *dir;        // block directory, per bucket of 2^dir_shift positions (pgi_layout.h)
-    const uint32_t *sb;         // block index at every superbucket start
-    const uint32_t *dense;      // records of the dense buckets (pgi_layout.h)
+    const uint64_t *blocks;     // 8 words per 64-byte block: block b = bucket b = positions [b << bshift, (b + 1) << bshift), then chunks
     const uint64_t *q_start;    // quirk tables (n_quirk entries) or nullptr
     const uint64_t *q_val;
     uint64_t n, n_blocks, n_quirk;
-    uint32_t dir_shift, has_quirk, sb_shift, pad_;
+    uint32_t bshift, has_quirk;
     uint64_t C[8];
 };
 
@@ -68,54 +65,12 @@ PGI_HD void ld_block(const uint64_t *blk, uint32_t w[16]) {
     for (int i = 0; i < 8; ++i) { w[2 * i] = (uint32_t) blk[i]; w[2 * i + 1] = (uint32_t) (blk[i] >> 32); }
 #endif
 }
-PGI_HD uint64_t block_start(const uint32_t w[16]) { return (uint64_t) w[0] | (uint64_t) (w[7] & 0xFFu) << 32; }
-PGI_HD uint64_t block_start_at(const uint64_t *blocks, uint64_t idx) {      // start of block idx, from memory
-    const uint64_t a = ld64(blocks + idx * PGI_BLOCK_WORDS), b = ld64(blocks + idx * PGI_BLOCK_WORDS + 3);
-    return (a & 0xFFFFFFFFull) | ((b >> 32) & 0xFFull) << 32;
-}
-
-// ------------------------------------------------------------------------------------ block locate
-// Replaces blocks_start_pos.predecessor(pos) (src/r-index.cpp:594,621; SDSL: 2-3 dependent cache lines).
 PGI_HD uint32_t ld32(const uint32_t *p) {
 #if defined(__CUDA_ARCH__)
     return __ldg(p);
 #else
     return *p;
 #endif
-}
-// Block guess from the two directory words of pos: exact unless the bucket is one of the (never seen) dense buckets
-// beyond the 65535 that have a record, in which case the guess is SHORT (start(guess) <= pos always holds).
-PGI_HD uint64_t locate_guess(const RiDev &ix, uint64_t pos, uint32_t e, uint32_t base) {
-    const uint32_t rel = (uint32_t) pos & ((1u << ix.dir_shift) - 1u);
-    if ((e & 0xFFFFu) == 0xFFFFu) {                                       // dense bucket: count the boundaries at or before rel
-        const uint32_t *rec = ix.dense + (uint64_t) (e >> 16) * PGI_DENSE_U32;
-        uint32_t cnt = 0;
-        for (uint32_t i = 1; i < PGI_DENSE_U32; ++i) {
-            const uint32_t x = ld32(rec + i);
-            const uint32_t c = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
-            cnt += c;
-            if (c < 4u) break;                                            // ascending: nothing further can count
-        }
-        return (uint64_t) ld32(rec) + cnt;
-    }
-    const uint32_t t1 = (e >> 16) & 0xFFu, t2 = e >> 24;                 // 0 = no boundary: (0 - 1) < rel is false
-    return (uint64_t) base + (e & 0xFFFFu) + ((t1 - 1u) < rel) + ((t2 - 1u) < rel);
-}
-// Index of the run block containing pos: last block whose start <= pos. Slow path and non-hot callers.
-PGI_HD uint64_t locate_block(const RiDev &ix, uint64_t pos) {
-    const uint64_t b = pos >> ix.dir_shift;
-    uint64_t lo = locate_guess(ix, pos, ld32(ix.dir + b), ld32(ix.sb + (pos >> ix.sb_shift)));
-    uint64_t s1 = ((b + 1) << ix.dir_shift) >> ix.sb_shift; const uint64_t smax = ix.n >> ix.sb_shift;
-    if (s1 > smax) s1 = smax;                                             // the flattener clamps the same way
-    const uint32_t en = ld32(ix.dir + b + 1);
-    uint64_t up = (en & 0xFFFFu) == 0xFFFFu ? (uint64_t) ld32(ix.dense + (uint64_t) (en >> 16) * PGI_DENSE_U32)
-                                            : (uint64_t) ld32(ix.sb + s1) + (en & 0xFFFFu);      // block at the next bucket start
-    if (up >= ix.n_blocks) up = ix.n_blocks - 1;
-    while (lo < up) {                                                     // invariant: start(lo) <= pos
-        const uint64_t mid = (lo + up + 1) >> 1;
-        if (block_start_at(ix.blocks, mid) <= pos) lo = mid; else up = mid - 1;
-    }
-    return lo;
 }
 
 // ------------------------------------------------------------------------------------ in-block rank
@@ -171,12 +126,11 @@ PGI_HD ScanTab scan_tab(uint32_t tbl) {
 //     sum_i m_i * weight(c_i)  -  sum_i m_i * weight(c_{i+1})          (weight(c_12) = 0)
 // : per four runs two 16x2 mins, four PRMT table lookups (codes and next codes as selectors; weights and main flags) and
 // eight dp2a. No dependent chain over the runs, no per-run shifts and masks.
-struct PosRank { uint64_t W, M; uint32_t left; };   // left: positions of pos beyond the end of the block (0 when the block is the right one)
+struct PosRank { uint64_t W, M; };
 
-PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl, const ScanTab &T) {
-    const uint64_t d = pos - block_start(w);
-    const uint32_t r = d > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t) d;
-    const uint32_t rr = (r < 0xFFFFu ? r : 0xFFFFu) * 0x10001u;
+// rel = offset of the position inside its bucket (< 2^bshift <= 256)
+PGI_HD PosRank pos_rank(const uint32_t w[16], uint32_t rel, uint32_t tbl, const ScanTab &T) {
+    const uint32_t rr = rel * 0x10001u;
     const uint32_t c0 = w[9], c1 = w[8] >> 16;                          // codes 0..7, 8..11
     const uint32_t n0 = c0 >> 4 | c1 << 28, n1 = c1 >> 4 | 0x7000u;     // next codes; behind the last run: unused (weight 0)
     uint32_t aw = 0, an = 0, fw = 0, fn = 0, m1 = 0;
@@ -200,28 +154,42 @@ PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl, const 
     PosRank o;
     o.W = Wl + ((uint64_t) Wh << 32) + (uint64_t) (aw - an);
     o.M = Ml + ((uint64_t) Mh << 32) + (uint64_t) (fw - fn);
-    o.left = r - (m1 >> 16);                                          // m_11 = min(rel, length of the block)
     return o;
 }
-PGI_HD PosRank pos_rank(const uint32_t w[16], uint64_t pos, uint32_t tbl) { return pos_rank(w, pos, tbl, scan_tab(tbl)); }
+PGI_HD bool is_dir_block(const uint32_t w[16]) { return (w[9] & 0xFu) == PGI_CODE_DIRBLOCK; }
 
-// Exact but slow: search the block, then rank (the fallback of extend_desc; batched rank API).
+// Crowded bucket (pgi_layout.h): w is its directory block; pick the chunk containing rel and rank there. One more
+// dependent 64-byte access; rare by the choice of bshift.
 #if defined(__CUDA_ARCH__)
 __device__ __noinline__
 #else
 inline
 #endif
-PosRank rank_slow(const RiDev &ix, uint64_t pos, uint32_t tbl) {
+PosRank rank_in_chunk(const RiDev &ix, const uint32_t w[16], uint32_t rel, uint32_t tbl) {
+    uint32_t j = 0;
+#pragma unroll 1
+    for (int i = 10; i < 16; ++i) {
+        const uint32_t x = w[i];
+        const uint32_t c = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
+        j += c;                                                          // boundary b (> 0) counts when b <= rel; 0 = unused never counts
+        if (c < 4u) break;                                               // ascending
+    }
+    uint32_t v[16];
+    ld_block(ix.blocks + ((uint64_t) w[0] + j) * PGI_BLOCK_WORDS, v);
+    return pos_rank(v, rel, tbl, scan_tab(tbl));
+}
+// Rank of one position from memory (batched rank API, lane-private fetch mode, hostsim).
+PGI_HD PosRank rank_pos(const RiDev &ix, uint64_t pos, uint32_t tbl) {
     uint32_t w[16];
-    ld_block(ix.blocks + locate_block(ix, pos) * PGI_BLOCK_WORDS, w);
-    return pos_rank(w, pos, tbl);
+    ld_block(ix.blocks + (pos >> ix.bshift) * PGI_BLOCK_WORDS, w);
+    const uint32_t rel = (uint32_t) pos & ((1u << ix.bshift) - 1u);
+    if (rel && is_dir_block(w)) return rank_in_chunk(ix, w, rel, tbl);
+    return pos_rank(w, rel, tbl, scan_tab(tbl));     // offset 0 of a crowded bucket: the directory block's header is the answer
 }
 // True ranks of the six nuc codes at pos (batched rank API and tests; not on the MEM path).
 PGI_HD void rank_all(const RiDev &ix, uint64_t pos, uint64_t tr[6]) {
-    uint32_t w[16];
-    ld_block(ix.blocks + locate_block(ix, pos) * PGI_BLOCK_WORDS, w);
-#pragma unroll
-    for (int c = 0; c < 6; ++c) tr[c] = pos_rank(w, pos, 8u << (4 * c)).M;
+#pragma unroll 1
+    for (int c = 0; c < 6; ++c) tr[c] = rank_pos(ix, pos, 8u << (4 * c)).M;
 }
 
 // Quirk slot value Q(pos): column-0 cumulative of the reference's own 10-run block containing pos
@@ -260,34 +228,19 @@ PGI_HD BiInt extend_finish(const RiDev &ix, const BiInt &in, uint32_t d, const P
 // One backward extension with the per-byte descriptor d (desc_b[a]); forward extension = the same on
 // the swapped interval with desc_f[a] (src/r-index.cpp:758-764). All arithmetic mod 2^64, like the
 // reference's size_t. Positions beyond n read as n (defined UB).
-// Both positions (k and k+s) go through the same straight-line code, whether or not they share a block: the
-// 32 lanes of a warp stay converged, and both directory words and both blocks are requested before any is used.
+// Both positions (k and k+s) go through the same straight-line code, whether or not they share a bucket.
 PGI_HD BiInt extend_desc(const RiDev &ix, BiInt in, uint32_t d) {
     uint64_t p2 = in.k + (uint64_t) in.s, p1 = in.k;
     if (p2 > ix.n) p2 = ix.n;
     if (p1 > ix.n) p1 = ix.n;
-    // Every lane touches its own cache lines, so the L1 data pipe pays one wavefront per lane per load: a load whose
-    // address repeats the previous one (k and k+s in the same bucket / block: the common case once the interval is short)
-    // is predicated off and its value copied instead.
-    const uint64_t g1 = p1 >> ix.dir_shift, g2 = p2 >> ix.dir_shift, h1 = p1 >> ix.sb_shift, h2 = p2 >> ix.sb_shift;
-    const uint32_t e1 = ld32(ix.dir + g1), s1 = ld32(ix.sb + h1);
-    uint32_t e2 = e1, s2 = s1;
-    if (g2 != g1) e2 = ld32(ix.dir + g2);
-    if (h2 != h1) s2 = ld32(ix.sb + h2);
-    const uint64_t b1 = locate_guess(ix, p1, e1, s1), b2 = locate_guess(ix, p2, e2, s2);
-    uint32_t w[16], v[16];
+    const uint32_t tbl = d & 0xFFFFFFu, mask = (1u << ix.bshift) - 1u;
+    const uint64_t b1 = p1 >> ix.bshift, b2 = p2 >> ix.bshift;
+    const ScanTab T = scan_tab(tbl);
+    uint32_t w[16];
     ld_block(ix.blocks + b1 * PGI_BLOCK_WORDS, w);
-    if (b2 != b1) ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, v);
-    else {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = w[i];
-    }
-    const uint32_t tbl = d & 0xFFFFFFu;
-    PosRank r1 = pos_rank(w, p1, tbl), r2 = pos_rank(v, p2, tbl);
-    if (r1.left | r2.left) {                          // rare: a guess landed short (bucket with more than two boundaries)
-        if (r1.left) r1 = rank_slow(ix, p1, tbl);
-        if (r2.left) r2 = rank_slow(ix, p2, tbl);
-    }
+    PosRank r1 = (((uint32_t) p1 & mask) && is_dir_block(w)) ? rank_in_chunk(ix, w, (uint32_t) p1 & mask, tbl) : pos_rank(w, (uint32_t) p1 & mask, tbl, T);
+    if (b2 != b1) ld_block(ix.blocks + b2 * PGI_BLOCK_WORDS, w);        // k and k+s in one bucket (the common case once the interval is short): no second load
+    PosRank r2 = (((uint32_t) p2 & mask) && is_dir_block(w)) ? rank_in_chunk(ix, w, (uint32_t) p2 & mask, tbl) : pos_rank(w, (uint32_t) p2 & mask, tbl, T);
     return extend_finish(ix, in, d, r1, r2, p1, p2);
 }
 

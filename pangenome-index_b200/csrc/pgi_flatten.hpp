@@ -14,6 +14,7 @@
 // uploads; all query arithmetic is in pgi_core.cuh and runs on the GPU.
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -110,9 +111,7 @@ inline uint64_t bytecode_next(const uint8_t *&p, const uint8_t *end) {
 // ---------------------------------------------------------------------------------- flat images
 struct RiImage {
     RiConsts k;                          // scalars + tables copied to the device as one struct
-    std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte run block
-    std::vector<uint32_t> dir, sb;       // two-level block directory (pgi_layout.h)
-    std::vector<uint32_t> dense;         // records of the dense buckets (PGI_DENSE_U32 words each)
+    std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte block: one per bucket, then the chunk blocks
     std::vector<uint64_t> q_start, q_val;// quirk slot tables (legacy files with an absent nuc symbol)
     uint64_t n_file_runs = 0, n_ref_blocks = 0; bool encoded = false;
 };
@@ -131,108 +130,120 @@ struct TagImage {
 static const unsigned char kNuc[6] = {'\n', 'A', 'C', 'G', 'N', 'T'};   // include/pangenome_index/utils.hpp:11
 
 // ---------------------------------------------------------------------------------- run blocks
-// Packs (code, length) runs into 64-byte device blocks of PGI_RUNS_PER_BLOCK entries (pgi_layout.h).
-class BlockBuilder {
+// Collects the (code, length) runs of the file (adjacent runs of one symbol merged), 4 bytes per run.
+class RunCollector {
 public:
-    explicit BlockBuilder(std::vector<uint64_t> &out) : out_(out) {}
-    uint64_t cum[6] = {0, 0, 0, 0, 0, 0}; uint64_t pos = 0;      // state of the emitted entries
-    uint64_t lcum[6] = {0, 0, 0, 0, 0, 0}; uint64_t lpos = 0;    // state of the runs added so far
-    std::vector<uint64_t> starts;        // start position of every emitted block
+    std::vector<uint32_t> runs;          // code | length << 3, length < 2^29 (longer runs are split)
+    uint64_t lcum[6] = {0, 0, 0, 0, 0, 0}; uint64_t lpos = 0;    // counts / positions of the runs added so far
     void add(unsigned code, uint64_t len) {
         if (!len) return;
         lcum[code] += len; lpos += len;
         if (code == pcode_) { plen_ += len; return; }
-        flush_pending(); pcode_ = code; plen_ = len;
+        flush(); pcode_ = code; plen_ = len;
     }
-    void finish() { flush_pending(); if (ne_) emit(); }
+    void finish() { flush(); pcode_ = 8; }
 private:
-    std::vector<uint64_t> &out_; unsigned pcode_ = 8; uint64_t plen_ = 0;
-    uint64_t bstart_ = 0, bcum_[6]; uint32_t code_[PGI_RUNS_PER_BLOCK], end_[PGI_RUNS_PER_BLOCK]; unsigned ne_ = 0;
-    void flush_pending() {
-        while (plen_) {
-            uint64_t t = plen_ < PGI_MAX_RUN_ENTRY ? plen_ : PGI_MAX_RUN_ENTRY;
-            if (!ne_) { bstart_ = pos; std::memcpy(bcum_, cum, sizeof(cum)); }
-            code_[ne_] = pcode_; end_[ne_] = (uint32_t) (pos + t - bstart_); ++ne_;
-            cum[pcode_] += t; pos += t; plen_ -= t;
-            if (ne_ == PGI_RUNS_PER_BLOCK) emit();
-        }
-    }
-    void emit() {
-        if (bstart_ >> 40 || bcum_[1] >> 40 || bcum_[2] >> 40 || bcum_[3] >> 40 || bcum_[5] >> 40)
-            throw FormatError("index longer than 2^40 positions is not supported by the device layout");
-        if (bcum_[0] >> 32 || bcum_[4] >> 32)
-            throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
-        const uint64_t A = bcum_[1], C = bcum_[2], G = bcum_[3], T = bcum_[5], NL = bcum_[0], N = bcum_[4];
-        uint32_t w[PGI_BLOCK_U32];
-        w[0] = (uint32_t) bstart_; w[1] = (uint32_t) A; w[2] = (uint32_t) C; w[3] = (uint32_t) G; w[4] = (uint32_t) T;
-        w[5] = (uint32_t) NL; w[6] = (uint32_t) N;
-        w[7] = (uint32_t) (bstart_ >> 32) | (uint32_t) (A >> 32) << 8 | (uint32_t) (C >> 32) << 16 | (uint32_t) (G >> 32) << 24;
-        uint64_t codes = 0;
-        for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) codes |= (uint64_t) (i < ne_ ? code_[i] : PGI_CODE_UNUSED) << (4 * i);
-        auto end = [&](unsigned i) -> uint32_t { return end_[i < ne_ ? i : ne_ - 1]; };     // unused runs repeat the last end offset
-        w[8] = (uint32_t) (T >> 32) | (uint32_t) (codes >> 32) << 16;
-        w[9] = (uint32_t) codes;
-        for (unsigned j = 0; j < 6; ++j) w[10 + j] = end(2 * j) | end(2 * j + 1) << 16;
-        for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) out_.push_back((uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32);
-        starts.push_back(bstart_);
-        ne_ = 0;
+    unsigned pcode_ = 8; uint64_t plen_ = 0;
+    void flush() {
+        const uint64_t M = (1ull << 29) - 1;
+        while (plen_) { const uint64_t t = plen_ < M ? plen_ : M; runs.push_back((uint32_t) (pcode_ | t << 3)); plen_ -= t; }
     }
 };
 
-inline void build_block_dir(RiImage &im, const std::vector<uint64_t> &starts, uint64_t n) {
-    const uint64_t nb = starts.size();
-    if (nb == 0) throw FormatError("r-index has no runs");
-    if (nb >> 30) throw FormatError("too many run blocks (>= 2^30) for the 32-bit block directory / 16-byte-unit fetch indices");
-    // a bucket about as long as the average block (pgi_layout.h)
-    unsigned S = 0;
-    while (S < PGI_DIR_MAX_SHIFT && (n >> (S + 1)) >= nb) ++S;
-    const uint64_t nbuckets = (n >> S) + 1;
-    im.k.dir_shift = S; im.k.n_blocks = nb;
-    // largest superbucket whose block count fits the 16-bit delta: blocks inside [q << sb, (q + 1) << sb) for every q
-    unsigned SB = PGI_SB_MAX_SHIFT;
-    for (; SB > PGI_SB_MIN_SHIFT; --SB) {
-        bool ok = true; uint64_t i = 0;
-        for (uint64_t q = 0; ok && (q << SB) <= n; ++q) {
-            const uint64_t end = (q + 1) << SB; uint64_t j = i;
-            while (j + 1 < nb && starts[j + 1] < end) ++j;              // j = last block starting inside the superbucket
-            if (j - i >= 0xFFFF) ok = false;
-            i = j;
-        }
-        if (ok) break;
+// Buckets holding more than PGI_RUNS_PER_BLOCK clipped runs for a bucket size of 2^S positions.
+inline uint64_t count_overflow_buckets(const std::vector<uint32_t> &runs, unsigned S) {
+    uint64_t pos = 0, cur = 0, cnt = 0, over = 0;      // cur: bucket being filled, cnt: its entries so far
+    for (uint32_t e : runs) {
+        const uint64_t len = e >> 3, b0 = pos >> S, b1 = (pos + len - 1) >> S;
+        if (b0 != cur) { over += cnt > PGI_RUNS_PER_BLOCK; cur = b0; cnt = 0; }
+        ++cnt;
+        if (b1 != b0) { over += cnt > PGI_RUNS_PER_BLOCK; cur = b1; cnt = 1; }   // buckets strictly between hold one entry
+        pos += len;
     }
-    im.k.sb_shift = SB;
-    const uint64_t nsb = (n >> SB) + 1, sb_mask = (1ULL << SB) - 1;
-    im.dir.assign(nbuckets + 1, 0); im.sb.assign(nsb, 0);
-    uint64_t idx = 0;
-    for (uint64_t b = 0; b <= nbuckets; ++b) {
-        const uint64_t lo = b << S, hi = lo + (1ULL << S);
-        while (idx + 1 < nb && starts[idx + 1] <= lo) ++idx;
-        const uint64_t s = lo >> SB;
-        if (s < nsb && (lo & sb_mask) == 0) im.sb[s] = (uint32_t) idx;     // superbucket starts are bucket starts (S <= 8 < 19)
-        const uint64_t base = im.sb[s < nsb ? s : nsb - 1];
-        uint64_t t1 = 0, t2 = 0;
-        if (idx + 1 < nb && starts[idx + 1] < hi) t1 = starts[idx + 1] - lo;
-        if (idx + 2 < nb && starts[idx + 2] < hi) t2 = starts[idx + 2] - lo;
-        const uint64_t delta = idx - base;
-        if (delta >= 0xFFFF) throw FormatError("internal: block directory delta overflow");
-        im.dir[b] = (uint32_t) (delta | (t1 << 16) | (t2 << 24));
-        // dense bucket (more than two block boundaries inside): its own record with every boundary (pgi_layout.h)
-        if (idx + 3 < nb && starts[idx + 3] < hi && im.dense.size() / PGI_DENSE_U32 < 0xFFFF) {
-            uint32_t rec[PGI_DENSE_U32] = {0}; unsigned nbd = 0;
-            rec[0] = (uint32_t) idx;
-            for (uint64_t j = idx + 1; j < nb && starts[j] < hi; ++j) {
-                if (nbd == PGI_DENSE_BOUNDS) { nbd = PGI_DENSE_BOUNDS + 1; break; }
-                const uint32_t off = (uint32_t) (starts[j] - lo);
-                rec[1 + nbd / 4] |= off << (8 * (nbd % 4)); ++nbd;
-            }
-            if (nbd <= PGI_DENSE_BOUNDS) {               // (cannot overflow with >= 12-position blocks; kept as a guard)
-                const uint64_t id = im.dense.size() / PGI_DENSE_U32;
-                im.dense.insert(im.dense.end(), rec, rec + PGI_DENSE_U32);
-                im.dir[b] = (uint32_t) (0xFFFFu | id << 16);
-            }
-        }
+    return over + (cnt > PGI_RUNS_PER_BLOCK);
+}
+
+// One 64-byte block (pgi_layout.h) from up to 12 entries; cum = symbol counts before the first entry.
+inline void write_block(uint64_t *dst, const uint64_t cum[6], const uint32_t *code, const uint32_t *end, unsigned ne, uint32_t w0) {
+    if (cum[1] >> 40 || cum[2] >> 40 || cum[3] >> 40 || cum[5] >> 40)
+        throw FormatError("index longer than 2^40 positions is not supported by the device layout");
+    if (cum[0] >> 32 || cum[4] >> 32)
+        throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
+    const uint64_t A = cum[1], C = cum[2], G = cum[3], T = cum[5], NL = cum[0], N = cum[4];
+    uint32_t w[PGI_BLOCK_U32];
+    w[0] = w0; w[1] = (uint32_t) A; w[2] = (uint32_t) C; w[3] = (uint32_t) G; w[4] = (uint32_t) T; w[5] = (uint32_t) NL; w[6] = (uint32_t) N;
+    w[7] = (uint32_t) (A >> 32) << 8 | (uint32_t) (C >> 32) << 16 | (uint32_t) (G >> 32) << 24;
+    uint64_t codes = 0;
+    for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) codes |= (uint64_t) (i < ne ? code[i] : PGI_CODE_UNUSED) << (4 * i);
+    auto e = [&](unsigned i) -> uint32_t { return ne ? end[i < ne ? i : ne - 1] : 0u; };     // unused runs repeat the last end offset
+    w[8] = (uint32_t) (T >> 32) | (uint32_t) (codes >> 32) << 16;
+    w[9] = (uint32_t) codes;
+    for (unsigned j = 0; j < 6; ++j) w[10 + j] = e(2 * j) | e(2 * j + 1) << 16;
+    for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) dst[j] = (uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32;
+}
+
+// The bucket array (pgi_layout.h): block b = positions [b << S, (b + 1) << S); chunk blocks of crowded buckets behind.
+// totals[c] receives the number of occurrences of code c.
+inline void build_buckets(RiImage &im, const std::vector<uint32_t> &runs, uint64_t n, uint64_t totals[6]) {
+    if (runs.empty()) throw FormatError("r-index has no runs");
+    unsigned S = PGI_MAX_BSHIFT;
+    if (const char *e = std::getenv("PGI_BSHIFT")) {
+        S = (unsigned) std::atoi(e);
+        if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 8]");
+    } else {
+        for (; S > PGI_MIN_BSHIFT; --S) if (count_overflow_buckets(runs, S) <= ((n >> S) + 1) / 64) break;
     }
-    if (im.dense.empty()) im.dense.assign(PGI_DENSE_U32, 0);   // never a null table on the device
+    const uint64_t nb = (n >> S) + 1, bsize = 1ull << S;
+    im.k.bshift = S; im.k.n_buckets = nb;
+    im.blocks.assign((size_t) nb * PGI_BLOCK_WORDS, 0);
+    uint64_t cum[6] = {0, 0, 0, 0, 0, 0}, pos = 0, n_dir = 0;
+    size_t ri = 0; uint64_t carry_len = 0; unsigned carry_code = 0;        // part of a run that continues into this bucket
+    std::vector<uint32_t> code, end;
+    for (uint64_t b = 0; b < nb; ++b) {
+        const uint64_t lo = b << S, hi = lo + bsize;
+        uint64_t bcum[6]; std::memcpy(bcum, cum, sizeof(cum));
+        code.clear(); end.clear();
+        while (pos < hi && (carry_len || ri < runs.size())) {
+            if (!carry_len) { carry_code = runs[ri] & 7u; carry_len = runs[ri] >> 3; ++ri; }
+            const uint64_t t = carry_len < hi - pos ? carry_len : hi - pos;
+            if (!code.empty() && code.back() == carry_code) end.back() += (uint32_t) t;     // a run split at 2^29 by the collector
+            else { code.push_back(carry_code); end.push_back((uint32_t) (pos + t - lo)); }
+            cum[carry_code] += t; pos += t; carry_len -= t;
+        }
+        uint64_t *dst = im.blocks.data() + (size_t) b * PGI_BLOCK_WORDS;
+        const unsigned ne = (unsigned) code.size();
+        if (ne <= PGI_RUNS_PER_BLOCK) { write_block(dst, bcum, code.data(), end.data(), ne, 0u); continue; }
+        // crowded bucket: directory block + chunk blocks (chunk 0: 12 runs; later chunks: pad entry + 11 runs)
+        const uint64_t base = im.blocks.size() / PGI_BLOCK_WORDS;
+        uint8_t bounds[PGI_DIR_BOUNDS] = {0}; unsigned nchunks = 0;
+        uint64_t ccum[6]; std::memcpy(ccum, bcum, sizeof(bcum));
+        for (unsigned i = 0; i < ne;) {
+            uint32_t cc[PGI_RUNS_PER_BLOCK], ce[PGI_RUNS_PER_BLOCK]; unsigned k = 0;
+            if (nchunks) {
+                if (nchunks > PGI_DIR_BOUNDS) throw FormatError("internal: too many chunks in a bucket");
+                bounds[nchunks - 1] = (uint8_t) end[i - 1];                 // < 2^S <= 256, and > 0
+                cc[0] = PGI_CODE_UNUSED; ce[0] = end[i - 1]; k = 1;
+            }
+            uint64_t add[6] = {0, 0, 0, 0, 0, 0};
+            for (; k < PGI_RUNS_PER_BLOCK && i < ne; ++k, ++i) { cc[k] = code[i]; ce[k] = end[i]; add[code[i]] += end[i] - (i ? end[i - 1] : 0u); }
+            im.blocks.resize(im.blocks.size() + PGI_BLOCK_WORDS);
+            write_block(im.blocks.data() + im.blocks.size() - PGI_BLOCK_WORDS, ccum, cc, ce, k, 0u);
+            for (unsigned c = 0; c < 6; ++c) ccum[c] += add[c];
+            ++nchunks;
+        }
+        dst = im.blocks.data() + (size_t) b * PGI_BLOCK_WORDS;             // (the vector may have moved)
+        write_block(dst, bcum, nullptr, nullptr, 0, (uint32_t) base);    // header: counts before the bucket (the answer at offset 0)
+        uint32_t w[PGI_BLOCK_U32];
+        for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) { w[2 * j] = (uint32_t) dst[j]; w[2 * j + 1] = (uint32_t) (dst[j] >> 32); }
+        w[8] &= 0xFFFFu; w[9] = PGI_CODE_DIRBLOCK;                       // marker; the scan of offset 0 adds nothing whatever the entries
+        std::memcpy(&w[10], bounds, PGI_DIR_BOUNDS);
+        for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) dst[j] = (uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32;
+        ++n_dir;
+    }
+    if (pos != n || carry_len || ri != runs.size()) throw FormatError("run lengths do not add up to the BWT size");
+    im.k.n_blocks = im.blocks.size() / PGI_BLOCK_WORDS; im.k.n_dir_blocks = n_dir;
+    if (im.k.n_blocks >> 30) throw FormatError("too many run blocks (>= 2^30) for the 16-byte-unit fetch indices");
+    for (unsigned c = 0; c < 6; ++c) totals[c] = cum[c];
 }
 
 // Per-byte extension descriptors: SURVEY.md App. B2/B3 folded into weights over true ranks
@@ -319,7 +330,7 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
     std::vector<uint64_t> ref_starts; ref_starts.reserve(bsp.ones);
     bsp.for_each_one([&](uint64_t, uint64_t p) { ref_starts.push_back(p); });
 
-    BlockBuilder bb(im.blocks);
+    RunCollector bb;
     im.n_file_runs = 0;
     unsigned code_of[256]; for (int i = 0; i < 256; ++i) code_of[i] = 8;
     for (unsigned c = 0; c < 6; ++c) code_of[kNuc[c]] = c;
@@ -372,10 +383,10 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
         }
     }
     bb.finish();
-    if (bb.pos != k.n) throw FormatError("run lengths do not add up to the BWT size");
-    bool present[6]; for (unsigned c = 0; c < 6; ++c) present[c] = bb.cum[c] != 0;
-    // totals of every nuc code = R(pos >= n)
-    build_block_dir(im, bb.starts, k.n);
+    if (bb.lpos != k.n) throw FormatError("run lengths do not add up to the BWT size");
+    uint64_t totals[6];
+    build_buckets(im, bb.runs, k.n, totals);
+    bool present[6]; for (unsigned c = 0; c < 6; ++c) present[c] = totals[c] != 0;
     build_descriptors(im, present, !im.encoded);
     if (!k.has_quirk) { im.q_start.clear(); im.q_val.clear(); }
     k.n_quirk = im.q_start.size();

@@ -71,6 +71,21 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
 // extension with the count descriptors (a.desc = the desc_c bank), a lane is done when its read is used up or the range
 // became empty, and its record {0, len, range.first, size} (empty range: bwt_start 1, size 0 = the reference's {1,0})
 // goes to mem_buf[read] directly: one record per read, already in read order.
+// Crowded bucket (pgi_layout.h): sl = the lane's staged directory block, z = its swizzle. Index of the chunk block that
+// holds bucket offset rel (> 0): first chunk + number of chunk boundaries <= rel.
+__device__ __noinline__ uint32_t staged_chunk_of(const uint4 *sl, unsigned z, uint32_t rel) {
+    const uint4 c = sl[2u ^ z], d = sl[3u ^ z];
+    const uint32_t first = sl[0u ^ z].x;
+    const uint32_t bw[6] = {c.z, c.w, d.x, d.y, d.z, d.w};
+    uint32_t j = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const uint32_t x = bw[i];                                        // a boundary b (> 0) counts when b <= rel; 0 = unused never counts
+        j += (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
+    }
+    return first + j;
+}
+
 template <int MODE, int THREADS, int BPS, int OP = 0>
 __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
@@ -152,16 +167,20 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         // ---- one FMD extension
         // forward extension = backward extension of the swapped interval with the complement's descriptor
         // (src/r-index.cpp:758-764): ONE call site, so lanes in different phases share the same instructions
+        // The 8-byte window of the read holding the symbol is REQUESTED here and USED only behind the block fetch below, so
+        // that its latency overlaps the blocks' instead of preceding it (ncu r01g: a quarter of the stall samples sat on the
+        // extraction of the symbol, in front of the cp.async sequence).
         uint32_t sym = 0;
         const bool fwd = OP == 0 && L.phase == PH_P2;
-        if (need && L.j < L.len) {
+        const bool has_sym = need && L.j < L.len;
+        if (has_sym) {
             const uint64_t o = base + L.j;
             if ((o >> 3) != cwi) {
                 cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
                 if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
             }
-            sym = (uint32_t) (cw >> ((o & 7) * 8)) & 0xFFu;
         }
+        if (MODE == 0 && has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
         if (MODE == 0) {
             if (need) {
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
@@ -173,19 +192,14 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 else { L.b = u; --L.j; }
             }
         } else {
-            // (1) every lane with work resolves its two block indices from the directory
-            uint32_t b1 = PGI_NOBLK, b2 = PGI_NOBLK;       // b2 stays PGI_NOBLK when k and k+s share a block
+            // (1) the block of a position is its bucket number: no directory access (pgi_layout.h)
+            uint32_t b1 = PGI_NOBLK, b2 = PGI_NOBLK;       // b2 stays PGI_NOBLK when k and k+s share a bucket
             if (need) {
                 uint64_t p1 = fwd ? L.b.kp : L.b.k, p2 = p1 + (uint64_t) L.b.s;
                 if (p2 > a.ix.n) p2 = a.ix.n;
                 if (p1 > a.ix.n) p1 = a.ix.n;
-                const uint64_t g1 = p1 >> a.ix.dir_shift, g2 = p2 >> a.ix.dir_shift, h1 = p1 >> a.ix.sb_shift, h2 = p2 >> a.ix.sb_shift;
-                const uint32_t e1 = ld32(a.ix.dir + g1), s1 = ld32(a.ix.sb + h1);
-                uint32_t e2 = e1, s2 = s1;
-                if (g2 != g1) e2 = ld32(a.ix.dir + g2);
-                if (h2 != h1) s2 = ld32(a.ix.sb + h2);
-                b1 = (uint32_t) locate_guess(a.ix, p1, e1, s1);
-                const uint32_t bb = (uint32_t) locate_guess(a.ix, p2, e2, s2);
+                b1 = (uint32_t) (p1 >> a.ix.bshift);
+                const uint32_t bb = (uint32_t) (p2 >> a.ix.bshift);
                 if (bb != b1) b2 = bb;
             }
             // (2) the warp fetches the blocks together: quad q of round r serves slot 8 r + q
@@ -194,16 +208,45 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r.
             // Block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
             // lane adds its part number and needs one multiply-add for the address.
-            const uint32_t q1 = b1 == PGI_NOBLK ? PGI_NOBLK : b1 << 2, q2 = b2 == PGI_NOBLK ? PGI_NOBLK : b2 << 2;
+            auto coop_fetch = [&](uint32_t i1, uint32_t i2) {
+                const uint32_t q1 = i1 == PGI_NOBLK ? PGI_NOBLK : i1 << 2, q2 = i2 == PGI_NOBLK ? PGI_NOBLK : i2 << 2;
 #pragma unroll
-            for (unsigned r = 0; r < 4; ++r) {
-                const unsigned src = 8u * r + (lane >> 2);
-                const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
-                cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
-                cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
+                for (unsigned r = 0; r < 4; ++r) {
+                    const unsigned src = 8u * r + (lane >> 2);
+                    const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
+                    cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
+                    cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
+                }
+                cp_async_wait_all();
+                __syncwarp();
+            };
+            coop_fetch(b1, b2);
+            // (2b) crowded buckets: a staged block that is a DIRECTORY block (pgi_layout.h) is replaced by the chunk block
+            // holding the position, through one more cooperative fetch that the whole warp takes part in, so that the scan
+            // below stays ONE converged code path (a per-lane slow path here ran at 1.8 active lanes and cost half as many
+            // warp instructions as the scan itself: every fresh interval starts at position 0 of the crowded bucket 0).
+            // Offset 0 needs no chunk: the directory block's own header holds the counts before the bucket.
+            unsigned which2 = b2 != PGI_NOBLK ? 1u : 0u;
+            {
+                uint32_t c1 = PGI_NOBLK, c2 = PGI_NOBLK;
+                if (need) {
+                    uint64_t p1 = fwd ? L.b.kp : L.b.k, p2 = p1 + (uint64_t) L.b.s;
+                    if (p2 > a.ix.n) p2 = a.ix.n;
+                    if (p1 > a.ix.n) p1 = a.ix.n;
+                    const uint32_t mask = (1u << a.ix.bshift) - 1u, rel1 = (uint32_t) p1 & mask, rel2 = (uint32_t) p2 & mask;
+                    const unsigned z = (lane >> 1) & 3u;
+                    const uint4 *sl1 = wstage + lane * 4u, *sl2 = wstage + which2 * 128u + lane * 4u;
+                    if (rel1 && (sl1[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c1 = staged_chunk_of(sl1, z, rel1);
+                    if (rel2 && (sl2[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c2 = staged_chunk_of(sl2, z, rel2);
+                }
+                if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
+                    __syncwarp();                             // every lane has read its directory words
+                    coop_fetch(c1, c2);
+                    if (c2 != PGI_NOBLK) which2 = 1u;
+                }
             }
-            cp_async_wait_all();
-            __syncwarp();
+            asm volatile("" : "+l"(cw));                      // pins the use of the read window behind the wait
+            if (has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
             // (3) every lane with work scans its own blocks out of shared memory
             if (need) {
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
@@ -213,15 +256,12 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 const uint32_t di = (fwd ? 256u : 0u) + sym, d = s_desc[di], tbl = d & 0xFFFFFFu;
                 const uint4 tq = s_tab[di];
                 ScanTab T; T.x = tq.x; T.y = tq.y; T.z = tq.z; T.w = tq.w;
+                const uint32_t mask = (1u << a.ix.bshift) - 1u;
                 uint32_t w[16];
                 ld_staged(wstage, 0u, lane, w);
-                PosRank r1 = pos_rank(w, p1, tbl, T);
-                ld_staged(wstage, b2 != PGI_NOBLK ? 1u : 0u, lane, w);
-                PosRank r2 = pos_rank(w, p2, tbl, T);
-                if (r1.left | r2.left) {                      // rare: a guess landed short (bucket with more than two boundaries)
-                    if (r1.left) r1 = rank_slow(a.ix, p1, tbl);
-                    if (r2.left) r2 = rank_slow(a.ix, p2, tbl);
-                }
+                const PosRank r1 = pos_rank(w, (uint32_t) p1 & mask, tbl, T);
+                ld_staged(wstage, which2, lane, w);
+                const PosRank r2 = pos_rank(w, (uint32_t) p2 & mask, tbl, T);
                 t = extend_finish(a.ix, t, d, r1, r2, p1, p2);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
                 ++n_ext;

@@ -3,49 +3,44 @@
 #pragma once
 #include <stdint.h>
 
-// One run block = 64 bytes = 16 little-endian u32 words (two 32-byte DRAM sectors, one aligned 64 B burst):
-//   w0      start, low 32 bits          start = first BWT position covered by the block (40 bits)
-//   w1..w4  A, C, G, T, low 32 bits     symbol counts before the block (40 bits each)
-//   w5, w6  NL, N                       endmarker / 'N' counts before the block (32 bits each)
-//   w7      start_hi | A_hi << 8 | C_hi << 16 | G_hi << 24      (bits 32..39 of the 40-bit fields)
+// The BWT is cut into BUCKETS of 2^bshift consecutive positions and bucket b is the 64-byte block number b: the block
+// of a position is pos >> bshift -- no directory, no predecessor search, ONE random 64-byte access per rank query
+// (the reference's blocks_start_pos.predecessor + block decode, src/r-index.cpp:594,621, costs 3-4 dependent lines).
+// Runs are clipped at bucket boundaries (a run that crosses one appears in both buckets).
+//
+// One block = 64 bytes = 16 little-endian u32 words (two 32-byte DRAM sectors, one aligned 64 B burst):
+//   w0      normal block: 0;  directory block (below): index of its first chunk block
+//   w1..w4  A, C, G, T, low 32 bits     symbol counts before the first position of the block's runs (40 bits each)
+//   w5, w6  NL, N                       endmarker / 'N' counts before it (32 bits each)
+//   w7      0 | A_hi << 8 | C_hi << 16 | G_hi << 24             (bits 32..39 of the 40-bit fields)
 //   w8      T_hi | spare << 8 | codes 8..11 << 16               (one nibble per run)
 //   w9      codes 0..7                                          (one nibble per run, run 0 in the low nibble)
 //   w10..w15 E_0..E_11, two per word (even run in the low half)
 // Run i of the block has symbol code c_i = index into nuc = {'\n','A','C','G','N','T'}
-// (include/pangenome_index/utils.hpp:11) and END OFFSET E_i = number of block positions up to and including run i
-// (16 bits, run lengths 1..4095: 12 * 4095 < 2^16). Unused runs have code 7 and repeat the last end offset, so E_11 is
-// always the length of the block. Storing ends instead of lengths makes the scan data-parallel: the positions of run i
-// that lie before block offset rel are min(rel, E_i) - min(rel, E_{i-1}), two runs per 16x2 SIMD min, and the weighted
-// sums are byte dot products (dp2a) against 8-byte weight tables looked up with the code nibbles as PRMT selectors
-// (pos_rank in pgi_core.cuh).
+// (include/pangenome_index/utils.hpp:11) and END OFFSET E_i = offset inside the BUCKET of the first position behind
+// run i (16 bits). Unused runs have code 7 and repeat the last end offset. Storing ends instead of lengths makes the
+// scan data-parallel: the positions of run i that lie before bucket offset rel are min(rel, E_i) - min(rel, E_{i-1}),
+// two runs per 16x2 SIMD min, and the weighted sums are byte dot products (dp2a) against 8-byte weight tables looked
+// up with the code nibbles as PRMT selectors (pos_rank in pgi_core.cuh).
+//
+// bshift is chosen per index (largest value <= 8 for which at most 1/64 of the buckets hold more than 12 clipped runs;
+// PGI_BSHIFT=<n> overrides it for tuning / tests). A bucket with MORE than 12 runs becomes a DIRECTORY block:
+//   w9 low nibble = 0xF (no run has that code), w0 = index of its first chunk block (chunks are stored behind the
+//   n_buckets primary blocks), bytes of w10..w15 = bucket offsets at which chunks 1, 2, ... start (0: unused); its
+//   header (w1..w8 low half) holds the counts before the bucket, which is the whole answer for bucket offset 0.
+// A chunk block has the normal format with the counts before ITS first run in the header; chunk 0 holds 12 runs,
+// later chunks start with a pad entry (code 7, E = the chunk's start offset) so that the same scan applies, then 11
+// runs. A position in such a bucket costs ONE more dependent 64-byte access (count the boundaries <= rel, load that
+// chunk): dense stretches are rare by the choice of bshift (but not negligible: the first n_seq BWT rows are runs of
+// length 1 next to C['A'], where every search for an 'A' starts).
 #define PGI_BLOCK_U32 16
 #define PGI_BLOCK_WORDS 8            /* the same block counted in u64 words (host vectors are u64) */
 #define PGI_RUNS_PER_BLOCK 12
-#define PGI_MAX_RUN_ENTRY 4095ull
 #define PGI_CODE_UNUSED 7u
-
-// Block directory: two levels, both read with independent loads (no dependent chain between them).
-//   sb[pos >> sb_shift]      (u32) index of the block containing the first position of the superbucket (2^19..2^30
-//                            positions: the table is a handful of cache lines, so 32 lanes' loads share wavefronts)
-//   dir[pos >> dir_shift]    (u32) bits 0..15  block index at the bucket start, relative to its superbucket's sb entry
-//                                  bits 16..23 offset inside the bucket of the 1st block boundary (0: none)
-//                                  bits 24..31 offset of the 2nd block boundary (0: none)
-// dir_shift <= 8, chosen so that a bucket is about one block long: 4 bytes per ~block instead of the 8 bytes per half
-// block of a one-level table, so the directory of a 2 G-position index is 31 MB and lives in L2 while the blocks stream
-// from HBM. A bucket with more than two boundaries makes the guess land short; the scan notices (positions left over
-// after the last run) and the rare slow path searches the block starts.
-// Dense buckets: a bucket with MORE than two block boundaries inside (short runs: e.g. the first n_seq BWT rows, which
-// hold the last symbol of every sequence, next to C['A'] = n_seq where every search for an 'A' starts) gets the
-// reserved delta 0xFFFF and, in bits 16..31, the number of a 32-byte record in the dense table:
-//   word 0      (u32) absolute index of the block containing the first position of the bucket
-//   bytes 4..31 offsets inside the bucket of every block boundary, ascending (0: none)
-// so that the guess is exact there too (a bucket holds at most 256 / 12 boundaries). Only when more than 65535
-// buckets are dense do the rest keep the two-boundary form and fall back to the search.
-#define PGI_DENSE_U32 8
-#define PGI_DENSE_BOUNDS 28
-#define PGI_SB_MIN_SHIFT 19           /* 2^19 / 12 < 2^16: the 16-bit delta always fits */
-#define PGI_SB_MAX_SHIFT 30           /* the flattener takes the largest shift whose deltas still fit: the sb table is then a few cache lines */
-#define PGI_DIR_MAX_SHIFT 8
+#define PGI_CODE_DIRBLOCK 0xFu
+#define PGI_MAX_BSHIFT 8             /* chunk boundaries are bytes */
+#define PGI_MIN_BSHIFT 4
+#define PGI_DIR_BOUNDS 24            /* bytes of w10..w15 */
 
 // Sources of one rank-vector slot R(pos)[i]: true rank of nuc code 0..5,
 // the legacy "column-0 cumulative at the reference block start" quirk, or constant zero.
@@ -62,8 +57,8 @@
 #define PGI_DESC_MAIN_QUIRK (1u << 27)
 #define PGI_DESC_MAIN_ZERO (1u << 28)
 typedef struct {
-    uint64_t n, sigma, n_blocks, n_quirk, mem_tail;
-    uint32_t dir_shift, has_quirk, sb_shift, pad_;
+    uint64_t n, sigma, n_blocks, n_quirk, mem_tail;       // n_blocks: primary (bucket) blocks + chunk blocks
+    uint32_t bshift, has_quirk; uint64_t n_buckets, n_dir_blocks;
     uint32_t slot[8];          // source of R(pos)[i], i < sigma (0..5 true rank of that nuc code, PGI_SRC_QUIRK, PGI_SRC_ZERO)
     uint64_t C[8];
     uint8_t sym_map[256];

@@ -17,9 +17,9 @@ static thread_local std::string g_err;
 
 static void bind(sim_index *s) {
     RiDev &d = s->rd; const RiImage &im = s->ri;
-    d.blocks = im.blocks.data(); d.dir = im.dir.data(); d.sb = im.sb.data(); d.dense = im.dense.data();
+    d.blocks = im.blocks.data();
     d.q_start = im.q_start.empty() ? nullptr : im.q_start.data(); d.q_val = im.q_val.empty() ? nullptr : im.q_val.data();
-    d.n = im.k.n; d.n_blocks = im.k.n_blocks; d.n_quirk = im.k.n_quirk; d.dir_shift = im.k.dir_shift; d.has_quirk = im.k.has_quirk; d.sb_shift = im.k.sb_shift; d.pad_ = 0;
+    d.n = im.k.n; d.n_blocks = im.k.n_blocks; d.n_quirk = im.k.n_quirk; d.bshift = im.k.bshift; d.has_quirk = im.k.has_quirk;
     for (int i = 0; i < 8; ++i) d.C[i] = im.k.C[i];
     if (s->has_tags) {
         TagDev &t = s->td; const TagImage &g = s->tg;
@@ -43,12 +43,12 @@ sim_index *sim_create(const void *ri, uint64_t ri_len, const void *tg, uint64_t 
     } catch (const std::exception &e) { g_err = e.what(); return nullptr; }
 }
 void sim_free(sim_index *s) { delete s; }
-// info: n, sigma, n_blocks, dir_shift, has_quirk, n_file_runs, n_ref_blocks, encoded, tag m, tag shift, tag low_bytes, starts_regular
+// info: n, sigma, n_blocks, bucket shift, has_quirk, n_file_runs, n_ref_blocks, encoded, tag m, tag shift, tag low_bytes, starts_regular
 void sim_info(const sim_index *s, uint64_t *info) {
-    info[0] = s->ri.k.n; info[1] = s->ri.k.sigma; info[2] = s->ri.k.n_blocks; info[3] = s->ri.k.dir_shift; info[4] = s->ri.k.has_quirk;
+    info[0] = s->ri.k.n; info[1] = s->ri.k.sigma; info[2] = s->ri.k.n_blocks; info[3] = s->ri.k.bshift; info[4] = s->ri.k.has_quirk;
     info[5] = s->ri.n_file_runs; info[6] = s->ri.n_ref_blocks; info[7] = s->ri.encoded;
     info[8] = s->has_tags ? s->tg.intervals.k.m : 0; info[9] = s->has_tags ? s->tg.intervals.k.shift : 0;
-    info[10] = s->has_tags ? s->tg.intervals.k.low_bytes : 0; info[11] = s->has_tags ? s->tg.starts_regular : 0;
+    info[10] = s->has_tags ? s->tg.intervals.k.low_bytes : 0; info[11] = s->has_tags ? s->tg.starts_regular : 0; info[12] = s->ri.k.n_dir_blocks; info[13] = s->ri.k.n_buckets;
 }
 void sim_extend_batch(const sim_index *s, uint64_t n, const uint64_t *in3, const uint8_t *sym, const uint8_t *dir, uint64_t *out3) {
     for (uint64_t i = 0; i < n; ++i) {

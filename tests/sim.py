@@ -33,8 +33,8 @@ class Index:
         if not self.h:
             raise RuntimeError(L.sim_last_error().decode())
         info = (ctypes.c_uint64 * 16)(); L.sim_info(self.h, info)
-        keys = ["n", "sigma", "n_blocks", "dir_shift", "has_quirk", "n_file_runs", "n_ref_blocks", "encoded",
-                "tag_m", "tag_shift", "tag_low_bytes", "starts_regular"]
+        keys = ["n", "sigma", "n_blocks", "bshift", "has_quirk", "n_file_runs", "n_ref_blocks", "encoded",
+                "tag_m", "tag_shift", "tag_low_bytes", "starts_regular", "n_crowded", "n_buckets"]
         self.info = dict(zip(keys, list(info)))
     def __del__(self):
         try:

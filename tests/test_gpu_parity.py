@@ -236,3 +236,22 @@ def test_query_tags_large_and_refusal(capi):
         g5.query_tags(reads[:400], off[:11])
     r5, o5 = datasets.sample_reads(s5["text"], 500, 150, 0.01, seed=2)                  # find_mems itself works on it
     compare(g5.find_mems(r5, o5, 20, 1), orc.Index(s5["ri"]).find_mems(r5, o5, 20, 1), False)
+
+@pytest.mark.parametrize("shift", ["8", "4"])
+def test_crowded_buckets(capi, shift, monkeypatch):
+    """Bucket size forced (PGI_BSHIFT) so that most buckets are crowded (8: directory block + cooperatively fetched chunk
+    blocks on every trip) or tiny (4): the answers do not depend on the device layout."""
+    monkeypatch.setenv("PGI_BSHIFT", shift)
+    for name in ("xy_legacy_bytecode", "synth_enc_compact"):
+        c = get_case(name)
+        g = capi.Index(c["ri"], c["tags"], c["layout"]); o = orc.Index(c["ri"], c["tags"], c["layout"])
+        assert g.info["bucket_shift"] == int(shift)
+        if shift == "8": assert g.info["n_crowded_buckets"] > g.info["n"] // 256 // 2
+        reads, off = datasets.sample_reads(c["text"], 3000, 150, 0.01, seed=23)
+        compare(g.find_mems(reads, off, 20, 1), o.find_mems(reads, off, 20, 1), True)
+        rs = datasets.ragged_reads(c["text"], seed=6); r2, o2 = orc.pack_reads(rs)
+        compare(g.find_mems(r2, o2, 3, 1), o.find_mems(r2, o2, 3, 1), True)
+        q, qo = orc.pack_reads(query_reads(c["text"], seed=3, n=1500))
+        compare_query_tags(g.query_tags(q, qo), o.query_tags(q, qo), True)
+        rng = np.random.default_rng(2); pos = rng.integers(0, o.n + 1, 20000).astype(np.uint64)
+        assert np.array_equal(g.rank_batch(pos), o.rank_batch(pos))
