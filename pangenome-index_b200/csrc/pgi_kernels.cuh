@@ -74,16 +74,16 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
 // Crowded bucket (pgi_layout.h): sl = the lane's staged directory block, z = its swizzle. Index of the chunk block that
 // holds bucket offset rel (> 0): first chunk + number of chunk boundaries <= rel.
 __device__ __noinline__ uint32_t staged_chunk_of(const uint4 *sl, unsigned z, uint32_t rel) {
-    const uint4 c = sl[2u ^ z], d = sl[3u ^ z];
-    const uint32_t first = sl[0u ^ z].x;
-    const uint32_t bw[6] = {c.z, c.w, d.x, d.y, d.z, d.w};
-    uint32_t j = 0;
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        const uint32_t x = bw[i];                                        // a boundary b (> 0) counts when b <= rel; 0 = unused never counts
-        j += (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
+    uint32_t j = sl[0u ^ z].x;                                           // first chunk
+    const uint32_t *c = reinterpret_cast<const uint32_t *>(sl + (2u ^ z)), *d = reinterpret_cast<const uint32_t *>(sl + (3u ^ z));
+#pragma unroll 1
+    for (int i = 2; i < 8; ++i) {                                        // boundary words: w10, w11 (part 2), w12..w15 (part 3)
+        const uint32_t x = i < 4 ? c[i] : d[i - 4];                      // a boundary b (> 0) counts when b <= rel; 0 = unused never counts
+        const uint32_t n = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
+        j += n;
+        if (n < 4u) break;                                               // ascending: nothing further can count
     }
-    return first + j;
+    return j;
 }
 
 template <int MODE, int THREADS, int BPS, int OP = 0>
