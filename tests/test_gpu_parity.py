@@ -255,3 +255,17 @@ def test_crowded_buckets(capi, shift, monkeypatch):
         compare_query_tags(g.query_tags(q, qo), o.query_tags(q, qo), True)
         rng = np.random.default_rng(2); pos = rng.integers(0, o.n + 1, 20000).astype(np.uint64)
         assert np.array_equal(g.rank_batch(pos), o.rank_batch(pos))
+
+def test_long_reads_with_indel_errors(capi):
+    """BASELINE configs[4] as a parity case: 10 kbp reads with 5 % errors (substitutions + 1 bp indels): long backward /
+    forward chains per lane, lanes of one warp finishing at very different times, many MEMs per read."""
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    g = capi.Index(s["ri"], s["tags0"], 0); o = orc.Index(s["ri"], s["tags0"], 0)
+    reads, off = datasets.sample_reads(s["text"], 300, 10000, 0.04, seed=31, indel=0.01)
+    G = g.find_mems(reads, off, 20, 1); R = o.find_mems(reads, off, 20, 1, count_work=True)
+    compare(G, R, True)
+    assert G["extensions"] == R["counters"]["E"] and G["n_mems"] > 300 * 50
+    mixed = [reads[int(off[i]):int(off[i + 1])].tobytes()[: (10000 if i % 7 == 0 else 37 * (i % 11))] for i in range(120)]   # long and short lanes in one warp
+    mr, mo = orc.pack_reads(mixed)
+    compare(g.find_mems(mr, mo, 12, 2), o.find_mems(mr, mo, 12, 2), True)
+    compare_query_tags(g.query_tags(mr, mo), o.query_tags(mr, mo), True)
