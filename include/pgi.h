@@ -74,6 +74,8 @@ typedef struct {
     uint64_t has_tags, tag_layout, tag_runs, tag_items, tag_item_width, tag_universe;
     uint64_t device_bytes;   /* bytes of HBM held by the index */
     uint64_t n_crowded_buckets; /* buckets with more than 12 runs (directory block + chunk blocks: one more access) */
+    uint64_t has_locate;     /* the file carries samples / last / last_to_run and pgi_locate_batch works on it */
+    uint64_t max_length;     /* Header::max_length: SA value = seq_id * max_length + seq_offset (r-index.hpp:424-431) */
     uint64_t C[8];
     uint8_t  sym_map[256];
 } pgi_index_info_t;
@@ -103,6 +105,24 @@ int pgi_rank_batch(pgi_index *, uint64_t n, const uint64_t *pos, uint64_t *out8)
  * chosen by the layout the index was created with. Intervals are [start[i], end[i]] inclusive.
  * Result: tag_off / tags / n_runs of `out` (n_mems = n; mems, mem_off are NULL). Free with pgi_result_free. */
 int pgi_tag_query_batch(pgi_index *, uint64_t n, const uint64_t *start, const uint64_t *end, pgi_result *out);
+
+/* Batched FastLocate::locate_encoded (src/r-index.cpp:1300-1343): for every BWT range [first[i],
+ * second[i]] (inclusive; second < first = empty) the SA value of its first row from the sample of that row's run
+ * (getSample, include/pangenome_index/r-index.hpp:616) plus one phi step (locateNext, src/r-index.cpp:1369-1372) per row.
+ * Result (malloc'd host arrays, free with pgi_locate_result_free):
+ *   ids[id_off[i] .. id_off[i+1])  the reference's return value: sorted unique SEQUENCE IDS (seqId, r-index.hpp:429)
+ *   sa[row_off[i] + t]             the SA value (seq_id * max_length + seq_offset) of row first[i] + t, i.e. the values
+ *                                  the reference holds in `first` while it walks the range (decompressSA, :1345-1356)
+ * The reference's legacy twin FastLocate::locate has an empty body (:1281-1296); on a legacy file the same algorithm runs
+ * over the file's own logical runs. PGI_EFORMAT when the file has no samples or is an encoded file without N (the
+ * reference's run lookup skips six cumulatives where five exist); PGI_EINVAL for a range beyond the BWT. */
+typedef struct {
+    uint64_t n, n_ids, n_rows;
+    uint64_t *id_off, *ids;     /* n + 1, n_ids  */
+    uint64_t *row_off, *sa;     /* n + 1, n_rows */
+} pgi_locate_result;
+int pgi_locate_batch(pgi_index *, uint64_t n, const uint64_t *first, const uint64_t *second, pgi_locate_result *out);
+void pgi_locate_result_free(pgi_locate_result *);
 
 /* The hot path: for every read, find_all_mems (include/pangenome_index/algorithm.hpp:739-757) and,
  * when the index has tags, the tag query of src/find_mems.cpp:128 for every MEM.

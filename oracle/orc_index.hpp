@@ -264,6 +264,76 @@ struct FastLocate {
         return range;
     }
 
+    // ---- locate: toehold sample + phi ------------------------------------------------------
+    static const uint64_t NO_POSITION = UINT64_MAX;                                  // r-index.hpp:49
+    uint64_t getSample(uint64_t run_id) const { return samples.get(run_id); }        // r-index.hpp:616-618
+    uint64_t seqId(uint64_t offset) const { return offset / max_length; }            // r-index.hpp:429
+    uint64_t seqOffset(uint64_t offset) const { return offset % max_length; }        // r-index.hpp:431
+    uint64_t locateFirst() const { return getSample(0); }                            // r-index.hpp:490-492
+
+    // FastLocate::locateNext, r-index.cpp:1369-1372 (phi): the SA value of the row below the one holding prev.
+    // Defined UB: no predecessor in `last` / a run id past the samples read as sample 0.
+    uint64_t locateNext(uint64_t prev) const {
+        uint64_t j = last.predecessor_index(prev);
+        if (j == UINT64_MAX) return 0;
+        uint64_t run = last_to_run.get(j) + 1;
+        return (run < samples.size() ? samples.get(run) : 0) + (prev - last.ones[j]);
+    }
+
+    // The run lookup at the head of locate_encoded, r-index.cpp:1308-1329: logical run (block_id * block size + index in
+    // the block) containing BWT row pos, and the row it starts at. skip_header reads SIX ByteCode values whatever the
+    // file holds (:85-90): on an encoded file without N the scan starts inside the run headers (restated literally).
+    void run_id_and_start(uint64_t pos, uint64_t &run_id, uint64_t &run_start) const {
+        uint64_t bid, bstart; locate_block(pos, bid, bstart);
+        uint64_t nb = blocks_encoded_start_bits.size();
+        run_id = 0; run_start = 0;
+        if (!is_encoded()) {
+            // EXTENSION, not reference behaviour: the legacy twin FastLocate::locate has an empty body (:1281-1296) and
+            // locate_encoded is undefined on a legacy file. The same lookup over the legacy block's runs, so that the
+            // shipped legacy files (the only ones with samples the reference ships) can be located on.
+            if (bid >= blocks.size()) return;
+            uint64_t cur = 0, runnum = 0;
+            for (const auto &rn : blocks[bid].runs) { if (cur + rn.second > pos - bstart) break; cur += rn.second; runnum++; }
+            run_id = bid * 10 + runnum; run_start = bstart + cur;
+            return;
+        }
+        if (bid >= nb) return;
+        size_t loc = (size_t) blocks_encoded_start_bits.get(bid);
+        for (int i = 0; i < 6; ++i) (void) bytecode_read(blocks_encoded_stream.data(), blocks_encoded_stream.size(), loc);
+        uint64_t cur = 0, runnum = 0;
+        for (;;) {
+            if (loc >= blocks_encoded_stream.size()) break;                              // reference: unbounded loop; defined as "last run seen"
+            uint8_t header = blocks_encoded_stream[loc++];
+            uint64_t prefix = header & 0x1F;
+            uint64_t run_length = prefix < 31 ? prefix + 1 : 32 + bytecode_read(blocks_encoded_stream.data(), blocks_encoded_stream.size(), loc);
+            if (cur + run_length > pos - bstart) break;
+            cur += run_length; runnum++;
+        }
+        run_id = bid * (encoded_block_size ? encoded_block_size : 10) + runnum;
+        run_start = bstart + cur;
+    }
+
+    // FastLocate::locate_encoded, r-index.cpp:1300-1343: sorted unique SEQUENCE IDS of the rows of [state.first,
+    // state.second]. `sa` (optional) receives the raw SA values row by row (the values the reference holds in `first`).
+    std::vector<uint64_t> locate_encoded(std::pair<uint64_t, uint64_t> state, uint64_t first = NO_POSITION, std::vector<uint64_t> *sa = nullptr) const {
+        std::vector<uint64_t> result;
+        if (state.second < state.first) return result;
+        uint64_t offset_of_first = state.first;
+        if (first == NO_POSITION) {
+            uint64_t run_id; run_id_and_start(state.first, run_id, offset_of_first);
+            first = getSample(run_id);
+        }
+        while (offset_of_first < state.first) { first = locateNext(first); offset_of_first++; }
+        result.push_back(seqId(first)); if (sa) sa->push_back(first);
+        for (uint64_t i = state.first + 1; i <= state.second; i++) {
+            first = locateNext(first);
+            result.push_back(seqId(first)); if (sa) sa->push_back(first);
+        }
+        std::sort(result.begin(), result.end());
+        result.erase(std::unique(result.begin(), result.end()), result.end());
+        return result;
+    }
+
     // r-index.cpp:758-764 / :1500-1509
     bi_interval forward_extend_encoded(const bi_interval &bint, uint64_t symbol, uint64_t *distinct_blocks = nullptr) const {
         bi_interval tmp{bint.reverse, bint.forward, bint.size};

@@ -235,6 +235,30 @@ char *orc_format_query_tags(const orc_result *r, uint64_t first_index, uint64_t 
     return buf;
 }
 
+// locate_encoded for a batch of BWT ranges [first[i], second[i]]: out_off (n + 1) / out (sorted unique sequence ids per
+// query, up to cap values in total); sa_out (optional, sum of range sizes values up to sa_cap): raw SA values row by row.
+// Returns the total number of ids (may exceed cap: then nothing beyond cap was written).
+uint64_t orc_locate_batch(const orc_index *ix, uint64_t n, const uint64_t *first, const uint64_t *second,
+                          uint64_t *out_off, uint64_t *out, uint64_t cap, uint64_t *sa_out, uint64_t sa_cap) {
+    uint64_t tot = 0, sa_tot = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+        std::vector<uint64_t> sa;
+        std::vector<uint64_t> v = ix->ri.locate_encoded({first[i], second[i]}, FastLocate::NO_POSITION, sa_out ? &sa : nullptr);
+        out_off[i] = tot;
+        for (uint64_t x : v) { if (tot < cap) out[tot] = x; ++tot; }
+        for (uint64_t x : sa) { if (sa_tot < sa_cap) sa_out[sa_tot] = x; ++sa_tot; }
+    }
+    out_off[n] = tot;
+    return tot;
+}
+// decompressSA, r-index.cpp:1345-1356: SA value of every BWT row through locateFirst + locateNext.
+void orc_decompress_sa(const orc_index *ix, uint64_t *out) {
+    uint64_t n = ix->ri.bwt_size();
+    if (!n) return;
+    out[0] = ix->ri.locateFirst();
+    for (uint64_t i = 1; i < n; ++i) out[i] = ix->ri.locateNext(out[i - 1]);
+}
+
 void orc_result_free(orc_result *r) {
     std::free(r->mem_off); std::free(r->mems); std::free(r->tag_off); std::free(r->tags); std::free(r->n_runs);
     std::memset(r, 0, sizeof(*r));

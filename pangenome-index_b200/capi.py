@@ -10,7 +10,7 @@ _lib = None
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
-           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
+           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -20,7 +20,11 @@ class Result(ctypes.Structure):
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
                                                "has_quirk_slot", "has_tags", "tag_layout", "tag_runs", "tag_items", "tag_item_width",
-                                               "tag_universe", "device_bytes", "n_crowded_buckets"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
+                                               "tag_universe", "device_bytes", "n_crowded_buckets", "has_locate", "max_length"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
+
+class LocateResult(ctypes.Structure):
+    _fields_ = [("n", ctypes.c_uint64), ("n_ids", ctypes.c_uint64), ("n_rows", ctypes.c_uint64), ("id_off", ctypes.c_void_p),
+                ("ids", ctypes.c_void_p), ("row_off", ctypes.c_void_p), ("sa", ctypes.c_void_p)]
 
 class PgiError(RuntimeError):
     pass
@@ -59,6 +63,8 @@ def lib():
         L.pgi_free.argtypes = [vp]
         L.pgi_query_tags.argtypes = [vp, vp, vp, u64, vp, ctypes.POINTER(Result)]
         L.pgi_batch_run_query_tags.argtypes = [vp]
+        L.pgi_locate_batch.argtypes = [vp, u64, vp, vp, ctypes.POINTER(LocateResult)]
+        L.pgi_locate_result_free.argtypes = [ctypes.POINTER(LocateResult)]
         L.pgi_format_query_tags_text.restype = ctypes.c_void_p
         L.pgi_format_query_tags_text.argtypes = [ctypes.POINTER(Result), u64, ctypes.POINTER(u64)]
         L.pgi_host_alloc.restype = vp; L.pgi_host_alloc.argtypes = [ctypes.c_size_t]; L.pgi_host_free.argtypes = [vp]
@@ -98,7 +104,7 @@ class Index:
             _ck(L.pgi_index_create(ri, len(ri) if ri else 0, tags, len(tags) if tags else 0, tag_layout, device, ctypes.byref(h)))
             self.h = h
         info = IndexInfo(); _ck(L.pgi_index_info(self.h, ctypes.byref(info)))
-        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:16]}
+        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:18]}
         self.n = info.n; self.sigma = info.sigma; self.has_tags = bool(info.has_tags)
         self.C = list(info.C)[: info.sigma]; self.sym_map = bytes(info.sym_map)
     def clone_to(self, device):
@@ -144,6 +150,15 @@ class Index:
             p = L.pgi_format_query_tags_text(ctypes.byref(res), 0, ctypes.byref(ln))
             out["text"] = ctypes.string_at(p, ln.value); L.pgi_free(p)
         L.pgi_result_free(ctypes.byref(res))
+        return out
+
+    def locate_batch(self, first, second):
+        """FastLocate::locate_encoded per BWT range -> (id_off [n+1], sorted unique sequence ids, row_off [n+1], SA values row by row)."""
+        first = np.ascontiguousarray(first, dtype=np.uint64); second = np.ascontiguousarray(second, dtype=np.uint64)
+        res = LocateResult(); L = lib()
+        _ck(L.pgi_locate_batch(self.h, len(first), first.ctypes.data, second.ctypes.data, ctypes.byref(res)))
+        out = (_arr(res.id_off, res.n + 1), _arr(res.ids, res.n_ids), _arr(res.row_off, res.n + 1), _arr(res.sa, res.n_rows))
+        L.pgi_locate_result_free(ctypes.byref(res))
         return out
 
     def find_mems_raw(self, reads_ptr, off_ptr, n_reads, min_len, min_occ):

@@ -71,7 +71,8 @@ template <typename T> T *upload(const std::vector<T> &v, std::vector<void *> &ow
 
 struct pgi_index {
     int device = 0;
-    RiDev ri; TagDev tg; bool has_tags = false, has_ri = true;
+    RiDev ri; TagDev tg; LocDev loc; bool has_tags = false, has_ri = true, has_locate = false;
+    uint64_t n_rs_dir = 0, n_rs_low = 0, n_last_dir = 0, n_last_low = 0, n_samples_words = 0, n_ltr_words = 0;
     RiConsts consts; SparseRankConsts ivk;
     uint32_t *d_desc = nullptr, *d_desc_c = nullptr;      // extension descriptors; LF-step descriptors of the whole-read search
     std::vector<void *> owned;
@@ -106,7 +107,7 @@ static void fill_info(pgi_index *ix, const RiImage &ri, const TagImage *tg, uint
         f.has_tags = 1; f.tag_layout = (uint64_t) tg->layout; f.tag_runs = tg->intervals.k.m; f.tag_items = tg->n_items;
         f.tag_item_width = tg->width; f.tag_universe = tg->intervals.k.size;
     }
-    f.device_bytes = bytes;
+    f.device_bytes = bytes; f.has_locate = ri.k.locate_ok; f.max_length = ri.k.max_length;
     for (int i = 0; i < 8; ++i) f.C[i] = ri.k.C[i];
     std::memcpy(f.sym_map, ri.k.sym_map, 256);
 }
@@ -143,6 +144,22 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
             desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
         }
         ix->d_desc_c = upload(desc, ix->owned, bytes);
+        std::memset(&ix->loc, 0, sizeof(ix->loc));
+        if (ri_bytes && ri.k.locate_ok) {
+            LocDev &l = ix->loc; ix->has_locate = true;
+            auto up_sr = [&](const SparseRankImage &im, SparseRankDev &d, uint64_t &nd, uint64_t &nl) {
+                d.dir = upload(im.dir, ix->owned, bytes); nd = im.dir.size();
+                d.low = upload(im.low, ix->owned, bytes); nl = im.low.size();
+                d.size = im.k.size; d.m = im.k.m; d.shift = im.k.shift; d.low_bytes = im.k.low_bytes;
+            };
+            up_sr(ri.run_starts, l.run_starts, ix->n_rs_dir, ix->n_rs_low);
+            up_sr(ri.last, l.last, ix->n_last_dir, ix->n_last_low);
+            l.samples.words = upload(ri.samples.words, ix->owned, bytes); ix->n_samples_words = ri.samples.words.size();
+            l.samples.n = ri.samples.n; l.samples.width = ri.samples.width; l.samples.pad = 0;
+            l.last_to_run.words = upload(ri.last_to_run.words, ix->owned, bytes); ix->n_ltr_words = ri.last_to_run.words.size();
+            l.last_to_run.n = ri.last_to_run.n; l.last_to_run.width = ri.last_to_run.width; l.last_to_run.pad = 0;
+            l.max_length = ri.k.max_length;
+        }
         std::memset(&ix->tg, 0, sizeof(ix->tg));
         if (has_tags) {
             TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = tg.intervals.k;
@@ -188,6 +205,9 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix = new pgi_index(); ix->device = device; ix->consts = src->consts; ix->ivk = src->ivk; ix->info = src->info;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         ix->ri = src->ri; ix->tg = src->tg; ix->has_tags = src->has_tags; ix->has_ri = src->has_ri;
+        ix->loc = src->loc; ix->has_locate = src->has_locate;
+        ix->n_rs_dir = src->n_rs_dir; ix->n_rs_low = src->n_rs_low; ix->n_last_dir = src->n_last_dir; ix->n_last_low = src->n_last_low;
+        ix->n_samples_words = src->n_samples_words; ix->n_ltr_words = src->n_ltr_words;
         ix->n_block_words = src->n_block_words; ix->n_quirk = src->n_quirk; ix->n_iv_dir = src->n_iv_dir;
         ix->n_iv_low = src->n_iv_low; ix->n_starts = src->n_starts; ix->n_words = src->n_words; ix->n_stream = src->n_stream;
         const int sd = src->device;
@@ -196,6 +216,14 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);
         ix->d_desc_c = clone_arr(src->d_desc_c, sd, PGI_DESC_WORDS, device, ix->owned);
+        if (src->has_locate) {
+            ix->loc.run_starts.dir = clone_arr(src->loc.run_starts.dir, sd, src->n_rs_dir, device, ix->owned);
+            ix->loc.run_starts.low = clone_arr(src->loc.run_starts.low, sd, src->n_rs_low, device, ix->owned);
+            ix->loc.last.dir = clone_arr(src->loc.last.dir, sd, src->n_last_dir, device, ix->owned);
+            ix->loc.last.low = clone_arr(src->loc.last.low, sd, src->n_last_low, device, ix->owned);
+            ix->loc.samples.words = clone_arr(src->loc.samples.words, sd, src->n_samples_words, device, ix->owned);
+            ix->loc.last_to_run.words = clone_arr(src->loc.last_to_run.words, sd, src->n_ltr_words, device, ix->owned);
+        }
         if (src->has_tags) {
             ix->tg.iv.dir = clone_arr(src->tg.iv.dir, sd, src->n_iv_dir, device, ix->owned);
             ix->tg.iv.low = clone_arr(src->tg.iv.low, sd, src->n_iv_low, device, ix->owned);
@@ -617,6 +645,74 @@ extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *st
         out->mems = nullptr; out->mem_off = nullptr; out->owner = b;
         return PGI_OK;
     } catch (const CudaError &e) { pool_give(ix, b); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+}
+
+// FastLocate::locate_encoded for a batch of BWT ranges.
+extern "C" int pgi_locate_batch(pgi_index *ix, uint64_t n, const uint64_t *first, const uint64_t *second, pgi_locate_result *out) {
+    if (!ix || !out || ((!first || !second) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
+    if (!ix->has_locate) return fail(PGI_EFORMAT, ix->info.is_encoded && ix->info.sigma != 6
+        ? "encoded r-index without N: the reference's locate_encoded skips six cumulatives where five exist (src/r-index.cpp:85-90,1313); not reproduced"
+        : "the r-index file carries no suffix-array samples (samples / last / last_to_run are empty): nothing to locate with");
+    std::memset(out, 0, sizeof(*out));
+    std::vector<uint64_t> row_off(n + 1, 0);
+    for (uint64_t i = 0; i < n; ++i) {
+        if (second[i] >= first[i] && second[i] >= ix->info.n) return fail(PGI_EINVAL, "range beyond the BWT (undefined in the reference)");
+        row_off[i + 1] = row_off[i] + (second[i] >= first[i] ? second[i] - first[i] + 1 : 0);
+    }
+    const uint64_t rows = row_off[n];
+    pgi_batch *b = pool_take(ix);
+    if (!b) return PGI_ECUDA;
+    uint64_t *h_id_off = nullptr, *h_ids = nullptr, *h_row_off = nullptr, *h_sa = nullptr;
+    try {
+        DeviceGuard g(ix->device);
+        cudaStream_t st = b->stream;
+        DevBuf d_first, d_second, d_row_off, d_sa, d_ids, d_ids2, d_ucnt, d_id_off, d_out;
+        struct Release { std::vector<DevBuf *> v; ~Release() { for (DevBuf *x : v) x->release(); } } rel{{&d_first, &d_second, &d_row_off, &d_sa, &d_ids, &d_ids2, &d_ucnt, &d_id_off, &d_out}};
+        d_first.need((n + 1) * 8); d_second.need((n + 1) * 8); d_row_off.need((n + 1) * 8); d_sa.need((rows + 1) * 8); d_ids.need((rows + 1) * 8);
+        d_ids2.need((rows + 1) * 8); d_ucnt.need((n + 1) * 8); d_id_off.need((n + 1) * 8);
+        if (n) { CK(cudaMemcpyAsync(d_first.p, first, n * 8, cudaMemcpyHostToDevice, st)); CK(cudaMemcpyAsync(d_second.p, second, n * 8, cudaMemcpyHostToDevice, st)); }
+        CK(cudaMemcpyAsync(d_row_off.p, row_off.data(), (n + 1) * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(d_ucnt.p, 0, (n + 1) * 8, st));
+        uint64_t n_ids = 0;
+        if (n && rows) {
+            locate_kernel<<<grid_for(n, 128), 128, 0, st>>>(ix->loc, n, d_first.as<uint64_t>(), d_second.as<uint64_t>(), d_row_off.as<uint64_t>(), d_sa.as<uint64_t>(), d_ids.as<uint64_t>());
+            CK(cudaGetLastError());
+            size_t tmp = 0;
+            CK(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp, d_ids.as<uint64_t>(), d_ids2.as<uint64_t>(), (int64_t) rows, (int64_t) n,
+                                                  d_row_off.as<int64_t>(), d_row_off.as<int64_t>() + 1, st));
+            b->d_cub.need(tmp);
+            CK(cub::DeviceSegmentedSort::SortKeys(b->d_cub.p, tmp, d_ids.as<uint64_t>(), d_ids2.as<uint64_t>(), (int64_t) rows, (int64_t) n,
+                                                  d_row_off.as<int64_t>(), d_row_off.as<int64_t>() + 1, st));
+            locate_unique_kernel<<<grid_for(n, 128), 128, 0, st>>>(n, d_row_off.as<uint64_t>(), d_ids2.as<uint64_t>(), d_ucnt.as<uint64_t>());
+            CK(cudaGetLastError());
+        }
+        int launches = 0;
+        exclusive_scan(b, d_ucnt.as<uint64_t>(), d_id_off.as<uint64_t>(), n + 1, launches);
+        n_ids = read_back(b, d_id_off.as<uint64_t>() + n);
+        d_out.need((n_ids + 1) * 8);
+        if (n && n_ids) {
+            locate_copy_kernel<<<grid_for(n, 128), 128, 0, st>>>(n, d_row_off.as<uint64_t>(), d_id_off.as<uint64_t>(), d_ids2.as<uint64_t>(), d_out.as<uint64_t>());
+            CK(cudaGetLastError());
+        }
+        h_id_off = (uint64_t *) std::malloc((n + 1) * 8); h_ids = (uint64_t *) std::malloc((n_ids + 1) * 8);
+        h_row_off = (uint64_t *) std::malloc((n + 1) * 8); h_sa = (uint64_t *) std::malloc((rows + 1) * 8);
+        if (!h_id_off || !h_ids || !h_row_off || !h_sa) throw std::bad_alloc();
+        CK(cudaMemcpyAsync(h_id_off, d_id_off.p, (n + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (n_ids) CK(cudaMemcpyAsync(h_ids, d_out.p, n_ids * 8, cudaMemcpyDeviceToHost, st));
+        if (rows) CK(cudaMemcpyAsync(h_sa, d_sa.p, rows * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        std::memcpy(h_row_off, row_off.data(), (n + 1) * 8);
+        pool_give(ix, b);
+        out->n = n; out->n_ids = n_ids; out->n_rows = rows; out->id_off = h_id_off; out->ids = h_ids; out->row_off = h_row_off; out->sa = h_sa;
+        return PGI_OK;
+    } catch (const CudaError &e) { pool_give(ix, b); std::free(h_id_off); std::free(h_ids); std::free(h_row_off); std::free(h_sa); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e));
+    } catch (const std::bad_alloc &) { pool_give(ix, b); std::free(h_id_off); std::free(h_ids); std::free(h_row_off); std::free(h_sa); return fail(PGI_ENOMEM, "out of host memory"); }
+}
+extern "C" void pgi_locate_result_free(pgi_locate_result *r) {
+    if (!r) return;
+    std::free(r->id_off); std::free(r->ids); std::free(r->row_off); std::free(r->sa);
+    std::memset(r, 0, sizeof(*r));
 }
 
 extern "C" int pgi_extend_batch(pgi_index *ix, uint64_t n, const pgi_bi_interval *in, const uint8_t *sym, const uint8_t *dir, pgi_bi_interval *out) {

@@ -37,6 +37,14 @@ struct SparseRankDev {
     uint64_t size, m; uint32_t shift, low_bytes;
 };
 
+// Bit-packed int_vector<0> as in the file; locate structures (toehold samples + phi).
+struct PackedDev { const uint64_t *words; uint64_t n; uint32_t width, pad; };
+struct LocDev {
+    SparseRankDev run_starts, last;     // first BWT row of every logical run; FastLocate::last
+    PackedDev samples, last_to_run;
+    uint64_t max_length;
+};
+
 struct TagDev {
     SparseRankDev iv;           // bwt_intervals
     const uint64_t *starts; uint64_t n_starts;
@@ -341,6 +349,46 @@ PGI_HD uint64_t sparse_rank1(const SparseRankDev &s, uint64_t i) {
     uint64_t r = lo;
     for (uint64_t j = lo; j < hi; ++j) r += sparse_low(s, j) < x;
     return r;
+}
+
+// Predecessor in a sparse set: index j of the last element <= x and its value; false when there is none.
+// Replaces sd_vector::predecessor (src/r-index.cpp:1370; blocks_start_pos for the run lookup of locate_encoded).
+PGI_HD bool sparse_pred(const SparseRankDev &s, uint64_t x, uint64_t &j, uint64_t &val) {
+    if (s.m == 0) return false;
+    if (x >= s.size) x = s.size - 1;
+    uint64_t b = x >> s.shift;
+    const uint64_t r = sparse_rank1(s, x + 1);            // elements <= x
+    if (r == 0) return false;
+    j = r - 1;
+    if (ld64(s.dir + b) > j) {                            // the element sits in an earlier bucket: last b' with dir[b'] <= j
+        uint64_t lo = 0, up = b - 1;
+        while (lo < up) { const uint64_t mid = (lo + up + 1) >> 1; if (ld64(s.dir + mid) <= j) lo = mid; else up = mid - 1; }
+        b = lo;
+    }
+    val = (b << s.shift) | sparse_low(s, j);
+    return true;
+}
+PGI_HD uint64_t packed_get(const PackedDev &p, uint64_t i) {   // 0 past the end (defined UB)
+    if (i >= p.n) return 0;
+    const uint64_t bit = i * p.width, w = bit >> 6; const uint32_t sh = (uint32_t) (bit & 63);
+    uint64_t v = ld64(p.words + w) >> sh;
+    if (sh + p.width > 64) v |= ld64(p.words + w + 1) << (64 - sh);
+    return p.width < 64 ? v & ((1ULL << p.width) - 1) : v;
+}
+// FastLocate::locateNext (phi), src/r-index.cpp:1369-1372.
+PGI_HD uint64_t locate_next(const LocDev &l, uint64_t prev) {
+    uint64_t j, val;
+    if (!sparse_pred(l.last, prev, j, val)) return 0;
+    return packed_get(l.samples, packed_get(l.last_to_run, j) + 1) + (prev - val);
+}
+// Head of FastLocate::locate_encoded (src/r-index.cpp:1308-1329): SA value of BWT row `row` from the sample of its
+// logical run plus one phi step per row between the run's first row and `row`.
+PGI_HD uint64_t locate_row(const LocDev &l, uint64_t row) {
+    uint64_t run = 0, start = 0;
+    if (!sparse_pred(l.run_starts, row, run, start)) return 0;
+    uint64_t v = packed_get(l.samples, run);
+    for (uint64_t p = start; p < row; ++p) v = locate_next(l, v);
+    return v;
 }
 
 // ------------------------------------------------------------------------------------ tag items

@@ -109,14 +109,25 @@ inline uint64_t bytecode_next(const uint8_t *&p, const uint8_t *end) {
 }
 
 // ---------------------------------------------------------------------------------- flat images
+struct SparseRankImage {
+    SparseRankConsts k; std::vector<uint64_t> dir; std::vector<uint8_t> low;
+};
+// A bit-packed sdsl::int_vector<0> kept exactly as in the file (+ 2 spare words: a 2-word read never leaves the array).
+struct PackedImage { std::vector<uint64_t> words; uint64_t n = 0; unsigned width = 0; };
+inline void pack_from_view(const IntVectorView &v, PackedImage &im) {
+    im.n = v.size(); im.width = v.width;
+    const size_t nw = (size_t) ((v.bits + 63) / 64);
+    im.words.assign(nw + 2, 0);
+    if (nw) std::memcpy(im.words.data(), v.payload, nw * 8);
+}
 struct RiImage {
     RiConsts k;                          // scalars + tables copied to the device as one struct
     std::vector<uint64_t> blocks;        // PGI_BLOCK_WORDS u64 per 64-byte block: one per bucket, then the chunk blocks
     std::vector<uint64_t> q_start, q_val;// quirk slot tables (legacy files with an absent nuc symbol)
     uint64_t n_file_runs = 0, n_ref_blocks = 0; bool encoded = false;
-};
-struct SparseRankImage {
-    SparseRankConsts k; std::vector<uint64_t> dir; std::vector<uint8_t> low;
+    // locate (toehold samples + phi), only when the file carries samples (pgi_layout.h: locate_ok)
+    SparseRankImage run_starts, last;    // first BWT row of every logical run; `last` (SA values at the last row of every run)
+    PackedImage samples, last_to_run;
 };
 struct TagImage {
     int layout = 0; SparseRankImage intervals;
@@ -305,16 +316,45 @@ inline void build_descriptors(RiImage &im, const bool present[6], bool legacy) {
     }
 }
 
+// ---------------------------------------------------------------------------------- sparse rank
+// Sorted set of positions in [0, size) -> bucket directory + per-element low parts (DESIGN.md).
+// for_each(f) must call f(j, position) for j = 0 .. ones - 1 in increasing order of position.
+template <typename ForEach>
+inline void build_sparse_rank_from(uint64_t size, uint64_t ones, ForEach &&for_each, SparseRankImage &im) {
+    SparseRankConsts &k = im.k; std::memset(&k, 0, sizeof(k));
+    k.size = size; k.m = ones;
+    unsigned S = 0;                              // about four elements per bucket
+    if (ones) while (S < 62 && (size >> S) > ones / 4 + 1) ++S;
+    else S = 62;
+    k.shift = S; k.low_bytes = S <= 8 ? 1 : S <= 16 ? 2 : S <= 32 ? 4 : 8;
+    const uint64_t nbuckets = (size >> S) + 1;
+    im.dir.assign(nbuckets + 1, 0);
+    im.low.assign((size_t) (ones * k.low_bytes + 16), 0);   // 16 spare bytes: vector loads may over-read
+    uint64_t prev = 0; bool first = true;
+    for_each([&](uint64_t j, uint64_t p) {
+        if (p >= size || (!first && p <= prev)) throw FormatError("sd_vector positions are not strictly increasing inside the universe");
+        first = false; prev = p;
+        im.dir[(p >> S) + 1]++;
+        uint64_t lowv = p & ((S >= 64) ? ~0ULL : ((1ULL << S) - 1));
+        std::memcpy(&im.low[(size_t) (j * k.low_bytes)], &lowv, k.low_bytes);
+    });
+    for (uint64_t b = 0; b < nbuckets; ++b) im.dir[b + 1] += im.dir[b];
+    k.n_buckets = nbuckets;
+}
+inline void build_sparse_rank(const SdVectorView &sd, SparseRankImage &im) {
+    build_sparse_rank_from(sd.size, sd.ones, [&](auto &&f) { sd.for_each_one(f); }, im);
+}
+
 // ---------------------------------------------------------------------------------- .ri
 inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
     Reader r(bytes, len);
     if (r.get<uint32_t>() != 0x6B3741D8u) throw FormatError("FastLocate: Invalid tag");       // r-index.hpp:85-115
     uint32_t version = r.get<uint32_t>();
     if (version != 1) throw FormatError("FastLocate: Expected v1, got v" + std::to_string(version));
-    (void) r.get<uint64_t>();                      // max_length
+    const uint64_t max_length = r.get<uint64_t>();
     const uint64_t flags = r.get<uint64_t>();
-    IntVectorView iv; SdVectorView sd;
-    iv.parse(r, 0); sd.parse(r); iv.parse(r, 0);   // samples, last, last_to_run: not on the find_mems path
+    IntVectorView iv, samples_v, ltr_v; SdVectorView last_v;
+    samples_v.parse(r, 0); last_v.parse(r); ltr_v.parse(r, 0);   // not on the find_mems path: kept for locate (below)
     iv.parse(r, 8);
     if (iv.size() != 256) throw FormatError("sym_map must have 256 entries");
     RiConsts &k = im.k; std::memset(&k, 0, sizeof(k));
@@ -332,6 +372,9 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
 
     RunCollector bb;
     im.n_file_runs = 0;
+    const bool want_locate = samples_v.size() > 0 && max_length > 0;
+    std::vector<uint64_t> run_start_pos;            // first row of every LOGICAL run (file record; never merged: each has its own sample)
+    if (want_locate) run_start_pos.reserve((size_t) samples_v.size());
     unsigned code_of[256]; for (int i = 0; i < 256; ++i) code_of[i] = 8;
     for (unsigned c = 0; c < 6; ++c) code_of[kNuc[c]] = c;
     auto check_block = [&](uint64_t b, const uint64_t *file_cum, unsigned ncum) {
@@ -353,6 +396,7 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
             for (uint64_t j = 0; j < nr; ++j) {
                 uint64_t sym = r.get<uint64_t>(), l = r.get<uint64_t>();
                 if (sym > 255 || code_of[sym] > 5) throw FormatError("BWT symbol outside {\\n,A,C,G,N,T} is not supported");
+                if (want_locate && l) run_start_pos.push_back(bb.lpos);
                 bb.add(code_of[sym], l); ++im.n_file_runs;
             }
         }
@@ -378,6 +422,7 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
                 uint8_t h = *p++; unsigned code = h >> 5; uint64_t l = (h & 31) + 1;
                 if ((h & 31) == 31) l = 32 + bytecode_next(p, end);
                 if (code > 5) throw FormatError("encoded run with symbol code > 5");
+                if (want_locate) run_start_pos.push_back(bb.lpos);
                 bb.add(code, l); ++im.n_file_runs;
             }
         }
@@ -388,33 +433,19 @@ inline void flatten_ri(const void *bytes, size_t len, RiImage &im) {
     build_buckets(im, bb.runs, k.n, totals);
     bool present[6]; for (unsigned c = 0; c < 6; ++c) present[c] = totals[c] != 0;
     build_descriptors(im, present, !im.encoded);
+    // locate: samples[run] = SA value at the first row of logical run `run`; phi through last / last_to_run
+    // (src/r-index.cpp:1300-1343, 1369-1372). On an encoded file without N the reference's run lookup skips six
+    // ByteCode values where five exist (:85-90) -- refused like count (pgi_layout.h).
+    k.max_length = max_length; k.locate_ok = 0;
+    if (want_locate && run_start_pos.size() == samples_v.size() && last_v.ones == ltr_v.size() && (!im.encoded || k.sigma == 6)) {
+        build_sparse_rank_from(k.n, run_start_pos.size(), [&](auto &&f) { for (uint64_t j = 0; j < run_start_pos.size(); ++j) f(j, run_start_pos[j]); }, im.run_starts);
+        build_sparse_rank(last_v, im.last);
+        pack_from_view(samples_v, im.samples); pack_from_view(ltr_v, im.last_to_run);
+        k.locate_ok = 1;
+    }
     if (!k.has_quirk) { im.q_start.clear(); im.q_val.clear(); }
     k.n_quirk = im.q_start.size();
     k.mem_tail = r.remaining();   // bytes after the index (0 for a well-formed file)
-}
-
-// ---------------------------------------------------------------------------------- sparse rank
-// Sorted set of positions in [0, size) -> bucket directory + per-element low parts (DESIGN.md).
-inline void build_sparse_rank(const SdVectorView &sd, SparseRankImage &im) {
-    SparseRankConsts &k = im.k; std::memset(&k, 0, sizeof(k));
-    k.size = sd.size; k.m = sd.ones;
-    unsigned S = 0;                              // about four elements per bucket
-    if (sd.ones) while (S < 62 && (sd.size >> S) > sd.ones / 4 + 1) ++S;
-    else S = 62;
-    k.shift = S; k.low_bytes = S <= 8 ? 1 : S <= 16 ? 2 : S <= 32 ? 4 : 8;
-    const uint64_t nbuckets = (sd.size >> S) + 1;
-    im.dir.assign(nbuckets + 1, 0);
-    im.low.assign((size_t) (sd.ones * k.low_bytes + 16), 0);   // 16 spare bytes: vector loads may over-read
-    uint64_t prev = 0; bool first = true;
-    sd.for_each_one([&](uint64_t j, uint64_t p) {
-        if (p >= sd.size || (!first && p <= prev)) throw FormatError("sd_vector positions are not strictly increasing inside the universe");
-        first = false; prev = p;
-        im.dir[(p >> S) + 1]++;
-        uint64_t lowv = p & ((S >= 64) ? ~0ULL : ((1ULL << S) - 1));
-        std::memcpy(&im.low[(size_t) (j * k.low_bytes)], &lowv, k.low_bytes);
-    });
-    for (uint64_t b = 0; b < nbuckets; ++b) im.dir[b + 1] += im.dir[b];
-    k.n_buckets = nbuckets;
 }
 
 // ---------------------------------------------------------------------------------- tags

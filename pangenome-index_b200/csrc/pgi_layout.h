@@ -69,7 +69,8 @@ typedef struct {
     // format with all weights zero. count_ok = 0: encoded file without N, on which the reference reads a run header as
     // a sixth cumulative (r-index.cpp:577) -- not reproduced, the count entry points refuse such an index.
     uint32_t desc_c[256];
-    uint32_t count_ok, pad2_;
+    uint32_t count_ok, locate_ok;   // locate_ok: the file carries samples and its run lookup is well defined in the reference
+    uint64_t max_length;            // Header::max_length: SA value = seq_id * max_length + seq_offset (r-index.hpp:424-431)
 } RiConsts;
 
 // Sorted set S of positions in [0,size): rank1(i) = |{p in S : p < i}|.

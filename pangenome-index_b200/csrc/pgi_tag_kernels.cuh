@@ -151,4 +151,36 @@ __global__ void gather_indep_kernel(const uint4 *buf, uint32_t n_slots, uint32_t
     if (acc == 0x12345u) atomicAdd(sink, 1ull);
 }
 
+// ------------------------------------------------------------------------------------ locate (toehold + phi)
+// FastLocate::locate_encoded (src/r-index.cpp:1300-1343), one thread per BWT range [first, second]: SA value of the first
+// row from the sample of its run, then one phi step (locateNext, :1369-1372) per further row -- an inherently serial
+// chain of four dependent random accesses per row; parallelism comes from the number of ranges in flight.
+// sa[row_off[i] + t] = SA value of row first + t; ids = the same divided by max_length (seqId, r-index.hpp:429).
+__global__ void locate_kernel(LocDev l, uint64_t n, const uint64_t *first, const uint64_t *second, const uint64_t *row_off,
+                              uint64_t *sa, uint64_t *ids) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t f = first[i], e = second[i];
+    if (e < f) return;
+    uint64_t o = row_off[i];
+    uint64_t v = locate_row(l, f);
+    sa[o] = v; ids[o] = v / l.max_length;
+    for (uint64_t r = f; r < e; ++r) { v = locate_next(l, v); ++o; sa[o] = v; ids[o] = v / l.max_length; }
+}
+// std::unique over the sorted ids of every range, in place; ucnt[i] = number kept.
+__global__ void locate_unique_kernel(uint64_t n, const uint64_t *row_off, uint64_t *ids, uint64_t *ucnt) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t a = row_off[i], b = row_off[i + 1];
+    uint64_t k = a;
+    for (uint64_t p = a; p < b; ++p) { const uint64_t x = ids[p]; if (k == a || ids[k - 1] != x) ids[k++] = x; }
+    ucnt[i] = k - a;
+}
+__global__ void locate_copy_kernel(uint64_t n, const uint64_t *row_off, const uint64_t *id_off, const uint64_t *ids, uint64_t *out) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t a = row_off[i], d = id_off[i], c = id_off[i + 1] - d;
+    for (uint64_t t = 0; t < c; ++t) out[d + t] = ids[a + t];
+}
+
 } // namespace pgi

@@ -7,6 +7,7 @@
 //     load / load_encoded             src/r-index.cpp:378-459
 //     backward/forward_extend[_encoded]   src/r-index.cpp:713-764, 1395-1428, 1500-1509
 //     count / count_encoded           include/pangenome_index/r-index.hpp:541-556 (LF / LF_encoded src/r-index.cpp:650-711)
+//     locate / locate_encoded, decompressSA / decompressDA, seqId / seqOffset   src/r-index.cpp:1300-1372
 //     bwt_size, is_encoded, complement, sym_map, C
 //   panindexer::TagArray              include/pangenome_index/tag_arrays.hpp:27-128 (query side only)
 //     load_compressed_tags[_compact]  src/tag_arrays.cpp:739-776
@@ -85,6 +86,34 @@ public:
         return out;
     }
     range_type count(std::string &pattern) const { return count_encoded(pattern); }
+
+    // FastLocate::locate_encoded, src/r-index.cpp:1300-1343: sorted unique sequence ids of the rows of `state`
+    // (toehold sample of the first row's run + one phi step per row). `first` must be NO_POSITION (the library finds the
+    // toehold itself). locate() forwards to it (the reference's legacy body is empty, :1281-1296).
+    static constexpr size_t NO_POSITION = ~(size_t) 0;                       // r-index.hpp:49
+    std::vector<size_t> locate_encoded(range_type state, size_t first = NO_POSITION) const {
+        if (!ix_) throw std::runtime_error("FastLocate: no index loaded");
+        if (first != NO_POSITION) throw std::runtime_error("FastLocate::locate_encoded: a caller-provided toehold is not supported");
+        const uint64_t a = state.first, b = state.second; pgi_locate_result r;
+        pgi_check(pgi_locate_batch(ix_, 1, &a, &b, &r));
+        std::vector<size_t> out(r.ids, r.ids + r.n_ids);
+        pgi_locate_result_free(&r);
+        return out;
+    }
+    std::vector<size_t> locate(range_type state, size_t first = NO_POSITION) const { return locate_encoded(state, first); }
+    // decompressSA / decompressDA, src/r-index.cpp:1345-1365: SA value (seq_id * max_length + seq_offset) / sequence id of every row.
+    std::vector<size_t> decompressSA() const {
+        if (!ix_) throw std::runtime_error("FastLocate: no index loaded");
+        if (!info_.n) return {};
+        const uint64_t a = 0, b = info_.n - 1; pgi_locate_result r;
+        pgi_check(pgi_locate_batch(ix_, 1, &a, &b, &r));
+        std::vector<size_t> out(r.sa, r.sa + r.n_rows);
+        pgi_locate_result_free(&r);
+        return out;
+    }
+    std::vector<size_t> decompressDA() const { auto v = decompressSA(); for (auto &x : v) x = seqId(x); return v; }
+    size_t seqId(size_t offset) const { return offset / info_.max_length; }     // r-index.hpp:429
+    size_t seqOffset(size_t offset) const { return offset % info_.max_length; } // r-index.hpp:431
 
     pgi_index *handle() const { return ix_; }
     const std::string &file_bytes() const { return bytes_; }

@@ -92,6 +92,21 @@ int sim_count(const sim_index *s, const char *read, uint64_t len, uint64_t *out2
     out2[0] = b.k; out2[1] = (uint64_t) b.s;
     return 0;
 }
+// SA values of rows [first, second] through locate_row / locate_next over the flattened samples (pgi_locate_batch's
+// arithmetic). Returns 0, or 1 when the index refuses locate.
+int sim_locate(const sim_index *s, uint64_t first, uint64_t second, uint64_t *sa_out) {
+    if (!s->ri.k.locate_ok) return 1;
+    LocDev l;
+    auto sr = [](const SparseRankImage &im, SparseRankDev &d) { d.dir = im.dir.data(); d.low = im.low.data(); d.size = im.k.size; d.m = im.k.m; d.shift = im.k.shift; d.low_bytes = im.k.low_bytes; };
+    sr(s->ri.run_starts, l.run_starts); sr(s->ri.last, l.last);
+    l.samples = PackedDev{s->ri.samples.words.data(), s->ri.samples.n, s->ri.samples.width, 0};
+    l.last_to_run = PackedDev{s->ri.last_to_run.words.data(), s->ri.last_to_run.n, s->ri.last_to_run.width, 0};
+    l.max_length = s->ri.k.max_length;
+    if (second < first) return 0;
+    uint64_t v = locate_row(l, first); *sa_out++ = v;
+    for (uint64_t r = first; r < second; ++r) { v = locate_next(l, v); *sa_out++ = v; }
+    return 0;
+}
 // one tag query through tag_plan + item decoders; returns number_of_runs, *n_out sorted unique values written (<= cap)
 uint64_t sim_tag_query(const sim_index *s, uint64_t start, uint64_t end, uint64_t *out, uint64_t cap, uint64_t *n_out) {
     TagPlan p = tag_plan(s->td, start, end);

@@ -36,6 +36,9 @@ def lib():
                                      ctypes.POINTER(OrcResult)]
         L.orc_format_query_tags.restype = ctypes.c_void_p
         L.orc_format_query_tags.argtypes = [ctypes.POINTER(OrcResult), ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint64)]
+        L.orc_locate_batch.restype = ctypes.c_uint64
+        L.orc_locate_batch.argtypes = [ctypes.c_void_p, ctypes.c_uint64] + [ctypes.c_void_p] * 4 + [ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64]
+        L.orc_decompress_sa.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.orc_result_free.argtypes = [ctypes.POINTER(OrcResult)]
         L.orc_format_text.restype = ctypes.c_void_p
         L.orc_format_text.argtypes = [ctypes.POINTER(OrcResult), ctypes.c_uint64, ctypes.c_int, ctypes.POINTER(ctypes.c_uint64)]
@@ -127,6 +130,19 @@ def _query_tags(self, reads, read_off, with_tags=None, threads=0, text=True):
     lib().orc_result_free(ctypes.byref(res))
     return out
 Index.query_tags = _query_tags
+
+def _locate_batch(self, first, second, want_sa=False):
+    """locate_encoded (r-index.cpp:1300-1343) per range -> (offsets [n+1], sorted unique sequence ids[, SA values row by row])."""
+    first = np.ascontiguousarray(first, dtype=np.uint64); second = np.ascontiguousarray(second, dtype=np.uint64)
+    n = len(first); sizes = np.where(second >= first, second - first + np.uint64(1), 0).astype(np.uint64); tot = int(sizes.sum())
+    off = np.zeros(n + 1, dtype=np.uint64); out = np.zeros(max(1, tot), dtype=np.uint64); sa = np.zeros(max(1, tot), dtype=np.uint64)
+    k = lib().orc_locate_batch(self.h, n, first.ctypes.data, second.ctypes.data, off.ctypes.data, out.ctypes.data, tot,
+                               sa.ctypes.data if want_sa else None, tot)
+    return (off, out[:k].copy(), sa[:tot].copy()) if want_sa else (off, out[:k].copy())
+def _decompress_sa(self):
+    out = np.zeros(self.n, dtype=np.uint64); lib().orc_decompress_sa(self.h, out.ctypes.data); return out
+Index.locate_batch = _locate_batch
+Index.decompress_sa = _decompress_sa
 
 def pack_reads(reads):
     """list of bytes -> (uint8 concatenation, uint64 offsets)."""

@@ -23,6 +23,7 @@ def lib():
         L.sim_tag_query.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_uint64,
                                     ctypes.POINTER(ctypes.c_uint64)]
         L.sim_count.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
+        L.sim_locate.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -57,6 +58,12 @@ class Index:
         if lib().sim_count(self.h, read, len(read), out.ctypes.data):
             return None
         return int(out[0]), int(out[1])
+    def locate(self, first, second):
+        """SA values of BWT rows [first, second], or None when the index refuses locate."""
+        out = np.zeros(max(1, second - first + 1), dtype=np.uint64)
+        if lib().sim_locate(self.h, first, second, out.ctypes.data):
+            return None
+        return out[: max(0, second - first + 1)]
     def tag_query(self, start, end, cap=1 << 20):
         out = np.zeros(cap, dtype=np.uint64); n = ctypes.c_uint64()
         nr = lib().sim_tag_query(self.h, start, end, out.ctypes.data, cap, ctypes.byref(n))

@@ -269,3 +269,43 @@ def test_long_reads_with_indel_errors(capi):
     mr, mo = orc.pack_reads(mixed)
     compare(g.find_mems(mr, mo, 12, 2), o.find_mems(mr, mo, 12, 2), True)
     compare_query_tags(g.query_tags(mr, mo), o.query_tags(mr, mo), True)
+
+@pytest.mark.parametrize("name", ["xy_legacy", "synth_enc", "synth_enc_big"])
+def test_locate_batch(capi, name):
+    """SURVEY.md §8 f2: pgi_locate_batch = FastLocate::locate_encoded (toehold sample + phi) against the oracle; SA values
+    row by row against decompressSA; sorted unique sequence ids; empty ranges; refusals."""
+    prep = load_package().prep
+    if name == "xy_legacy": ri = datasets.gold("xy.ri")
+    elif name == "synth_enc": ri, _ = prep.rindex_from_rlbwt(datasets.synth_index()["rl_bwt"], encoded=True, with_samples=True)
+    else: ri, _ = prep.rindex_from_rlbwt(datasets.synth_index(ref_len=20000, n_hap=8, seed=21)["rl_bwt"], encoded=True, with_samples=True)
+    o = orc.Index(ri); g = capi.Index(ri); n = o.n
+    assert g.info["has_locate"] == 1 and g.info["max_length"] == o.info[5]
+    sa = o.decompress_sa()
+    rng = np.random.default_rng(4); N = 20000
+    a = rng.integers(0, n, N).astype(np.uint64); ln = np.where(rng.random(N) < 0.9, rng.integers(1, 50, N), rng.integers(50, 600, N)).astype(np.uint64)
+    b = np.minimum(a + ln - 1, np.uint64(n - 1)); b[:50] = a[:50] - np.uint64(1) * (a[:50] > 0)      # empty (second < first) where a > 0
+    a[50] = 0; b[50] = n - 1                                                                        # the whole BWT
+    id_off, ids, row_off, rows = g.locate_batch(a, b)
+    sizes = np.where(b >= a, b - a + 1, 0).astype(np.int64)
+    assert np.array_equal(np.diff(row_off.astype(np.int64)), sizes)
+    idx = np.repeat(a.astype(np.int64), sizes) + (np.arange(int(sizes.sum())) - np.repeat(row_off[:-1].astype(np.int64), sizes))
+    assert np.array_equal(rows, sa[idx])                                                            # every row of every range
+    k = 3000
+    ooff, oids = o.locate_batch(a[:k], b[:k])
+    assert np.array_equal(id_off[: k + 1], ooff) and np.array_equal(ids[: int(ooff[-1])], oids)
+    for i in rng.integers(0, N, 200):
+        assert np.array_equal(ids[id_off[i]:id_off[i + 1]], np.unique(sa[int(a[i]):int(b[i]) + 1] // np.uint64(o.info[5]))), i
+    e = g.locate_batch(np.zeros(0, np.uint64), np.zeros(0, np.uint64)); assert len(e[1]) == 0 and len(e[3]) == 0
+    with pytest.raises(capi.PgiError): g.locate_batch([0], [n])                                     # beyond the BWT
+    with pytest.raises(capi.PgiError): capi.Index(datasets.synth_index()["ri"]).locate_batch([0], [1])   # file without samples
+    # the FMD interval of a read and its located sequences agree with the text
+    if name != "xy_legacy":
+        text = datasets.synth_index(ref_len=20000, n_hap=8, seed=21)["text"] if name == "synth_enc_big" else datasets.synth_index()["text"]
+        seqs = text.split(b"\n")[:-1]
+        reads, off = datasets.sample_reads(text, 300, 25, 0.0, seed=8)
+        q = g.query_tags(reads, off, text=False)["mems"]
+        hit = q[:, 3] > 0
+        lo, li, _, _ = g.locate_batch(q[hit, 2], q[hit, 2] + q[hit, 3] - np.uint64(1))
+        for j, i in enumerate(np.nonzero(hit)[0][:100]):
+            rd = reads[i * 25:(i + 1) * 25].tobytes()
+            assert list(li[lo[j]:lo[j + 1]]) == [s for s in range(len(seqs)) if rd in seqs[s]], i

@@ -94,3 +94,24 @@ def test_count_matches_oracle(name):
         assert got == (int(R["mems"][i, 2]), int(R["mems"][i, 3])), (i, rd)
         hits += got[1] > 0
     assert hits > 100
+
+@pytest.mark.parametrize("name", ["xy_legacy", "two_contig_legacy", "synth_enc", "synth_leg"])
+def test_locate_matches_oracle(name):
+    """Locate (toehold sample of the run + phi steps) over the flattened samples / last / last_to_run against the oracle's
+    locate_encoded / decompressSA; refused on an encoded file without N and on files without samples."""
+    from conftest import load_package
+    prep = load_package().prep
+    if name == "xy_legacy": ri = datasets.gold("xy.ri")
+    elif name == "two_contig_legacy": ri = datasets.gold("two_contig_xy.ri")
+    else: ri, _ = prep.rindex_from_rlbwt(datasets.synth_index()["rl_bwt"], encoded=name == "synth_enc", with_samples=True)
+    o = orc.Index(ri); g = sim.Index(ri); sa = o.decompress_sa()
+    assert np.array_equal(g.locate(0, o.n - 1), sa)
+    rng = np.random.default_rng(9)
+    for _ in range(500):
+        a = int(rng.integers(0, o.n)); b = min(o.n - 1, a + int(rng.integers(0, 60)))
+        _, _, rows = o.locate_batch([a], [b], want_sa=True)
+        assert np.array_equal(g.locate(a, b), rows) and np.array_equal(rows, sa[a:b + 1]), (a, b)
+    assert sim.Index(datasets.synth_index()["ri"]).locate(0, 3) is None                 # built without samples
+    s5 = datasets.synth_index(ref_len=2000, n_hap=2, seed=3, encoded=True, n_N=0)
+    ri5, _ = prep.rindex_from_rlbwt(s5["rl_bwt"], encoded=True, with_samples=True)
+    assert sim.Index(ri5).locate(0, 3) is None                                           # encoded, sigma 5

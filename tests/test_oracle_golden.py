@@ -119,3 +119,28 @@ def test_x_index_rebuilt_from_rl_bwt():
     for pat in (b"GA", b"CAG", b"AAGC"):                        # T-free patterns count true occurrences
         cnt = sum(1 for i in range(len(text)) if text.startswith(pat, i))
         assert o.search(pat)[2] == cnt, pat
+
+def naive_suffix_order(text: bytes):
+    """(sequence id, offset in the sequence) of every BWT row: the rotation sort of tests/test_rindex.cpp:35-99."""
+    arr, seq, offs = [], [], []; k = sid = o = 0
+    for ch in text:
+        seq.append(sid); offs.append(o)
+        if ch == 10: arr.append(k); k += 1; sid += 1; o = 0
+        else: arr.append(ch + 1000); o += 1
+    n = len(arr); dbl = arr + arr
+    order = sorted(range(n), key=lambda i: dbl[i:i + n])
+    return np.array([seq[i] for i in order], dtype=np.uint64), np.array([offs[i] for i in order], dtype=np.uint64)
+
+@pytest.mark.parametrize("ri,text", [("xy.ri", "contigs_xy"), ("two_contig_xy.ri", "contigs_XY.txt")])
+def test_decompress_da_of_shipped_ri_equals_naive_document_array(ri, text):
+    """The reference's own locate tests (tests/test_rindex.cpp:103-244) assert decompressDA() == the document array of a
+    naive rotation sort. Same assertion for the oracle's getSample / locateNext / seqId on the SHIPPED .ri files and texts
+    (plus the offsets, which the reference's test does not look at): pins the locate restatement."""
+    o = orc.Index(datasets.gold(ri)); ml = o.info[5]
+    sa = o.decompress_sa(); ids, offs = naive_suffix_order(datasets.gold(text))
+    assert np.array_equal(sa // np.uint64(ml), ids) and np.array_equal(sa % np.uint64(ml), offs)
+    off, uids, rows = o.locate_batch(np.arange(o.n), np.arange(o.n), want_sa=True)      # every row through locate_encoded's run lookup
+    assert np.array_equal(rows, sa) and np.array_equal(uids, ids)
+    off, uids = o.locate_batch([0, 7, 100, 5, 9], [o.n - 1, 7, 180, 4, 8])
+    assert np.array_equal(uids[off[0]:off[1]], np.unique(ids)) and uids[off[1]] == ids[7] and off[4] == off[3]
+    assert np.array_equal(uids[off[2]:off[3]], np.unique(ids[100:181]))
