@@ -238,6 +238,23 @@ def main():
     G = ix.find_mems(reads_np[: ns * L], offs, args.min_len, args.min_occ, text=False)
     parity = bool(G["n_mems"] == R["n_mems"] and np.array_equal(G["mems"], R["mems"]) and np.array_equal(G["tags"], R["tags"])
                   and np.array_equal(G["n_runs"], R["n_runs"]) and G["extensions"] == R["counters"]["E"])
+    # ---- next row of the scope table, reported beside the headline, not part of it: the query_tags path
+    # (whole-read count_encoded + tag query of the final range) on the same reads, device-resident, with its own parity check
+    next_rows = {}
+    try:
+        qs = []
+        for i in range(2 + 3):
+            batch.set_device_reads(d_reads[i % pool].data_ptr(), d_off.data_ptr(), n, n * L)
+            batch.run_query_tags()
+            if i >= 2: qs.append((batch.stage_ms()[5], batch.device_result().extensions))
+        QG = ix.query_tags(reads_np[: ns * L], offs, text=False); QR = o.query_tags(reads_np[: ns * L], offs, text=False, threads=host_threads())
+        q_par = bool(np.array_equal(QG["mems"], QR["mems"]) and np.array_equal(QG["tags"], QR["tags"]) and np.array_equal(QG["n_runs"], QR["n_runs"]))
+        q_ms = float(np.median([x[0] for x in qs]))
+        next_rows["query_tags"] = {"reads_per_s": n / (q_ms * 1e-3), "ms_per_step": q_ms, "lf_steps_per_read": qs[-1][1] / n,
+                                   "matched_fraction": float((QR["mems"][:, 3] > 0).mean()), "parity_sample": "%d reads bit-exact vs oracle: %s" % (ns, q_par),
+                                   "cpu_port_reads_per_s": ns / QR["seconds"], "note": "150 bp reads with 1 % errors searched whole (right to left until the range is empty)"}
+    except Exception as e:
+        next_rows["query_tags"] = {"error": str(e)}
     c = R["counters"]; d_per_e = c["D"] / max(1, c["E"])
     cpu = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, args.cpu_seconds, count_work=False)
     cores = host_threads()
@@ -287,6 +304,7 @@ def main():
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
             "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",
                              "sample": "%d reads of the same batch in %.1f s, %d OpenMP threads (oracle/ restatement; the reference itself is single-threaded)" % (cpu["reads"], cpu["seconds"], cores)},
+            "next_rows": next_rows,
             "clocks": sampler.summary()}
     print(json.dumps(line), flush=True)
     if world > 1: dist.destroy_process_group()
