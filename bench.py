@@ -160,7 +160,8 @@ def main():
     w = make_workload(args, local, rank)
     t0 = time.time()
     ix = capi.Index(w["ri"], w["tags"], w["layout"], device=local)
-    if rank == 0: log("index on device: %.1f MB in %.1fs" % (ix.info["device_bytes"] / 1e6, time.time() - t0), ix.info)
+    index_create_s = time.time() - t0                       # parse + flatten on the host + upload: excluded from every timed region (SURVEY §8 d)
+    if rank == 0: log("index on device: %.1f MB in %.1fs" % (ix.info["device_bytes"] / 1e6, index_create_s), ix.info)
     L = args.read_len; n = args.reads_per_step; pool = w["reads"].shape[0]
     d_off = torch.arange(n + 1, dtype=torch.int64, device="cuda") * L
     stream = torch.cuda.current_stream()
@@ -255,6 +256,17 @@ def main():
                                    "cpu_port_reads_per_s": ns / QR["seconds"], "note": "150 bp reads with 1 % errors searched whole (right to left until the range is empty)"}
     except Exception as e:
         next_rows["query_tags"] = {"error": str(e)}
+    # ---- text formatting (src/find_mems.cpp:115-139 stdout grammar): host-bound, reported separately (SURVEY §8 d)
+    fmt = {}
+    try:
+        import ctypes
+        r = ix.find_mems_raw(h_reads[0].data_ptr(), h_off.data_ptr(), n, args.min_len, args.min_occ)
+        ln = ctypes.c_uint64(); t1 = time.perf_counter()
+        ptxt = capi.lib().pgi_format_text(ctypes.byref(r), 1, 1, ctypes.byref(ln)); t_fmt = time.perf_counter() - t1
+        capi.lib().pgi_free(ptxt); ix.result_free(r)
+        fmt = {"reads_per_s": n / t_fmt, "text_bytes_per_step": int(ln.value), "threads": 1, "note": "pgi_format_text, one host thread; not inside value / e2e"}
+    except Exception as e:
+        fmt = {"error": str(e)}
     c = R["counters"]; d_per_e = c["D"] / max(1, c["E"])
     cpu = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, args.cpu_seconds, count_work=False)
     cores = host_threads()
@@ -304,6 +316,7 @@ def main():
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
             "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",
                              "sample": "%d reads of the same batch in %.1f s, %d OpenMP threads (oracle/ restatement; the reference itself is single-threaded)" % (cpu["reads"], cpu["seconds"], cores)},
+            "index_create_s": round(index_create_s, 2), "text_format": fmt,
             "next_rows": next_rows,
             "clocks": sampler.summary()}
     print(json.dumps(line), flush=True)
