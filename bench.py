@@ -17,6 +17,18 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 
+# stdout carries exactly ONE line, the JSON: file descriptor 1 is pointed at stderr for the whole run (NCCL, for one, prints
+# its version banner to stdout when the first communicator comes up) and the line is written to the saved descriptor.
+_JSON_OUT = None
+def emit_json(line):
+    out = _JSON_OUT if _JSON_OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n"); out.flush()
+def capture_stdout():
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w"); os.dup2(2, 1)
+
 def log(*a):
     print("[bench]", *a, file=sys.stderr, flush=True)
 
@@ -138,9 +150,10 @@ def run_reference(args, rank, world):
                        "note": "the reference's own find_mems is single-threaded and cannot be built here (SDSL/GBWT absent): this is the CPU restatement in oracle/, parallelised over reads with OpenMP"},
             "cpu_baseline": {"value": rate, "unit": "reads/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": rate, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit_json(line)
 
 def main():
+    capture_stdout()
     args = parse_args()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
     if args.impl == "reference":
@@ -319,7 +332,7 @@ def main():
             "index_create_s": round(index_create_s, 2), "text_format": fmt,
             "next_rows": next_rows,
             "clocks": sampler.summary()}
-    print(json.dumps(line), flush=True)
+    emit_json(line)
     if world > 1: dist.destroy_process_group()
 
 if __name__ == "__main__":
