@@ -95,6 +95,32 @@ int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **out);
 void pgi_index_free(pgi_index *);
 int pgi_index_info(const pgi_index *, pgi_index_info_t *out);
 
+/* ---- Cached flattened index image.
+ * Replaces MemoryMappedIndexManager / ChunkedMemoryMappedIndexManager::open (src/find_mems_memory_mapped.cpp:36-45,
+ * src/find_mems_chunked.cpp:29-50: the .ri / .tags files are mmap'ed, whole or in chunks of chunk_size_mb, instead of
+ * being deserialised). Here the SDSL files are flattened once into the device layout and written as ONE image file;
+ * opening it maps the file read-only and streams it to HBM through two pinned staging buffers of chunk_bytes: no
+ * parsing, no host copy of the index, host memory bounded by 2 x chunk_bytes however large the index. */
+typedef struct {
+    uint64_t file_bytes, payload_bytes;
+    uint64_t n, sigma, n_dev_blocks, bucket_shift, is_encoded;
+    uint64_t has_ri, has_tags, tag_layout, has_locate;
+    uint64_t src_ri_bytes, src_tag_bytes;   /* sizes of the files the image was made from                              */
+    uint64_t src_ri_sum, src_tag_sum;       /* pgi_image_source_sum of those files (staleness check)                    */
+    uint64_t chunk_bytes, chunks_copied;    /* filled by pgi_index_open_image only                                      */
+} pgi_image_info_t;
+/* Host-only: flatten the files (same arguments as pgi_index_create) and write the image to `path` (atomically:
+ * path.tmp + rename). Needs no CUDA device. */
+int pgi_image_write(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len, int tag_layout, const char *path);
+/* Host-only: validate the header of an image (verify != 0: also the checksum of every section) and describe it. */
+int pgi_image_info(const char *path, int verify, pgi_image_info_t *out);
+/* Cheap content stamp of a source file (FNV-1a over its first and last 64 KiB); compared with src_*_sum. */
+uint64_t pgi_image_source_sum(const void *bytes, size_t len);
+/* Map an image and upload it to GPU `device`. chunk_bytes = 0: 64 MiB (the reference's chunk_size_mb argument, in
+ * bytes). verify != 0 (or PGI_IMAGE_VERIFY=1): check every section checksum first. The resulting index is
+ * indistinguishable from one made by pgi_index_create from the same files. `info` may be NULL. */
+int pgi_index_open_image(const char *path, int device, uint64_t chunk_bytes, int verify, pgi_index **out, pgi_image_info_t *info);
+
 /* Batched FastLocate::backward_extend_encoded (src/r-index.cpp:713-756) / forward_extend_encoded
  * (:758-764): out[i] = extend(in[i], sym[i]); dir[i] 0 = backward, 1 = forward. Host buffers. */
 int pgi_extend_batch(pgi_index *, uint64_t n, const pgi_bi_interval *in, const uint8_t *sym,

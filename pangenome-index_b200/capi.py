@@ -10,7 +10,8 @@ _lib = None
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
-           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free"]
+           "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
+           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -25,6 +26,11 @@ class IndexInfo(ctypes.Structure):
 class LocateResult(ctypes.Structure):
     _fields_ = [("n", ctypes.c_uint64), ("n_ids", ctypes.c_uint64), ("n_rows", ctypes.c_uint64), ("id_off", ctypes.c_void_p),
                 ("ids", ctypes.c_void_p), ("row_off", ctypes.c_void_p), ("sa", ctypes.c_void_p)]
+
+class ImageInfo(ctypes.Structure):
+    _fields_ = [(k, ctypes.c_uint64) for k in ["file_bytes", "payload_bytes", "n", "sigma", "n_dev_blocks", "bucket_shift", "is_encoded", "has_ri",
+                                               "has_tags", "tag_layout", "has_locate", "src_ri_bytes", "src_tag_bytes", "src_ri_sum", "src_tag_sum",
+                                               "chunk_bytes", "chunks_copied"]]
 
 class PgiError(RuntimeError):
     pass
@@ -69,6 +75,10 @@ def lib():
         L.pgi_format_query_tags_text.argtypes = [ctypes.POINTER(Result), u64, ctypes.POINTER(u64)]
         L.pgi_host_alloc.restype = vp; L.pgi_host_alloc.argtypes = [ctypes.c_size_t]; L.pgi_host_free.argtypes = [vp]
         L.pgi_random_access_gbs.argtypes = [i32, u64, ctypes.c_uint32, u64, i32, ctypes.POINTER(ctypes.c_double)]
+        L.pgi_image_write.argtypes = [vp, ctypes.c_size_t, vp, ctypes.c_size_t, i32, ctypes.c_char_p]
+        L.pgi_image_info.argtypes = [ctypes.c_char_p, i32, ctypes.POINTER(ImageInfo)]
+        L.pgi_image_source_sum.restype = u64; L.pgi_image_source_sum.argtypes = [vp, ctypes.c_size_t]
+        L.pgi_index_open_image.argtypes = [ctypes.c_char_p, i32, u64, i32, ctypes.POINTER(vp), ctypes.POINTER(ImageInfo)]
         _lib = L
     return _lib
 
@@ -93,8 +103,26 @@ def _result_to_dict(res, L, with_tags, text=True):
         out["text"] = ctypes.string_at(p, ln.value); L.pgi_free(p)
     return out
 
+def image_write(ri: bytes, tags: bytes, tag_layout, path):
+    """Flatten the SDSL files on the host and write the cached device image (no GPU needed)."""
+    _ck(lib().pgi_image_write(ri, len(ri) if ri else 0, tags, len(tags) if tags else 0, tag_layout, os.fsencode(path)))
+
+def image_info(path, verify=False):
+    f = ImageInfo(); _ck(lib().pgi_image_info(os.fsencode(path), int(verify), ctypes.byref(f)))
+    return {k: getattr(f, k) for k, _ in ImageInfo._fields_}
+
+def image_source_sum(data: bytes):
+    return lib().pgi_image_source_sum(data, len(data))
+
 class Index:
     """Device-resident index (FastLocate + optional TagArray) on one GPU."""
+    @classmethod
+    def open_image(cls, path, device=0, chunk_bytes=0, verify=False):
+        """mmap a cached image and stream it to HBM in chunks (the memory-mapped / chunked index managers of the reference)."""
+        h = ctypes.c_void_p(); f = ImageInfo()
+        _ck(lib().pgi_index_open_image(os.fsencode(path), device, chunk_bytes, int(verify), ctypes.byref(h), ctypes.byref(f)))
+        ix = cls(None, device=device, _handle=h); ix.image = {k: getattr(f, k) for k, _ in ImageInfo._fields_}
+        return ix
     def __init__(self, ri: bytes, tags: bytes = None, tag_layout=0, device=0, _handle=None):
         L = lib(); self.device = device
         if _handle is not None:

@@ -12,6 +12,7 @@
 #include <vector>
 #include "../../include/pgi.h"
 #include "pgi_flatten.hpp"
+#include "pgi_image.hpp"
 #include "pgi_tag_kernels.cuh"
 
 using namespace pgi;
@@ -99,86 +100,198 @@ static int check_device(int device) {
     return 0;
 }
 
-static void fill_info(pgi_index *ix, const RiImage &ri, const TagImage *tg, uint64_t bytes) {
+static void fill_info(pgi_index *ix, const ImageMeta &m, uint64_t bytes) {
     pgi_index_info_t &f = ix->info; std::memset(&f, 0, sizeof(f));
-    f.n = ri.k.n; f.sigma = ri.k.sigma; f.is_encoded = ri.encoded; f.n_ref_blocks = ri.n_ref_blocks; f.n_runs = ri.n_file_runs;
-    f.n_dev_blocks = ri.k.n_blocks; f.bucket_shift = ri.k.bshift; f.n_crowded_buckets = ri.k.n_dir_blocks; f.has_quirk_slot = ri.k.has_quirk;
-    if (tg) {
-        f.has_tags = 1; f.tag_layout = (uint64_t) tg->layout; f.tag_runs = tg->intervals.k.m; f.tag_items = tg->n_items;
-        f.tag_item_width = tg->width; f.tag_universe = tg->intervals.k.size;
+    f.n = m.k.n; f.sigma = m.k.sigma; f.is_encoded = m.encoded; f.n_ref_blocks = m.n_ref_blocks; f.n_runs = m.n_file_runs;
+    f.n_dev_blocks = m.k.n_blocks; f.bucket_shift = m.k.bshift; f.n_crowded_buckets = m.k.n_dir_blocks; f.has_quirk_slot = m.k.has_quirk;
+    if (m.has_tags) {
+        f.has_tags = 1; f.tag_layout = m.tag_layout; f.tag_runs = m.iv_k.m; f.tag_items = m.tag_n_items;
+        f.tag_item_width = m.tag_width; f.tag_universe = m.iv_k.size;
     }
-    f.device_bytes = bytes; f.has_locate = ri.k.locate_ok; f.max_length = ri.k.max_length;
-    for (int i = 0; i < 8; ++i) f.C[i] = ri.k.C[i];
-    std::memcpy(f.sym_map, ri.k.sym_map, 256);
+    f.device_bytes = bytes; f.has_locate = m.k.locate_ok; f.max_length = m.k.max_length;
+    for (int i = 0; i < 8; ++i) f.C[i] = m.k.C[i];
+    std::memcpy(f.sym_map, m.k.sym_map, 256);
 }
 
-extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
-                                int tag_layout, int device, pgi_index **out) {
-    if ((!ri_bytes && !tag_bytes) || !out) return fail(PGI_EINVAL, "null argument");
-    if (int rc = check_device(device)) return rc;
-    pgi_index *ix = nullptr;
+// Host -> HBM copy of one section. chunk == 0: one cudaMemcpy (the source is ordinary process memory). chunk > 0: the
+// source is a file mapping; it is copied through two pinned staging buffers of `chunk` bytes, the memcpy out of the page
+// cache (page faults, read-ahead) of chunk i + 1 overlapping the DMA of chunk i. Host memory stays at 2 x chunk however
+// large the index is -- the role of chunk_size_mb in the reference's ChunkedMemoryMappedIndexManager
+// (src/find_mems_chunked.cpp:29-43).
+struct Stager {
+    size_t chunk = 0; void *pin[2] = {nullptr, nullptr}; cudaEvent_t done[2]; cudaStream_t st = nullptr; int turn = 0; bool ok = false;
+    uint64_t chunks = 0;
+    void init(size_t chunk_bytes) {
+        chunk = chunk_bytes;
+        if (!chunk) return;
+        CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) { CK(cudaHostAlloc(&pin[i], chunk, cudaHostAllocDefault)); CK(cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming)); }
+        ok = true;
+    }
+    void copy(void *dst, const void *src, size_t bytes) {
+        if (!chunk) { CK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice)); return; }
+        for (size_t at = 0; at < bytes; at += chunk) {
+            const size_t n = std::min(chunk, bytes - at);
+            CK(cudaEventSynchronize(done[turn]));                       // the buffer's previous DMA has drained
+            std::memcpy(pin[turn], (const char *) src + at, n);
+            CK(cudaMemcpyAsync((char *) dst + at, pin[turn], n, cudaMemcpyHostToDevice, st));
+            CK(cudaEventRecord(done[turn], st));
+            turn ^= 1; ++chunks;
+        }
+    }
+    void finish() { if (chunk && st) CK(cudaStreamSynchronize(st)); }
+    ~Stager() {
+        if (!ok) { if (st) cudaStreamDestroy(st); for (int i = 0; i < 2; ++i) if (pin[i]) cudaFreeHost(pin[i]); return; }
+        cudaStreamSynchronize(st);
+        for (int i = 0; i < 2; ++i) { cudaFreeHost(pin[i]); cudaEventDestroy(done[i]); }
+        cudaStreamDestroy(st);
+    }
+};
+
+// Allocate + fill the device copy of every section of a flattened index (fresh from flatten_ri / flatten_tags, or a
+// mapped image file) and wire the device structs. Throws CudaError.
+static pgi_index *upload_view(const IndexView &v, int device, size_t chunk_bytes, uint64_t *chunks_out) {
+    DeviceGuard g(device);
+    pgi_index *ix = new pgi_index();
     try {
-        RiImage ri; TagImage tg; bool has_tags = tag_bytes && tag_len;
-        std::memset(&ri.k, 0, sizeof(ri.k));
-        if (ri_bytes) flatten_ri(ri_bytes, ri_len, ri);
-        if (has_tags) flatten_tags(tag_bytes, tag_len, tag_layout, tg);
-        DeviceGuard g(device);
-        ix = new pgi_index(); ix->device = device; ix->consts = ri.k; ix->has_ri = ri_bytes != nullptr;
+        const ImageMeta &m = v.m;
+        ix->device = device; ix->consts = m.k; ix->has_ri = m.has_ri != 0;
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         uint64_t bytes = 0;
-        RiDev &d = ix->ri;
-        d.blocks = upload(ri.blocks, ix->owned, bytes); ix->n_block_words = ri.blocks.size();
-        d.q_start = upload(ri.q_start, ix->owned, bytes); d.q_val = upload(ri.q_val, ix->owned, bytes); ix->n_quirk = ri.q_start.size();
-        d.n = ri.k.n; d.n_blocks = ri.k.n_blocks; d.n_quirk = ri.k.n_quirk; d.bshift = ri.k.bshift; d.has_quirk = ri.k.has_quirk;
-        for (int i = 0; i < 8; ++i) d.C[i] = ri.k.C[i];
+        Stager stg; stg.init(chunk_bytes);
+        auto up = [&](int s, uint64_t &n_elems) -> void * {
+            const uint64_t nb = v.bytes[s]; n_elems = nb / kSectionElem[s];
+            void *d = nullptr; const size_t alloc = nb ? (size_t) nb : kSectionElem[s];
+            CK(cudaMalloc(&d, alloc)); ix->owned.push_back(d); bytes += alloc;
+            if (nb) stg.copy(d, v.ptr[s], (size_t) nb); else CK(cudaMemset(d, 0, alloc));
+            return d;
+        };
+        RiDev &d = ix->ri; uint64_t nq2 = 0;
+        d.blocks = (const uint64_t *) up(SEC_BLOCKS, ix->n_block_words);
+        d.q_start = (const uint64_t *) up(SEC_Q_START, ix->n_quirk); d.q_val = (const uint64_t *) up(SEC_Q_VAL, nq2);
+        d.n = m.k.n; d.n_blocks = m.k.n_blocks; d.n_quirk = m.k.n_quirk; d.bshift = m.k.bshift; d.has_quirk = m.k.has_quirk;
+        for (int i = 0; i < 8; ++i) d.C[i] = m.k.C[i];
         std::vector<uint32_t> desc(PGI_DESC_WORDS);      // 512 descriptors, then their 512 x 4 scan tables (pos_rank)
-        for (int i = 0; i < 256; ++i) { desc[i] = ri.k.desc_b[i]; desc[256 + i] = ri.k.desc_f[i]; }
+        for (int i = 0; i < 256; ++i) { desc[i] = m.k.desc_b[i]; desc[256 + i] = m.k.desc_f[i]; }
         for (int i = 0; i < 512; ++i) {
             const ScanTab t = scan_tab(desc[i] & 0xFFFFFFu);
             desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
         }
         ix->d_desc = upload(desc, ix->owned, bytes);
         for (int i = 0; i < 512; ++i) {                    // the count bank in the same shape (both halves: the kernel never asks for "forward")
-            desc[i] = ri.k.desc_c[i & 255];
+            desc[i] = m.k.desc_c[i & 255];
             const ScanTab t = scan_tab(desc[i] & 0xFFFFFFu);
             desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w;
         }
         ix->d_desc_c = upload(desc, ix->owned, bytes);
         std::memset(&ix->loc, 0, sizeof(ix->loc));
-        if (ri_bytes && ri.k.locate_ok) {
+        if (m.has_ri && m.has_locate) {
             LocDev &l = ix->loc; ix->has_locate = true;
-            auto up_sr = [&](const SparseRankImage &im, SparseRankDev &d, uint64_t &nd, uint64_t &nl) {
-                d.dir = upload(im.dir, ix->owned, bytes); nd = im.dir.size();
-                d.low = upload(im.low, ix->owned, bytes); nl = im.low.size();
-                d.size = im.k.size; d.m = im.k.m; d.shift = im.k.shift; d.low_bytes = im.k.low_bytes;
+            auto up_sr = [&](const SparseRankConsts &k, int sdir, int slow, SparseRankDev &sd, uint64_t &nd, uint64_t &nl) {
+                sd.dir = (const uint64_t *) up(sdir, nd); sd.low = (const uint8_t *) up(slow, nl);
+                sd.size = k.size; sd.m = k.m; sd.shift = k.shift; sd.low_bytes = k.low_bytes;
             };
-            up_sr(ri.run_starts, l.run_starts, ix->n_rs_dir, ix->n_rs_low);
-            up_sr(ri.last, l.last, ix->n_last_dir, ix->n_last_low);
-            l.samples.words = upload(ri.samples.words, ix->owned, bytes); ix->n_samples_words = ri.samples.words.size();
-            l.samples.n = ri.samples.n; l.samples.width = ri.samples.width; l.samples.pad = 0;
-            l.last_to_run.words = upload(ri.last_to_run.words, ix->owned, bytes); ix->n_ltr_words = ri.last_to_run.words.size();
-            l.last_to_run.n = ri.last_to_run.n; l.last_to_run.width = ri.last_to_run.width; l.last_to_run.pad = 0;
-            l.max_length = ri.k.max_length;
+            up_sr(m.rs_k, SEC_RS_DIR, SEC_RS_LOW, l.run_starts, ix->n_rs_dir, ix->n_rs_low);
+            up_sr(m.last_k, SEC_LAST_DIR, SEC_LAST_LOW, l.last, ix->n_last_dir, ix->n_last_low);
+            l.samples.words = (const uint64_t *) up(SEC_SAMPLES, ix->n_samples_words);
+            l.samples.n = m.samples_n; l.samples.width = (uint32_t) m.samples_width; l.samples.pad = 0;
+            l.last_to_run.words = (const uint64_t *) up(SEC_LAST_TO_RUN, ix->n_ltr_words);
+            l.last_to_run.n = m.ltr_n; l.last_to_run.width = (uint32_t) m.ltr_width; l.last_to_run.pad = 0;
+            l.max_length = m.k.max_length;
         }
         std::memset(&ix->tg, 0, sizeof(ix->tg));
-        if (has_tags) {
-            TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = tg.intervals.k;
-            t.iv.dir = upload(tg.intervals.dir, ix->owned, bytes); ix->n_iv_dir = tg.intervals.dir.size();
-            t.iv.low = upload(tg.intervals.low, ix->owned, bytes); ix->n_iv_low = tg.intervals.low.size();
-            t.iv.size = tg.intervals.k.size; t.iv.m = tg.intervals.k.m; t.iv.shift = tg.intervals.k.shift; t.iv.low_bytes = tg.intervals.k.low_bytes;
-            t.starts = upload(tg.starts, ix->owned, bytes); t.n_starts = tg.starts.size(); ix->n_starts = tg.starts.size();
-            t.words = upload(tg.words, ix->owned, bytes); ix->n_words = tg.words.size();
-            t.stream = upload(tg.stream, ix->owned, bytes); ix->n_stream = tg.stream.size();
-            t.n_items = tg.n_items; t.width = tg.width; t.layout = (uint32_t) tg.layout; t.starts_regular = tg.starts_regular; t.pad = 0;
+        if (m.has_tags) {
+            TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = m.iv_k;
+            t.iv.dir = (const uint64_t *) up(SEC_IV_DIR, ix->n_iv_dir); t.iv.low = (const uint8_t *) up(SEC_IV_LOW, ix->n_iv_low);
+            t.iv.size = m.iv_k.size; t.iv.m = m.iv_k.m; t.iv.shift = m.iv_k.shift; t.iv.low_bytes = m.iv_k.low_bytes;
+            t.starts = (const uint64_t *) up(SEC_STARTS, ix->n_starts); t.n_starts = ix->n_starts;
+            t.words = (const uint64_t *) up(SEC_WORDS, ix->n_words);
+            t.stream = (const uint8_t *) up(SEC_STREAM, ix->n_stream);
+            t.n_items = m.tag_n_items; t.width = (uint32_t) m.tag_width; t.layout = (uint32_t) m.tag_layout; t.starts_regular = (uint32_t) m.tag_starts_regular; t.pad = 0;
         }
-        fill_info(ix, ri, has_tags ? &tg : nullptr, bytes);
+        stg.finish();
+        fill_info(ix, m, bytes);
         CK(cudaDeviceSynchronize());
-        *out = ix;
+        if (chunks_out) *chunks_out = stg.chunks;
+        return ix;
+    } catch (...) { pgi_index_free(ix); throw; }
+}
+
+// Flatten the SDSL files on the host (no device involved).
+static void flatten_files(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len, int tag_layout,
+                          RiImage &ri, TagImage &tg, IndexView &v) {
+    const bool has_tags = tag_bytes && tag_len;
+    std::memset(&ri.k, 0, sizeof(ri.k));
+    if (ri_bytes) flatten_ri(ri_bytes, ri_len, ri);
+    if (has_tags) flatten_tags(tag_bytes, tag_len, tag_layout, tg);
+    view_of(ri_bytes ? &ri : nullptr, has_tags ? &tg : nullptr, v);
+}
+
+#define PGI_CATCH_ALL \
+    catch (const FormatError &e) { return fail(PGI_EFORMAT, e.what()); } \
+    catch (const CudaError &e) { return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); } \
+    catch (const std::bad_alloc &) { return fail(PGI_ENOMEM, "out of host memory while flattening the index"); } \
+    catch (const std::exception &e) { return fail(PGI_EINVAL, e.what()); }
+
+extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
+                                int tag_layout, int device, pgi_index **out) {
+    if ((!ri_bytes && !tag_bytes) || !out) return fail(PGI_EINVAL, "null argument");
+    if (int rc = check_device(device)) return rc;
+    try {
+        RiImage ri; TagImage tg; IndexView v;
+        flatten_files(ri_bytes, ri_len, tag_bytes, tag_len, tag_layout, ri, tg, v);
+        *out = upload_view(v, device, 0, nullptr);
         return PGI_OK;
-    } catch (const FormatError &e) { pgi_index_free(ix); return fail(PGI_EFORMAT, e.what());
-    } catch (const CudaError &e) { pgi_index_free(ix); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e));
-    } catch (const std::bad_alloc &) { pgi_index_free(ix); return fail(PGI_ENOMEM, "out of host memory while flattening the index");
-    } catch (const std::exception &e) { pgi_index_free(ix); return fail(PGI_EINVAL, e.what()); }
+    } PGI_CATCH_ALL
+}
+
+// ------------------------------------------------------------------------------------------ cached device image
+extern "C" int pgi_image_write(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len, int tag_layout, const char *path) {
+    if ((!ri_bytes && !tag_bytes) || !path) return fail(PGI_EINVAL, "null argument");
+    try {
+        RiImage ri; TagImage tg; IndexView v;
+        flatten_files(ri_bytes, ri_len, tag_bytes, tag_len, tag_layout, ri, tg, v);
+        write_image(v, path, ri_bytes ? ri_len : 0, ri_bytes ? edge_sum(ri_bytes, ri_len) : 0,
+                    (tag_bytes && tag_len) ? tag_len : 0, (tag_bytes && tag_len) ? edge_sum(tag_bytes, tag_len) : 0);
+        return PGI_OK;
+    } PGI_CATCH_ALL
+}
+
+static void image_info_of(const MappedImage &im, pgi_image_info_t *f) {
+    std::memset(f, 0, sizeof(*f));
+    const ImageHeader &h = *im.h;
+    f->file_bytes = h.file_bytes; f->n = h.meta.k.n; f->sigma = h.meta.k.sigma; f->n_dev_blocks = h.meta.k.n_blocks; f->bucket_shift = h.meta.k.bshift;
+    f->has_ri = h.meta.has_ri; f->has_tags = h.meta.has_tags; f->tag_layout = h.meta.tag_layout; f->has_locate = h.meta.has_locate; f->is_encoded = h.meta.encoded;
+    f->src_ri_bytes = h.src_ri_bytes; f->src_tag_bytes = h.src_tag_bytes; f->src_ri_sum = h.src_ri_sum; f->src_tag_sum = h.src_tag_sum;
+    for (int s = 0; s < SEC_COUNT; ++s) f->payload_bytes += h.sec[s].bytes;
+}
+
+extern "C" int pgi_image_info(const char *path, int verify, pgi_image_info_t *out) {
+    if (!path || !out) return fail(PGI_EINVAL, "null argument");
+    try {
+        MappedImage im; im.open(path, verify != 0);
+        image_info_of(im, out);
+        return PGI_OK;
+    } PGI_CATCH_ALL
+}
+
+extern "C" uint64_t pgi_image_source_sum(const void *bytes, size_t len) { return bytes ? edge_sum(bytes, len) : 0; }
+
+extern "C" int pgi_index_open_image(const char *path, int device, uint64_t chunk_bytes, int verify, pgi_index **out, pgi_image_info_t *info) {
+    if (!path || !out) return fail(PGI_EINVAL, "null argument");
+    if (int rc = check_device(device)) return rc;
+    try {
+        const char *env = std::getenv("PGI_IMAGE_VERIFY");
+        MappedImage im; im.open(path, verify != 0 || (env && env[0] == '1'));
+        ::madvise((void *) im.base, im.len, MADV_SEQUENTIAL);
+        IndexView v; im.view(v);
+        if (!chunk_bytes) chunk_bytes = 64ull << 20;
+        if (chunk_bytes < 4096) chunk_bytes = 4096;
+        uint64_t chunks = 0;
+        *out = upload_view(v, device, (size_t) chunk_bytes, &chunks);
+        if (info) { image_info_of(im, info); info->chunks_copied = chunks; info->chunk_bytes = chunk_bytes; }
+        return PGI_OK;
+    } PGI_CATCH_ALL
 }
 
 extern "C" int pgi_index_info(const pgi_index *ix, pgi_index_info_t *out) {

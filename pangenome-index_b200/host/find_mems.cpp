@@ -13,6 +13,16 @@
 // src/query_tags.cpp:39-112: every batch goes through pgi_query_tags (whole-read count_encoded / count + the tag query
 // of the final range) and the text is that of src/query_tags.cpp:103-108 preceded by the two lines
 // query_compressed_compact prints itself; read_index counts non-empty lines from 0 (readSequencesFromFile :27-37).
+//
+// Compiled with -DPGI_MMAP / -DPGI_CHUNKED it is `find_mems_memory_mapped <ri> <tags> <reads> <mem_length> <min_occ>`
+// (src/find_mems_memory_mapped.cpp:13-114) / `find_mems_chunked ... [chunk_size_mb]` (src/find_mems_chunked.cpp:13-121;
+// default 2048). The reference's variants avoid deserialising the index into RAM: MemoryMappedIndexManager maps the two
+// files, the chunked manager maps them in windows of chunk_size_mb. Here the SDSL files are flattened ONCE into a cached
+// device image next to the .ri file (<ri>.pgimg, or --image PATH; rebuilt when the source files change), and every later
+// run maps that image and streams it to HBM through two pinned staging buffers -- of chunk_size_mb for the chunked
+// variant, 64 MiB for the memory-mapped one: no parsing, host memory bounded by 2 x chunk. Like the reference's variants
+// (FastLocate::load + TagArray::load_compressed_tags + query_compressed) they expect ByteCode tags, but take either
+// layout. The per-read text is that of find_mems; the trailer adds the reference's size / chunk lines.
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -26,8 +36,31 @@
 #include <thread>
 #include <vector>
 #include "panindexer.hpp"
+#if defined(PGI_MMAP) || defined(PGI_CHUNKED)
+#define PGI_IMAGE_DRIVER 1
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#endif
 
 namespace {
+
+#ifdef PGI_IMAGE_DRIVER
+struct MapFile {                                 // read-only mapping of a source file (only the pages that are used get read)
+    const char *p = nullptr; size_t len = 0;
+    bool open(const std::string &path) {
+        const int fd = ::open(path.c_str(), O_RDONLY);
+        if (fd < 0) return false;
+        struct stat st;
+        if (::fstat(fd, &st) != 0) { ::close(fd); return false; }
+        len = (size_t) st.st_size;
+        if (len) { void *m = ::mmap(nullptr, len, PROT_READ, MAP_SHARED, fd, 0); if (m == MAP_FAILED) { ::close(fd); return false; } p = (const char *) m; }
+        ::close(fd); return true;
+    }
+    ~MapFile() { if (p) ::munmap((void *) p, len); }
+};
+#endif
 
 struct Batch {
     uint64_t id = 0, first_seq = 1, n = 0, bytes = 0;
@@ -67,7 +100,7 @@ private:
     std::mutex mu_; std::condition_variable cv_; std::vector<T> q_; bool closed_ = false;
 };
 
-std::string slurp_file(const std::string &path, const char *what) {
+[[maybe_unused]] std::string slurp_file(const std::string &path, const char *what) {
     std::ifstream in(path, std::ios::binary);
     if (!in) { std::fprintf(stderr, "Cannot open %s: %s\n", what, path.c_str()); std::exit(EXIT_FAILURE); }
     return panindexer::slurp(in);
@@ -93,8 +126,23 @@ int main(int argc, char **argv) {
 #endif
     const std::string r_index_file = argv[1], tag_array_index = argv[2], reads_file = argv[3];
     int gpus = 1; uint64_t batch_reads = 1u << 20; std::string layout = "auto"; bool text = true;
-    for (int i = n_fixed; i < argc; ++i) {
+    int first_opt = n_fixed;
+#ifdef PGI_IMAGE_DRIVER
+    std::string image_path = r_index_file + ".pgimg"; bool rebuild = false, verify = false;
+    uint64_t chunk_size_mb = 64;
+#ifdef PGI_CHUNKED
+    chunk_size_mb = 2048;                                                                                // src/find_mems_chunked.cpp:29
+    if (argc > n_fixed && std::strncmp(argv[n_fixed], "--", 2) != 0) { chunk_size_mb = (uint64_t) std::stoi(argv[n_fixed]); first_opt = n_fixed + 1; }
+    if (chunk_size_mb < 1) chunk_size_mb = 1;
+#endif
+#endif
+    for (int i = first_opt; i < argc; ++i) {
         std::string a = argv[i];
+#ifdef PGI_IMAGE_DRIVER
+        if (a == "--image" && i + 1 < argc) { image_path = argv[++i]; continue; }
+        if (a == "--rebuild-image") { rebuild = true; continue; }
+        if (a == "--verify-image") { verify = true; continue; }
+#endif
         if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);
         else if (a == "--batch" && i + 1 < argc) batch_reads = std::strtoull(argv[++i], nullptr, 10);
         else if (a == "--tags-layout" && i + 1 < argc) layout = argv[++i];
@@ -108,6 +156,40 @@ int main(int argc, char **argv) {
 
     using clk = std::chrono::steady_clock;
     auto t_load = clk::now();
+#ifdef PGI_IMAGE_DRIVER
+#ifdef PGI_CHUNKED
+    std::cerr << "Opening chunked memory-mapped indices..." << std::endl;
+    std::cerr << "Chunk size: " << chunk_size_mb << " MB" << std::endl;
+#else
+    std::cerr << "Opening memory-mapped indices..." << std::endl;
+#endif
+    std::vector<pgi_index *> ix(gpus, nullptr);
+    pgi_image_info_t img;
+    {
+        MapFile ri, tg;
+        if (!ri.open(r_index_file) || !tg.open(tag_array_index)) { std::cerr << "Failed to open memory-mapped indices" << std::endl; return EXIT_FAILURE; }
+        const uint64_t ri_sum = pgi_image_source_sum(ri.p, ri.len), tg_sum = pgi_image_source_sum(tg.p, tg.len);
+        bool fresh = !rebuild && pgi_image_info(image_path.c_str(), 0, &img) == PGI_OK && img.src_ri_bytes == ri.len && img.src_tag_bytes == tg.len &&
+                     img.src_ri_sum == ri_sum && img.src_tag_sum == tg_sum &&
+                     (layout == "auto" || img.tag_layout == (layout == "bytecode" ? (uint64_t) PGI_TAGS_BYTECODE_LEN : (uint64_t) PGI_TAGS_SDSL_COMPACT));
+        if (!fresh) {
+            std::cerr << "Flattening the index into " << image_path << " (first use, or the source files changed)" << std::endl;
+            int rc = PGI_EFORMAT;                  // the reference's variants read ByteCode tags (load_compressed_tags): try that layout first
+            if (layout == "bytecode" || layout == "auto") rc = pgi_image_write(ri.p, ri.len, tg.p, tg.len, PGI_TAGS_BYTECODE_LEN, image_path.c_str());
+            if (rc == PGI_EFORMAT && (layout == "compact" || layout == "auto")) rc = pgi_image_write(ri.p, ri.len, tg.p, tg.len, PGI_TAGS_SDSL_COMPACT, image_path.c_str());
+            if (rc != PGI_OK) { std::fprintf(stderr, "find_mems: cannot load the index: %s\n", pgi_last_error()); return EXIT_FAILURE; }
+        } else std::cerr << "Using the cached image " << image_path << std::endl;
+    }
+    if (pgi_index_open_image(image_path.c_str(), 0, chunk_size_mb << 20, verify ? 1 : 0, &ix[0], &img) != PGI_OK) {
+        std::fprintf(stderr, "find_mems: cannot open the index image: %s\n", pgi_last_error()); return EXIT_FAILURE;
+    }
+    for (int g = 1; g < gpus; ++g)
+        if (pgi_index_clone_to(ix[0], g, &ix[g]) != PGI_OK) { std::fprintf(stderr, "find_mems: cannot replicate the index on GPU %d: %s\n", g, pgi_last_error()); return EXIT_FAILURE; }
+    const double image_gb = (double) img.file_bytes / (1024.0 * 1024.0 * 1024.0);
+    std::cerr << "Opening memory-mapped indices took " << std::chrono::duration<double>(clk::now() - t_load).count() << " seconds ("
+              << img.chunks_copied << " chunk copies)" << std::endl;
+    std::cerr << "Total memory-mapped size: " << image_gb << " GB" << std::endl;
+#else
     std::cerr << "Reading the rindex file (encoded)" << std::endl;
     std::string ri = slurp_file(r_index_file, "r-index");
     std::cerr << "Reading the tag array index" << std::endl;
@@ -123,6 +205,8 @@ int main(int argc, char **argv) {
     }
     ri.clear(); ri.shrink_to_fit(); tg.clear(); tg.shrink_to_fit();
     std::cerr << "Loading and flattening the index took " << std::chrono::duration<double>(clk::now() - t_load).count() << " seconds" << std::endl;
+
+#endif
 
     FILE *rf = std::fopen(reads_file.c_str(), "rb");
     if (!rf) { std::cerr << "Cannot open reads file: " << reads_file << std::endl; return EXIT_FAILURE; }
@@ -214,6 +298,11 @@ int main(int argc, char **argv) {
 #ifndef PGI_QUERY_TAGS
     // src/find_mems.cpp:143-146 (values are not comparable: MEM finding and tag lookup are one fused GPU pass here)
     std::printf("\nTotal time for finding all MEMs: %g seconds\nTotal time for all tag queries: %g seconds\n", gpu_seconds, 0.0);
+#ifdef PGI_CHUNKED      // src/find_mems_chunked.cpp:112-116
+    std::printf("Chunked memory-mapped indices used: %g GB\nChunk size: %llu MB\n", image_gb, (unsigned long long) chunk_size_mb);
+#elif defined(PGI_MMAP) // src/find_mems_memory_mapped.cpp:105-108
+    std::printf("Memory-mapped indices used: %g GB\n", image_gb);
+#endif
 #else
     (void) mem_length; (void) min_occ; (void) gpu_seconds;
     if (total_reads == 0) { std::cerr << "No reads found in file." << std::endl; return 1; }     // src/query_tags.cpp:82-85

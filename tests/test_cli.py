@@ -86,3 +86,47 @@ def test_query_tags_cli_stdout_equals_oracle(tmp_path):
     (tmp_path / "empty.txt").write_bytes(b"\n\n")
     p = subprocess.run([QT, str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "empty.txt")], capture_output=True)
     assert p.returncode == 1 and b"No reads found in file." in p.stderr
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["xy_bytecode", "synth_compact"])
+def test_mmap_and_chunked_cli_stdout_equals_oracle(tmp_path, case):
+    """host/find_mems_memory_mapped and host/find_mems_chunked (src/find_mems_memory_mapped.cpp, src/find_mems_chunked.cpp):
+    the per-read text of find_mems, then the reference's trailer lines. The first run writes the cached device image,
+    later runs map it; a changed source file invalidates it."""
+    MM = os.path.join(HOST, "find_mems_memory_mapped"); CH = os.path.join(HOST, "find_mems_chunked")
+    if case == "xy_bytecode":
+        ri, tg, layout, text = datasets.gold("xy.ri"), datasets.gold("xy_bidirectional_compressed.tags"), 1, datasets.gold("contigs_xy")
+    else:
+        s = datasets.synth_index(); ri, tg, layout, text = s["ri"], s["tags0"], 0, s["text"]
+    reads, off = datasets.sample_reads(text, 400, 150, 0.02, seed=5)
+    rs = [reads[int(off[i]):int(off[i + 1])].tobytes() for i in range(400)]
+    (tmp_path / "x.ri").write_bytes(ri); (tmp_path / "x.tags").write_bytes(tg); (tmp_path / "reads.txt").write_bytes(b"\n".join(rs) + b"\n")
+    want = orc.Index(ri, tg, layout).find_mems(reads, off, 20, 1)["text"]
+    base = [str(tmp_path / "x.ri"), str(tmp_path / "x.tags"), str(tmp_path / "reads.txt"), "20", "1"]
+    img = str(tmp_path / "x.ri.pgimg")
+    p = subprocess.run([MM] + base, capture_output=True)
+    assert p.returncode == 0, p.stderr.decode()
+    assert strip_timing(p.stdout) == want and b"Flattening the index into" in p.stderr and os.path.exists(img)
+    tail = p.stdout[p.stdout.rfind(b"\nTotal time for finding all MEMs:"):].split(b"\n")
+    assert tail[3].startswith(b"Memory-mapped indices used: ") and tail[3].endswith(b" GB") and tail[4:] == [b""]
+    stamp = os.path.getmtime(img)
+    p = subprocess.run([MM] + base + ["--batch", "64", "--verify-image"], capture_output=True)
+    assert p.returncode == 0 and strip_timing(p.stdout) == want and b"Using the cached image" in p.stderr and os.path.getmtime(img) == stamp
+    for extra, mb in ([], 2048), (["1"], 1), (["3", "--batch", "77"], 3):
+        p = subprocess.run([CH] + base + extra, capture_output=True)
+        assert p.returncode == 0, p.stderr.decode()
+        assert strip_timing(p.stdout) == want and b"Using the cached image" in p.stderr
+        tail = p.stdout[p.stdout.rfind(b"\nTotal time for finding all MEMs:"):].split(b"\n")
+        assert tail[3].startswith(b"Chunked memory-mapped indices used: ") and tail[4] == b"Chunk size: %d MB" % mb and tail[5:] == [b""]
+        assert b"Chunk size: %d MB" % mb in p.stderr
+    # a changed source file makes the image stale
+    s2 = datasets.synth_index(seed=8) if case == "synth_compact" else None
+    if s2:
+        (tmp_path / "x.ri").write_bytes(s2["ri"]); (tmp_path / "x.tags").write_bytes(s2["tags0"])
+        r2, o2 = datasets.sample_reads(s2["text"], 100, 150, 0.02, seed=6)
+        (tmp_path / "reads.txt").write_bytes(b"\n".join(r2[int(o2[i]):int(o2[i + 1])].tobytes() for i in range(100)) + b"\n")
+        p = subprocess.run([CH] + base, capture_output=True)
+        assert p.returncode == 0 and b"Flattening the index into" in p.stderr
+        assert strip_timing(p.stdout) == orc.Index(s2["ri"], s2["tags0"], 0).find_mems(r2, o2, 20, 1)["text"]
+    p = subprocess.run([MM, str(tmp_path / "nope.ri")] + base[1:], capture_output=True)
+    assert p.returncode != 0 and b"Failed to open memory-mapped indices" in p.stderr
