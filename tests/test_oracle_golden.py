@@ -144,3 +144,25 @@ def test_decompress_da_of_shipped_ri_equals_naive_document_array(ri, text):
     off, uids = o.locate_batch([0, 7, 100, 5, 9], [o.n - 1, 7, 180, 4, 8])
     assert np.array_equal(uids[off[0]:off[1]], np.unique(ids)) and uids[off[1]] == ids[7] and off[4] == off[3]
     assert np.array_equal(uids[off[2]:off[3]], np.unique(ids[100:181]))
+
+def test_build_rindex_cli_regenerates_shipped_files(tmp_path):
+    """prep/build_rindex (src/build_rindex.cpp:11-20: FastLocate(rlbwt) + serialize_encoded to stdout; --legacy =
+    FastLocate::serialize): the legacy output IS the shipped .ri, byte for byte; the encoded output parses to EOF and
+    holds the same BWT."""
+    import subprocess
+    from conftest import ROOT
+    exe = os.path.join(ROOT, "pangenome-index_b200", "prep", "build_rindex")
+    for rl, ri in [("contigs_xy.rl_bwt", "xy.ri"), ("contigs_XY.rl_bwt", "two_contig_xy.ri")]:
+        src = os.path.join(datasets.GOLD, rl)
+        p = subprocess.run([exe, src, "--legacy"], capture_output=True)
+        assert p.returncode == 0 and p.stdout == datasets.gold(ri), ri
+        p = subprocess.run([exe, src], capture_output=True)
+        assert p.returncode == 0 and b"ENCODED_BLOCKS" in p.stderr
+        a = orc.Index(datasets.gold(ri)); b = orc.Index(p.stdout)
+        assert b.info[2] == 1 and b.ri_consumed == len(p.stdout) and b.n == a.n
+        pos = np.arange(0, a.n + 1, dtype=np.uint64)
+        assert np.array_equal(a.rank_batch(pos)[:, :4], b.rank_batch(pos)[:, :4])
+    p = subprocess.run([exe, str(tmp_path / "missing.rl_bwt")], capture_output=True)
+    assert p.returncode != 0 and b"cannot open" in p.stderr and p.stdout == b""
+    p = subprocess.run([exe], capture_output=True)
+    assert p.returncode != 0 and b"Usage" in p.stderr
