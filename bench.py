@@ -50,19 +50,45 @@ def parse_args():
     return p.parse_args()
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clocks / throttle reasons during the timed region (B200_PROFILING.md), read in-process through NVML
+    (nvidia_ml_py). Spawning `nvidia-smi` every 0.2 s from each of 8 ranks enumerated all GPUs under the driver's global
+    lock and stretched the host side of every step (r01o: 19.6 ms per step on 8 GPUs against 12.3 ms on one);
+    nvidia-smi remains the fallback, on rank 0 only, at a 1 s period."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
-    def __init__(self, gpu):
-        super().__init__(daemon=True); self.gpu = gpu; self.rows = []; self.stop_flag = False
+    def __init__(self, gpu, rank=0):
+        super().__init__(daemon=True); self.gpu = gpu; self.rank = rank; self.rows = []; self.stop_flag = False; self.h = None; self.nv = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            idx = gpu
+            if vis and all(x.strip().isdigit() for x in vis.split(",")): idx = int(vis.split(",")[gpu])
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx); self.nv = pynvml
+        except Exception:
+            self.h = None
+    def sample_nvml(self):
+        nv = self.nv
+        sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM); mx = nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM)
+        get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        r = int(get(self.h))
+        bit = lambda *names: next((getattr(nv, n) for n in names if hasattr(nv, n)), 0)
+        flags = [bit("nvmlClocksEventReasonHwSlowdown", "nvmlClocksThrottleReasonHwSlowdown"),
+                 bit("nvmlClocksEventReasonHwThermalSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown"),
+                 bit("nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"),
+                 bit("nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap")]
+        return [str(sm), str(mx)] + ["Active" if (r & f) else "Not Active" for f in flags]
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out: self.rows.append([x.strip() for x in out.split(",")])
+                if self.h is not None:
+                    self.rows.append(self.sample_nvml()); time.sleep(0.1); continue
+                if self.rank == 0:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                         capture_output=True, text=True, timeout=5).stdout.strip()
+                    if out: self.rows.append([x.strip() for x in out.split(",")])
             except Exception:
                 pass
-            time.sleep(0.2)
+            time.sleep(1.0)
     def summary(self):
         sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
@@ -198,13 +224,14 @@ def main():
 
     # ---- device-resident timing (value)
     for i in range(args.warmup): step_device(i)
-    sampler = ClockSampler(local); sampler.start()
+    sampler = ClockSampler(local, rank); sampler.start()
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0
-    e0.record(stream)
+    e0.record(stream); host_gap = []; t_prev = time.perf_counter()
     for i in range(args.steps):
         step_device(args.warmup + i)
+        t_now = time.perf_counter(); host_gap.append(1e3 * (t_now - t_prev)); t_prev = t_now      # host wall time of the step (diagnostic)
         ms = batch.stage_ms(); stage += np.array(ms); k1_ms += ms[0]; launches += int(ms[6]) + 0
         r = batch.device_result(); ext_total += r.extensions; mems_total += r.n_mems; tags_total += r.n_tags
     e1.record(stream)
@@ -235,9 +262,13 @@ def main():
     # ---- max over ranks
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([launches, ext_total, mems_total, tags_total], dtype=torch.float64, device="cuda")
+    per_rank = [[dev_ms / args.steps, e2e_ms / args.steps, max(host_gap)]]
     if world > 1:
+        mine = torch.tensor(per_rank[0], dtype=torch.float64, device="cuda"); allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine); per_rank = [[round(float(x), 3) for x in r] for r in allr]
         dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank == 0: log("per rank [device ms/step, e2e ms/step, slowest host step ms]:", per_rank, "rank 0 host ms per step:", [round(x, 2) for x in host_gap])
     if rank != 0:
         if world > 1: dist.destroy_process_group()
         return
@@ -315,17 +346,18 @@ def main():
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int64", "data": "synthetic",
             "config": {"workload": w["name"], "facts": w["facts"], "reads_per_step_per_gpu": n, "read_len": L, "substitution_rate": args.sub,
-                       "min_len": args.min_len, "min_occ": args.min_occ, "index": "replicated per GPU", "device_index_bytes": ix.info["device_bytes"],
+                       "min_len": args.min_len, "min_occ": args.min_occ, "index": "replicated per GPU", "device_index_bytes": ix.info["device_bytes"], "seed_k": ix.info["seed_k"],
                        "l2_policy": "read batch (%.0f MB) and index are cycled over %d distinct batches; inputs larger than L2" % (n * L / 1e6, pool),
                        "parity_sample": "%d reads bit-exact vs oracle: %s" % (ns, parity),
                        "mems_per_read": float(cnt[2]) / total_reads, "tags_per_read": float(cnt[3]) / total_reads,
                        "extensions_per_read": float(cnt[1]) / total_reads},
             "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": n * L + (n + 1) * 8, "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e2e_ms / args.steps, "concurrent_callers": E2E_CALLERS},
             "gpu_launches": int(cnt[0]),
+            "per_rank_ms_per_step": {"device": [r[0] for r in per_rank], "e2e": [r[1] for r in per_rank]},
             "stage_ms_per_step": {k: round(float(v) / args.steps, 3) for k, v in zip(["fmd_mem_kernel", "mem_order", "tag_plan", "tag_decode_sort", "tag_unique_compact", "run_total"], stage[:6])},
             "roofline": {"bound": "hbm", "kernel": "fmd_mem_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": k1_bytes_per_launch,
-                         "bytes_model": "128 B x D, D = distinct reference 10-run blocks touched per extension (oracle: D/E = %.3f) x E = %d extensions per launch (counted by the kernel)" % (d_per_e, ext_rank0 // args.steps),
+                         "bytes_model": "128 B x D, D = distinct reference 10-run blocks touched per extension (oracle: D/E = %.3f) x E = %d extensions per launch (the reference algorithm's count = the oracle's E; with seed_k > 0 the first seed_k extensions of a walk from the full interval are ONE 16-byte table lookup, so the kernel moves fewer bytes than the algorithm names and frac may exceed 1)" % (d_per_e, ext_rank0 // args.steps),
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
             "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",
                              "sample": "%d reads of the same batch in %.1f s, %d OpenMP threads (oracle/ restatement; the reference itself is single-threaded)" % (cpu["reads"], cpu["seconds"], cores)},

@@ -21,7 +21,7 @@ class Result(ctypes.Structure):
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
                                                "has_quirk_slot", "has_tags", "tag_layout", "tag_runs", "tag_items", "tag_item_width",
-                                               "tag_universe", "device_bytes", "n_crowded_buckets", "has_locate", "max_length"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
+                                               "tag_universe", "device_bytes", "n_crowded_buckets", "has_locate", "max_length", "seed_k"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
 
 class LocateResult(ctypes.Structure):
     _fields_ = [("n", ctypes.c_uint64), ("n_ids", ctypes.c_uint64), ("n_rows", ctypes.c_uint64), ("id_off", ctypes.c_void_p),
@@ -132,7 +132,7 @@ class Index:
             _ck(L.pgi_index_create(ri, len(ri) if ri else 0, tags, len(tags) if tags else 0, tag_layout, device, ctypes.byref(h)))
             self.h = h
         info = IndexInfo(); _ck(L.pgi_index_info(self.h, ctypes.byref(info)))
-        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:18]}
+        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:19]}
         self.n = info.n; self.sigma = info.sigma; self.has_tags = bool(info.has_tags)
         self.C = list(info.C)[: info.sigma]; self.sym_map = bytes(info.sym_map)
     def clone_to(self, device):

@@ -75,6 +75,7 @@ struct pgi_index {
     RiDev ri; TagDev tg; LocDev loc; bool has_tags = false, has_ri = true, has_locate = false;
     uint64_t n_rs_dir = 0, n_rs_low = 0, n_last_dir = 0, n_last_low = 0, n_samples_words = 0, n_ltr_words = 0;
     RiConsts consts; SparseRankConsts ivk;
+    uint4 *d_seed = nullptr; uint32_t seed_k = 0;          // seed table (pgi_core.cuh): 4^seed_k entries, built on the device at load
     uint32_t *d_desc = nullptr, *d_desc_c = nullptr;      // extension descriptors; LF-step descriptors of the whole-read search
     std::vector<void *> owned;
     // sizes of the uploaded arrays, for clone
@@ -108,7 +109,7 @@ static void fill_info(pgi_index *ix, const ImageMeta &m, uint64_t bytes) {
         f.has_tags = 1; f.tag_layout = m.tag_layout; f.tag_runs = m.iv_k.m; f.tag_items = m.tag_n_items;
         f.tag_item_width = m.tag_width; f.tag_universe = m.iv_k.size;
     }
-    f.device_bytes = bytes; f.has_locate = m.k.locate_ok; f.max_length = m.k.max_length;
+    f.device_bytes = bytes; f.has_locate = m.k.locate_ok; f.max_length = m.k.max_length; f.seed_k = ix->seed_k;
     for (int i = 0; i < 8; ++i) f.C[i] = m.k.C[i];
     std::memcpy(f.sym_map, m.k.sym_map, 256);
 }
@@ -147,6 +148,32 @@ struct Stager {
         cudaStreamDestroy(st);
     }
 };
+
+// Seed table (pgi_core.cuh): one thread per K-mer runs the K backward extensions from the full interval.
+__global__ void seed_table_kernel(RiDev ix, const uint32_t *desc, uint32_t K, uint32_t n_entries, uint4 *out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_entries) return;
+    const SeedWord e = seed_entry(ix, desc, i, K);
+    out[i] = make_uint4(e.x, e.y, e.z, e.w);
+}
+// K by index size: a K-mer should still occur (4^K well below n) and the table should stay a small fraction of the index.
+// PGI_SEEDK=<0..12> overrides it (0: no table) for tuning runs and tests. No table for indexes with a quirk slot
+// (interval sizes are not monotone there) or without an r-index part.
+static uint32_t choose_seed_k(const ImageMeta &m) {
+    if (!m.has_ri || m.k.has_quirk || m.k.n < 16) return 0;
+    uint32_t K = m.k.n >= (1ull << 28) ? 12u : m.k.n >= (1ull << 22) ? 10u : m.k.n >= (1ull << 16) ? 8u : 6u;
+    if (const char *e = std::getenv("PGI_SEEDK")) { const long v = std::strtol(e, nullptr, 10); if (v >= 0 && v <= (long) PGI_SEED_MAX_K) K = (uint32_t) v; }
+    return K;
+}
+static void build_seed_table(pgi_index *ix, uint32_t K, uint64_t &bytes) {
+    ix->seed_k = 0; ix->d_seed = nullptr;
+    if (!K) return;
+    const uint32_t n_entries = 1u << (2u * K);
+    void *d = nullptr; CK(cudaMalloc(&d, (size_t) n_entries * 16)); ix->owned.push_back(d); bytes += (uint64_t) n_entries * 16;
+    seed_table_kernel<<<(n_entries + 255) / 256, 256>>>(ix->ri, ix->d_desc, K, n_entries, (uint4 *) d);
+    CK(cudaGetLastError());
+    ix->d_seed = (uint4 *) d; ix->seed_k = K;
+}
 
 // Allocate + fill the device copy of every section of a flattened index (fresh from flatten_ri / flatten_tags, or a
 // mapped image file) and wire the device structs. Throws CudaError.
@@ -210,6 +237,7 @@ static pgi_index *upload_view(const IndexView &v, int device, size_t chunk_bytes
             t.n_items = m.tag_n_items; t.width = (uint32_t) m.tag_width; t.layout = (uint32_t) m.tag_layout; t.starts_regular = (uint32_t) m.tag_starts_regular; t.pad = 0;
         }
         stg.finish();
+        build_seed_table(ix, choose_seed_k(m), bytes);
         fill_info(ix, m, bytes);
         CK(cudaDeviceSynchronize());
         if (chunks_out) *chunks_out = stg.chunks;
@@ -329,6 +357,8 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
         ix->ri.q_val = clone_arr(src->ri.q_val, sd, src->n_quirk, device, ix->owned);
         ix->d_desc = clone_arr(src->d_desc, sd, PGI_DESC_WORDS, device, ix->owned);
         ix->d_desc_c = clone_arr(src->d_desc_c, sd, PGI_DESC_WORDS, device, ix->owned);
+        ix->seed_k = src->seed_k;
+        if (src->seed_k) ix->d_seed = clone_arr(src->d_seed, sd, (uint64_t) 1 << (2u * src->seed_k), device, ix->owned);
         if (src->has_locate) {
             ix->loc.run_starts.dir = clone_arr(src->loc.run_starts.dir, sd, src->n_rs_dir, device, ix->owned);
             ix->loc.run_starts.low = clone_arr(src->loc.run_starts.low, sd, src->n_rs_low, device, ix->owned);
@@ -488,6 +518,7 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
         MemArgs a;
         a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
         a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
+        a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0;
         a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
         if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
@@ -528,7 +559,7 @@ void run_count_stage(pgi_batch *b, int &launches) {
     CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
-    a.n_reads = n; a.min_len = 1; a.min_occ = 0;
+    a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0;
     a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = n;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }

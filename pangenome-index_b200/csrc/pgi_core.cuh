@@ -326,6 +326,78 @@ PGI_HD void lane_after_ext(MemLane &L, const BiInt &t, uint32_t min_len, uint64_
     }
 }
 
+// ------------------------------------------------------------------------------------ seed table
+// The first K extensions of every backward walk that starts from the FULL interval {0, 0, n} -- step 1 of
+// find_mems_function (algorithm.hpp:666-676) and its step 3 re-scan (:718-735) -- depend only on the K symbols read, so
+// their result is tabulated once per index: seed[idx] = the interval after backward-extending {0, 0, n} by the K symbols,
+// for every K-mer over {A, C, G, T}, produced by extend_desc itself (so every file-format quirk folded into the
+// descriptors is in the table). Interval sizes never grow along a walk when every rank is a true symbol rank (no quirk
+// slot: has_quirk == 0, the only case the table is built for), so "the K-th interval passes the min_occ test" implies
+// that the K - 1 before it did: one 16-byte lookup then stands for K trips of the kernel, and they are the expensive
+// ones (wide intervals: two distinct run blocks per extension). A K-mer with any other byte, or whose entry fails the
+// test, walks step by step as before (the failing position matters then).
+//
+// Window of the read: bytes [lo, lo + K) with lo = (position of the first symbol extended) - K + 1; byte i of the window
+// is read position lo + i; extensions run from byte K - 1 down to byte 0. Code of a byte = (byte >> 1) & 3
+// (A 0, C 1, T 2, G 3); idx = sum code_i << 2 i.
+#define PGI_SEED_MAX_K 12u
+struct SeedWord { uint32_t x, y, z, w; };            // k, k', s: low 32 bits in x, y, z; bits 32..39 in the bytes of w
+PGI_HD SeedWord seed_pack(const BiInt &b) {
+    SeedWord e; e.x = (uint32_t) b.k; e.y = (uint32_t) b.kp; e.z = (uint32_t) (uint64_t) b.s;
+    e.w = (uint32_t) ((b.k >> 32) & 0xFFu) | (uint32_t) ((b.kp >> 32) & 0xFFu) << 8 | (uint32_t) (((uint64_t) b.s >> 32) & 0xFFu) << 16;
+    return e;
+}
+PGI_HD BiInt seed_unpack(const SeedWord &e) {
+    BiInt b; b.k = (uint64_t) e.x | (uint64_t) (e.w & 0xFFu) << 32; b.kp = (uint64_t) e.y | (uint64_t) ((e.w >> 8) & 0xFFu) << 32;
+    b.s = (int64_t) ((uint64_t) e.z | (uint64_t) ((e.w >> 16) & 0xFFu) << 32);
+    return b;
+}
+PGI_HD uint8_t seed_symbol(uint32_t code) { return (uint8_t) ("ACTG"[code & 3u]); }
+// w0, w1, w2: the aligned 8-byte words holding the window (w1 / w2 may be anything when the window does not reach
+// them), sh = 8 * (lo & 7). Returns false when one of the K bytes is not exactly 'A', 'C', 'G' or 'T'.
+PGI_HD bool seed_index(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t sh, uint32_t K, uint32_t &idx) {
+    const uint64_t lo = sh ? (w0 >> sh) | (w1 << (64u - sh)) : w0;
+    const uint32_t hi = (uint32_t) (sh ? (w1 >> sh) | (w2 << (64u - sh)) : w1);
+    uint32_t bad = 0, id = 0;
+#pragma unroll
+    for (uint32_t g = 0; g < 3; ++g) {
+        const uint32_t v = g == 0 ? (uint32_t) lo : g == 1 ? (uint32_t) (lo >> 32) : hi;
+        const uint32_t c = (v >> 1) & 0x03030303u;
+        const uint32_t tf = (c >> 1) & ~c & 0x01010101u;                              // 'T' (code 2) is the one with bit 0 clear and bit 4 set
+        const uint32_t e = 0x40404040u | c << 1 | (tf ^ 0x01010101u) | tf << 4;       // the byte each code stands for
+        const uint32_t nb = K > 4u * g ? K - 4u * g : 0u;                             // bytes of this word inside the window
+        const uint32_t bm = nb >= 4u ? 0xFFFFFFFFu : (1u << (8u * nb)) - 1u;
+        bad |= (e ^ v) & bm;
+        uint32_t x = (c | c >> 6) & 0x000F000Fu;
+        x = (x | x >> 12) & 0xFFu;
+        id |= x << (8u * g);
+    }
+    idx = K >= 16u ? id : id & ((1u << (2u * K)) - 1u);
+    return bad == 0;
+}
+// Does the extension lane_settle just asked for start from the full interval with K symbols in reach?
+PGI_HD bool lane_seed_ready(const MemLane &L, uint32_t K, uint64_t n) {
+    if (L.b.s != (int64_t) n || (L.b.k | L.b.kp) != 0) return false;
+    if (L.phase == PH_P1) return L.j + 1u >= L.x + K;                                 // symbols j, j - 1, ..., j - K + 1 >= x
+    if (L.phase == PH_P3) return L.j < L.len && L.j >= L.x + K;                       // ... >= x + 1; pattern[len] is not a read byte
+    return false;
+}
+// K successful lane_after_ext steps at once (t = the table entry, known to pass ext_failed).
+PGI_HD void lane_seed_apply(MemLane &L, const BiInt &t, uint32_t K, uint32_t min_len) {
+    L.b = t;
+    if (L.phase == PH_P1 && L.j + 1u == K) { L.j = L.x + min_len; L.phase = PH_P2; }  // the K-th step was the one at j == 0
+    else L.j -= K;
+}
+// Entry of K-mer idx: K backward extensions from the full interval; {0, 0, 0} as soon as one comes back empty.
+PGI_HD SeedWord seed_entry(const RiDev &ix, const uint32_t *desc_b, uint32_t idx, uint32_t K) {
+    BiInt b; b.k = 0; b.kp = 0; b.s = (int64_t) ix.n;
+    for (uint32_t i = K; i-- > 0;) {
+        b = extend_desc(ix, b, desc_b[seed_symbol(idx >> (2u * i))]);
+        if (b.s <= 0) { b.k = 0; b.kp = 0; b.s = 0; break; }
+    }
+    return seed_pack(b);
+}
+
 // ------------------------------------------------------------------------------------ sparse rank
 // rank1(i) = number of set positions < i; i >= size counts everything (defined UB).
 PGI_HD uint64_t sparse_low(const SparseRankDev &s, uint64_t j) {

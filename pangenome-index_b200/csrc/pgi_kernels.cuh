@@ -30,6 +30,8 @@ struct MemArgs {
     uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
     uint64_t *mem_key;             // read id << 32 | index of the MEM within its read
     uint64_t *read_nmems;          // n_reads (+1) MEM counts per read
+    const uint4 *seed;             // seed table (pgi_core.cuh): 4^seed_k entries of 16 bytes, or nullptr
+    uint32_t seed_k, pad;          // 0: no table (OP 1, indexes with a quirk slot, PGI_SEEDK=0)
 };
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     __shared__ uint32_t s_desc[512];
     __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
     __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
+    __shared__ uint4 s_seed[OP == 0 ? THREADS : 1];              // per lane: the seed-table entry fetched by this trip's cp.async group
     for (int i = threadIdx.x; i < 512; i += blockDim.x) {
         s_desc[i] = a.desc[i];
         if (MODE) s_tab[i] = reinterpret_cast<const uint4 *>(a.desc + 512)[i];
@@ -106,6 +109,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0;
     bool exhausted = false, have = false;
+    bool stepwise = false;                       // the seed lookup of the pending walk was tried and is not usable: extend step by step
+    const uint32_t seed_k = OP == 0 ? a.seed_k : 0u;
     for (;;) {
         // ---- hand out reads to idle lanes
         const bool want = !have && !exhausted;
@@ -170,6 +175,23 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         // The 8-byte window of the read holding the symbol is REQUESTED here and USED only behind the block fetch below, so
         // that its latency overlaps the blocks' instead of preceding it (ncu r01g: a quarter of the stall samples sat on the
         // extraction of the symbol, in front of the cp.async sequence).
+        // Seed lookup (pgi_core.cuh "seed table"): a lane whose walk starts from the full interval with seed_k symbols in
+        // reach fetches ONE table entry in this trip instead of its run blocks and advances seed_k steps at once. The
+        // window of the read is requested here; the index is formed and the entry's cp.async joins the block fetch's
+        // group below, so the lookup costs no dependent latency beyond the one the trip pays anyway.
+        bool cand = false; uint64_t sw0 = 0, sw1 = 0, sw2 = 0; uint32_t ssh = 0;
+        if (OP == 0 && seed_k) {
+            cand = need && !stepwise && lane_seed_ready(L, seed_k, a.ix.n);
+            if (cand) {
+                const uint64_t lo = base + L.j + 1u - seed_k; const uint32_t o = (uint32_t) lo & 7u;
+                const uint64_t *p = a.reads64 + (lo >> 3);
+                sw0 = __ldg(p);
+                if (o + seed_k > 8u) sw1 = __ldg(p + 1);                  // words the window does not reach are not touched
+                if (o + seed_k > 16u) sw2 = __ldg(p + 2);
+                ssh = o * 8u;
+                need = false;                                             // no run blocks for this lane in this trip
+            }
+        }
         uint32_t sym = 0;
         const bool fwd = OP == 0 && L.phase == PH_P2;
         const bool has_sym = need && L.j < L.len;
@@ -181,8 +203,20 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             }
         }
         if (MODE == 0 && has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
+        if (MODE == 0 && OP == 0 && cand) {
+            uint32_t sidx = 0; bool ok = seed_index(sw0, sw1, sw2, ssh, seed_k, sidx);
+            if (ok) {
+                const uint4 e = __ldg(a.seed + sidx);
+                SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
+                const BiInt t = seed_unpack(q);
+                ok = !ext_failed(t, a.min_occ);
+                if (ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; }
+            }
+            stepwise = !ok;
+        }
         if (MODE == 0) {
             if (need) {
+                stepwise = false;
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
                 t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
@@ -208,7 +242,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r.
             // Block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
             // lane adds its part number and needs one multiply-add for the address.
-            auto coop_fetch = [&](uint32_t i1, uint32_t i2) {
+            auto coop_issue = [&](uint32_t i1, uint32_t i2) {
                 const uint32_t q1 = i1 == PGI_NOBLK ? PGI_NOBLK : i1 << 2, q2 = i2 == PGI_NOBLK ? PGI_NOBLK : i2 << 2;
 #pragma unroll
                 for (unsigned r = 0; r < 4; ++r) {
@@ -217,10 +251,19 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
                     cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
                 }
-                cp_async_wait_all();
-                __syncwarp();
             };
-            coop_fetch(b1, b2);
+            auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
+            coop_issue(b1, b2);
+            bool seed_ok = false;
+            if (OP == 0 && seed_k && __any_sync(FULL, cand)) {
+                if (cand) {
+                    uint32_t sidx = 0;
+                    seed_ok = seed_index(sw0, sw1, sw2, ssh, seed_k, sidx);
+                    cp_async16_if((uint32_t) __cvta_generic_to_shared(s_seed + threadIdx.x), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
+                }
+            }
+            cp_async_wait_all();
+            __syncwarp();
             // (2b) crowded buckets: a staged block that is a DIRECTORY block (pgi_layout.h) is replaced by the chunk block
             // holding the position, through one more cooperative fetch that the whole warp takes part in, so that the scan
             // below stays ONE converged code path (a per-lane slow path here ran at 1.8 active lanes and cost half as many
@@ -268,6 +311,17 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 if (OP == 0) lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
                 else if (ext_failed(u, 0)) L.phase = PH_DONE;                            // LF returned {1, 0}: stays empty
                 else { L.b = u; --L.j; }
+                stepwise = false;                             // whatever walk comes next may use the table again
+            }
+            if (OP == 0 && cand) {
+                if (seed_ok) {
+                    const uint4 e = s_seed[threadIdx.x];
+                    SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
+                    const BiInt t = seed_unpack(q);
+                    seed_ok = !ext_failed(t, a.min_occ);
+                    if (seed_ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; }
+                }
+                stepwise = !seed_ok;                          // other bytes / too few occurrences: the walk goes step by step
             }
             __syncwarp();                                     // the staging area is rewritten by the next trip
         }

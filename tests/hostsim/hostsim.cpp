@@ -6,13 +6,14 @@
 // libpgi.so never contains or calls this code; the GPU tests exercise the same header through the kernels.
 #include "../../pangenome-index_b200/csrc/pgi_flatten.hpp"
 #include "../../pangenome-index_b200/csrc/pgi_core.cuh"
+#include <cstring>
 #include <algorithm>
 #include <cstdlib>
 #include <string>
 
 using namespace pgi;
 
-struct sim_index { RiImage ri; TagImage tg; bool has_tags = false; RiDev rd; TagDev td; };
+struct sim_index { RiImage ri; TagImage tg; bool has_tags = false; RiDev rd; TagDev td; uint32_t seed_k = 0; std::vector<SeedWord> seed; };
 static thread_local std::string g_err;
 
 static void bind(sim_index *s) {
@@ -58,10 +59,25 @@ void sim_extend_batch(const sim_index *s, uint64_t n, const uint64_t *in3, const
         out3[3 * i] = b.k; out3[3 * i + 1] = b.kp; out3[3 * i + 2] = (uint64_t) b.s;
     }
 }
+// Seed table (pgi_core.cuh) built by the product's own seed_entry; K = 0 removes it. Returns the K in effect (0 on an index
+// with a quirk slot, where the product builds none either).
+uint32_t sim_set_seed_k(sim_index *s, uint32_t K) {
+    s->seed.clear(); s->seed_k = 0;
+    if (!K || K > PGI_SEED_MAX_K || s->rd.has_quirk) return 0;
+    s->seed.resize((size_t) 1 << (2 * K));
+    for (uint32_t i = 0; i < s->seed.size(); ++i) s->seed[i] = seed_entry(s->rd, s->ri.k.desc_b, i, K);
+    s->seed_k = K;
+    return K;
+}
 // find_all_mems of one read through the lane state machine; returns the MEM count (records of 4 u64 into out, up to cap).
 uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint64_t min_len, uint64_t min_occ, uint64_t *out, uint64_t cap, uint64_t *n_ext) {
     MemLane L; lane_begin(L, len, (uint32_t) min_len, s->rd.n);
     uint64_t nm = 0, ext = 0;
+    // the read as the kernel sees it: bytes at offset `base` of a buffer of aligned 8-byte words (alignment varies with len)
+    const uint64_t base = (len * 7 + 3) % 29;
+    std::vector<uint64_t> words((base + len) / 8 + 2, 0x5A5A5A5A5A5A5A5Aull);
+    std::memcpy((char *) words.data() + base, read, len);
+    bool stepwise = false; const uint32_t K = s->seed_k;
     for (;;) {
         const int st = lane_settle(L, (uint32_t) min_len, s->rd.n);
         if (st == LANE_EMIT) {
@@ -69,6 +85,20 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
             ++nm; lane_emitted(L, s->rd.n); continue;
         }
         if (st != LANE_EXTEND) break;
+        if (K && !stepwise && lane_seed_ready(L, K, s->rd.n)) {                     // fmd_mem_kernel's seed lookup, trip for trip
+            const uint64_t lo = base + L.j + 1u - K; const uint32_t o = (uint32_t) lo & 7u;
+            const uint64_t *p = words.data() + (lo >> 3);
+            const uint64_t w0 = p[0], w1 = o + K > 8u ? p[1] : 0, w2 = o + K > 16u ? p[2] : 0;
+            uint32_t idx = 0; bool ok = seed_index(w0, w1, w2, o * 8u, K, idx);
+            if (ok) {
+                const BiInt t = seed_unpack(s->seed[idx]);
+                ok = !ext_failed(t, min_occ);
+                if (ok) { lane_seed_apply(L, t, K, (uint32_t) min_len); ext += K; }
+            }
+            stepwise = !ok;
+            continue;
+        }
+        stepwise = false;
         const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
         BiInt t = L.b;
         if (L.phase == PH_P2) { std::swap(t.k, t.kp); t = extend_desc(s->rd, t, s->ri.k.desc_f[a]); std::swap(t.k, t.kp); }

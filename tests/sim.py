@@ -48,6 +48,10 @@ class Index:
         direction = np.ascontiguousarray(direction, dtype=np.uint8); out = np.zeros_like(iv3)
         lib().sim_extend_batch(self.h, len(sym), iv3.ctypes.data, sym.ctypes.data, direction.ctypes.data, out.ctypes.data)
         return out
+    def set_seed_k(self, k):
+        """Build (k > 0) or drop (k = 0) the seed table; returns the K in effect."""
+        lib().sim_set_seed_k.restype = ctypes.c_uint32; lib().sim_set_seed_k.argtypes = [ctypes.c_void_p, ctypes.c_uint32]
+        return lib().sim_set_seed_k(self.h, k)
     def find_mems(self, read: bytes, min_len, min_occ, cap=4096):
         out = np.zeros((cap, 4), dtype=np.uint64); ne = ctypes.c_uint64()
         n = lib().sim_find_mems(self.h, read, len(read), min_len, min_occ, out.ctypes.data, cap, ctypes.byref(ne))

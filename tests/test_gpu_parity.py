@@ -256,6 +256,42 @@ def test_crowded_buckets(capi, shift, monkeypatch):
         rng = np.random.default_rng(2); pos = rng.integers(0, o.n + 1, 20000).astype(np.uint64)
         assert np.array_equal(g.rank_batch(pos), o.rank_batch(pos))
 
+@pytest.mark.parametrize("K", ["0", "1", "4", "7", "8", "11", "12"])
+def test_seed_table_is_invisible(capi, K, monkeypatch):
+    """Seed table (pgi_core.cuh: the first K backward extensions of a walk from the full interval come from ONE lookup),
+    K forced through PGI_SEEDK: identical MEMs, tags, text AND extension count for every K, for min_len below / equal /
+    above K, min_occ > 1, ragged reads, other bytes, long reads; a cloned index carries the table; an index with a quirk
+    slot gets none."""
+    monkeypatch.setenv("PGI_SEEDK", K)
+    c = get_case("synth_enc_compact")
+    g = capi.Index(c["ri"], c["tags"], c["layout"]); o = orc.Index(c["ri"], c["tags"], c["layout"])
+    assert g.info["seed_k"] == int(K)
+    k = int(K)
+    for ml, mo in [(20, 1), (max(1, k), 1), (max(1, k - 1), 1), (k + 1, 2), (12, 40)]:
+        reads, off = datasets.sample_reads(c["text"], 4000, 150, 0.02, seed=40 + k + ml)
+        G = g.find_mems(reads, off, ml, mo); R = o.find_mems(reads, off, ml, mo, count_work=True)
+        compare(G, R, True)
+        assert G["extensions"] == R["counters"]["E"], (ml, mo)
+    rs = datasets.ragged_reads(c["text"], seed=8); r2, o2 = orc.pack_reads(rs)
+    compare(g.find_mems(r2, o2, 3, 1), o.find_mems(r2, o2, 3, 1), True)
+    compare(g.find_mems(r2, o2, 13, 1), o.find_mems(r2, o2, 13, 1), True)
+    q, qo = orc.pack_reads(query_reads(c["text"], seed=5, n=800))
+    compare_query_tags(g.query_tags(q, qo), o.query_tags(q, qo), True)               # OP 1 never uses the table
+    if K == "8":
+        s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+        gl = capi.Index(s["ri"], s["tags0"], 0); ol = orc.Index(s["ri"], s["tags0"], 0)
+        reads, off = datasets.sample_reads(s["text"], 200, 10000, 0.04, seed=33, indel=0.01)
+        G = gl.find_mems(reads, off, 20, 1); R = ol.find_mems(reads, off, 20, 1, count_work=True)
+        compare(G, R, True); assert G["extensions"] == R["counters"]["E"]
+        cl = g.clone_to(0)
+        assert cl.info["seed_k"] == 8
+        reads, off = datasets.sample_reads(c["text"], 2000, 150, 0.02, seed=77)
+        compare(cl.find_mems(reads, off, 20, 1), o.find_mems(reads, off, 20, 1), True)
+        x = get_case("xy_legacy_bytecode"); gx = capi.Index(x["ri"], x["tags"], x["layout"])
+        assert gx.info["seed_k"] == (0 if gx.info["has_quirk_slot"] else 8)
+        reads, off = datasets.sample_reads(x["text"], 2000, 150, 0.02, seed=78)
+        compare(gx.find_mems(reads, off, 20, 1), orc.Index(x["ri"], x["tags"], x["layout"]).find_mems(reads, off, 20, 1), True)
+
 def test_long_reads_with_indel_errors(capi):
     """BASELINE configs[4] as a parity case: 10 kbp reads with 5 % errors (substitutions + 1 bp indels): long backward /
     forward chains per lane, lanes of one warp finishing at very different times, many MEMs per read."""

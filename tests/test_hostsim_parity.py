@@ -61,6 +61,34 @@ def test_lane_machine_matches_find_all_mems(name, params):
         got, _ = g.find_mems(rd, ml, mo)
         assert np.array_equal(got, want), rd
 
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("K", [1, 3, 5, 6, 8])
+def test_seed_table_leaves_find_all_mems_unchanged(name, K):
+    """The seed table (pgi_core.cuh: one lookup for the first K backward extensions of a walk from the full interval) must
+    not change a single MEM nor the extension count, for every K, min_len below / equal / above K, min_occ > 1 (entries
+    that fail the occurrence test fall back to single steps), reads with other bytes, ragged and empty reads."""
+    c = case(name); o = orc.Index(c["ri"]); g = sim.Index(c["ri"])
+    k = g.set_seed_k(K)
+    if g.info["has_quirk"]:                              # quirk slot: no table (sizes are not monotone there)
+        assert k == 0; return
+    assert k == K
+    for ml, mo in [(20, 1), (K, 1), (max(1, K - 1), 1), (K + 1, 2), (12, 40)]:
+        nreads = 120
+        reads, off = datasets.sample_reads(c["text"], nreads, 150, 0.03, seed=K + ml + mo)
+        R = o.find_mems(reads, off, ml, mo, with_tags=False, count_work=True, threads=1)
+        tot_ext = 0
+        for i in range(nreads):
+            rd = reads[int(off[i]):int(off[i + 1])].tobytes()
+            mems, ne = g.find_mems(rd, ml, mo); tot_ext += ne
+            assert np.array_equal(mems, R["mems"][int(R["mem_off"][i]):int(R["mem_off"][i + 1])]), (ml, mo, i)
+        assert tot_ext == R["counters"]["E"], (ml, mo)
+        for rd in datasets.ragged_reads(c["text"], seed=5, n=40):
+            buf, o2 = orc.pack_reads([rd])
+            want = o.find_mems(buf, o2, ml, mo, with_tags=False)["mems"]
+            got, _ = g.find_mems(rd, ml, mo)
+            assert np.array_equal(got, want), (ml, mo, rd)
+    g.set_seed_k(0)
+
 @pytest.mark.parametrize("name", ["xy_legacy_bytecode", "synth_enc_compact", "synth_enc_bytecode"])
 def test_tag_plan_matches_oracle(name):
     c = case(name); o = orc.Index(c["ri"], c["tags"], c["layout"]); g = sim.Index(c["ri"], c["tags"], c["layout"])
