@@ -57,7 +57,8 @@ typedef struct {
     uint64_t *tag_off;   /* n_mems + 1  : tags of MEM m are tags[tag_off[m] .. tag_off[m+1])            */
     uint64_t *tags;      /* n_tags      : sorted unique encoded graph positions (node<<11|rev<<10|off)  */
     uint64_t *n_runs;    /* n_mems      : the reference's number_of_runs out-parameter                  */
-    uint64_t extensions; /* FMD extensions executed (work counter; equals the oracle's E)               */
+    uint64_t extensions; /* FMD extensions of the reference algorithm (work counter; equals the oracle's E) */
+    uint64_t seed_lookups; /* seed-table lookups; each stood for seed_k of those extensions (pgi_index_info_t) */
     void *owner;         /* internal */
 } pgi_result;
 

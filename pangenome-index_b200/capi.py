@@ -16,7 +16,7 @@ SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
                 ("mem_off", ctypes.c_void_p), ("mems", ctypes.c_void_p), ("tag_off", ctypes.c_void_p),
-                ("tags", ctypes.c_void_p), ("n_runs", ctypes.c_void_p), ("extensions", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
+                ("tags", ctypes.c_void_p), ("n_runs", ctypes.c_void_p), ("extensions", ctypes.c_uint64), ("seed_lookups", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
 
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
@@ -93,7 +93,7 @@ def _arr(ptr, n, dtype=np.uint64):
     return np.frombuffer(buf, dtype=dtype).copy()
 
 def _result_to_dict(res, L, with_tags, text=True):
-    out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags, extensions=res.extensions,
+    out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags, extensions=res.extensions, seed_lookups=res.seed_lookups,
                mem_off=_arr(res.mem_off, res.n_reads + 1 if res.mem_off else 0),
                mems=_arr(res.mems, 4 * res.n_mems if res.mems else 0).reshape(-1, 4),
                tag_off=_arr(res.tag_off, res.n_mems + 1), tags=_arr(res.tags, res.n_tags), n_runs=_arr(res.n_runs, res.n_mems))

@@ -82,6 +82,7 @@ struct pgi_index {
     uint64_t n_block_words = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
     std::mutex compute_mu;                                  // see pgi_find_mems
+    std::mutex upload_mu, download_mu;                      // one bulk copy per direction at a time (pgi_find_mems)
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
     int sm_count = 0;
 };
@@ -394,7 +395,7 @@ struct pgi_batch {
     DevBuf d_n_runs, d_cnt, d_raw_off, d_first, d_skip, d_raw, d_raw2, d_ucnt, d_tag_off, d_tags, d_large, d_seg_b, d_seg_e;
     PinBuf h_ctr, h_mem_off, h_mems, h_tag_off, h_tags, h_n_runs;
     double mems_per_read = 4.0;
-    uint64_t n_mems = 0, n_tags = 0, extensions = 0;
+    uint64_t n_mems = 0, n_tags = 0, extensions = 0, seed_lookups = 0;
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
     void release_all() {
@@ -478,11 +479,23 @@ void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_
     (void) launches;                                  // library (CUB) launches are not counted as ours
 }
 
-// counters in d_ctr / h_ctr (u64): [0] cursor, [1] mem_count, [2] ext_count, [3] large_count
-uint64_t read_back(pgi_batch *b, const void *dptr) {
-    CK(cudaMemcpyAsync(b->h_ctr.p, dptr, 8, cudaMemcpyDeviceToHost, b->stream));
+// counters in d_ctr / h_ctr (u64): [0] cursor, [1] mem_count, [2] ext_count, [3] large_count, [4] seed_count
+// A counter the host needs in the middle of a run is WRITTEN INTO PINNED HOST MEMORY BY A KERNEL (unified addressing: a
+// cudaHostAlloc pointer is valid on the device), not fetched with cudaMemcpyAsync: a copy, however small, queues on the
+// device-to-host copy engine behind the 200+ MB result download of whichever pgi_find_mems call finished just before, and
+// the compute token would be held idle for that long (concurrent callers, pgi_find_mems). Kernels do not queue there.
+__global__ void peek_kernel(const uint64_t *src, volatile uint64_t *host_dst, unsigned n) {
+    if (threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
+    __threadfence_system();
+}
+void peek(pgi_batch *b, const void *dptr, unsigned n) {
+    peek_kernel<<<1, 32, 0, b->stream>>>((const uint64_t *) dptr, b->h_ctr.as<uint64_t>(), n);
+    CK(cudaGetLastError());
     CK(cudaStreamSynchronize(b->stream));
-    return *b->h_ctr.as<uint64_t>();
+}
+uint64_t read_back(pgi_batch *b, const void *dptr) {
+    peek(b, dptr, 1);
+    return *b->h_ctr.as<volatile uint64_t>();
 }
 
 // K1 instantiations: block-fetch mode x CTA shape (pgi_kernels.cuh). PGI_K1=<name> picks one for tuning runs
@@ -519,13 +532,12 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
         a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
         a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
         a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0;
-        a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = cap;
+        a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
         if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(b->h_ctr.p, ctr, 32, cudaMemcpyDeviceToHost, b->stream));
-        CK(cudaStreamSynchronize(b->stream));
-        total = b->h_ctr.as<uint64_t>()[1]; b->extensions = b->h_ctr.as<uint64_t>()[2];
+        peek(b, ctr, 5);
+        total = b->h_ctr.as<volatile uint64_t>()[1]; b->extensions = b->h_ctr.as<volatile uint64_t>()[2]; b->seed_lookups = b->h_ctr.as<volatile uint64_t>()[4];
         if (total <= cap) break;
         cap = total + 1024; ++reruns;                    // append buffer overflowed: the count is exact, run again
     }
@@ -560,12 +572,12 @@ void run_count_stage(pgi_batch *b, int &launches) {
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0;
-    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.mem_cap = n;
+    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = n;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
     iota_kernel<<<grid_for(n + 1, 256), 256, 0, b->stream>>>(n + 1, b->d_mem_off.as<uint64_t>());
     ++launches; CK(cudaGetLastError());
-    b->extensions = read_back(b, ctr + 2);
+    b->extensions = read_back(b, ctr + 2); b->seed_lookups = 0;
     b->n_mems = n;
     CK(cudaEventRecord(b->ev[EV_MEM], b->stream)); CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
 }
@@ -685,7 +697,7 @@ extern "C" int pgi_batch_device_result(pgi_batch *b, pgi_result *out) {
     if (!b || !out) return fail(PGI_EINVAL, "null argument");
     if (!b->has_result) return fail(PGI_EINVAL, "no completed run on this batch");
     std::memset(out, 0, sizeof(*out));
-    out->n_reads = b->n_reads; out->n_mems = b->n_mems; out->n_tags = b->n_tags; out->extensions = b->extensions;
+    out->n_reads = b->n_reads; out->n_mems = b->n_mems; out->n_tags = b->n_tags; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups;
     out->mem_off = b->d_mem_off.as<uint64_t>(); out->mems = b->d_mems.as<pgi_mem>(); out->tag_off = b->d_tag_off.as<uint64_t>();
     out->tags = b->d_tags.as<uint64_t>(); out->n_runs = b->d_n_runs.as<uint64_t>();
     return PGI_OK;
@@ -706,7 +718,7 @@ extern "C" int pgi_batch_fetch(pgi_batch *b, pgi_result *out) {
         if (nm) CK(cudaMemcpyAsync(b->h_n_runs.p, b->d_n_runs.p, nm * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         std::memset(out, 0, sizeof(*out));
-        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = b->extensions;
+        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups;
         out->mem_off = b->h_mem_off.as<uint64_t>(); out->mems = b->h_mems.as<pgi_mem>(); out->tag_off = b->h_tag_off.as<uint64_t>();
         out->tags = b->h_tags.as<uint64_t>(); out->n_runs = b->h_n_runs.as<uint64_t>();
         return PGI_OK;
@@ -732,17 +744,24 @@ static int one_call(pgi_index *ix, bool count_mode, const char *reads, const uin
     static const auto t_origin = std::chrono::steady_clock::now();
     auto now_ms = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_origin).count(); };
     const double t0 = trace ? now_ms() : 0;
-    int rc = pgi_batch_upload(b, reads, read_off, n_reads);
+    // One upload at a time: concurrent callers that share the host-to-device link evenly ALL finish late (three 316 MB
+    // uploads side by side: 17.6 ms until the first kernel can start; one after the other: 5.7 ms), and the same for the
+    // result downloads. In steady state the pipeline is compute bound either way; this shortens its ramp-up and drain.
+    int rc;
+    {
+        std::lock_guard<std::mutex> up(ix->upload_mu);
+        rc = pgi_batch_upload(b, reads, read_off, n_reads);
+        if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
+    }
     double t1 = 0;
     // Concurrent callers pipeline instead of interleaving: the host->device copy is waited for OUTSIDE the compute token,
     // the kernels of one call at a time own the GPU (a persistent grid fills every SM anyway; two of them interleaved only
     // delay each other's short follow-up kernels), and the device->host copy again runs outside the token. In steady state
     // call k+1 uploads and call k-1 downloads while call k computes.
-    if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
     if (trace) t1 = now_ms();
     if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = batch_run(b, count_mode, min_len, min_occ); }
     const double t2 = trace ? now_ms() : 0;
-    if (rc == PGI_OK) rc = pgi_batch_fetch(b, out);
+    if (rc == PGI_OK) { std::lock_guard<std::mutex> down(ix->download_mu); rc = pgi_batch_fetch(b, out); }
     if (trace) std::fprintf(stderr, "[pgi] ctx %p reads %llu: enter %.2f uploaded %.2f run_done %.2f (mem kernel %.2f, stages %.2f ms) fetched %.2f\n", (void *) b,
                             (unsigned long long) n_reads, t0, t1, t2, b->stage_ms[0], b->stage_ms[5], now_ms());
     b->stream = own;
@@ -780,7 +799,7 @@ extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *st
         int launches = 0;
         CK(cudaEventRecord(b->ev[EV_START], b->stream));
         run_tag_stage(b, n, nullptr, ds, de, launches);
-        b->n_reads = 0; b->n_mems = n; b->extensions = 0; b->has_result = true;
+        b->n_reads = 0; b->n_mems = n; b->extensions = 0; b->seed_lookups = 0; b->has_result = true;
         b->d_mem_off.need(8); CK(cudaMemsetAsync(b->d_mem_off.p, 0, 8, b->stream));
         b->d_mems.need(std::max<uint64_t>(1, n) * 32);
         b->read_off = nullptr;

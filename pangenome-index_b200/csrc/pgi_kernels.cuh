@@ -25,7 +25,8 @@ struct MemArgs {
     uint64_t n_reads, min_len, min_occ;
     unsigned long long *cursor;    // next unassigned read
     unsigned long long *mem_count; // MEMs appended so far (keeps counting past mem_cap)
-    unsigned long long *ext_count; // FMD extensions executed
+    unsigned long long *ext_count; // FMD extensions of the reference algorithm (a seed lookup counts as its seed_k extensions)
+    unsigned long long *seed_count;// seed lookups that replaced seed_k extensions each
     uint64_t mem_cap;
     uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
     uint64_t *mem_key;             // read id << 32 | index of the MEM within its read
@@ -93,7 +94,6 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     __shared__ uint32_t s_desc[512];
     __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
     __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
-    __shared__ uint4 s_seed[OP == 0 ? THREADS : 1];              // per lane: the seed-table entry fetched by this trip's cp.async group
     for (int i = threadIdx.x; i < 512; i += blockDim.x) {
         s_desc[i] = a.desc[i];
         if (MODE) s_tab[i] = reinterpret_cast<const uint4 *>(a.desc + 512)[i];
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + ((lane >> 2) * 4u + ((lane & 3u) ^ ((lane >> 3) & 3u))) * 16u;
     MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
-    uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0;
+    uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0, n_seed = 0;
     bool exhausted = false, have = false;
     bool stepwise = false;                       // the seed lookup of the pending walk was tried and is not usable: extend step by step
     const uint32_t seed_k = OP == 0 ? a.seed_k : 0u;
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
                 const BiInt t = seed_unpack(q);
                 ok = !ext_failed(t, a.min_occ);
-                if (ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; }
+                if (ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; ++n_seed; }
             }
             stepwise = !ok;
         }
@@ -259,7 +259,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 if (cand) {
                     uint32_t sidx = 0;
                     seed_ok = seed_index(sw0, sw1, sw2, ssh, seed_k, sidx);
-                    cp_async16_if((uint32_t) __cvta_generic_to_shared(s_seed + threadIdx.x), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
+                    // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
+                    // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
+                    cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + lane * 4u), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
                 }
             }
             cp_async_wait_all();
@@ -315,11 +317,11 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             }
             if (OP == 0 && cand) {
                 if (seed_ok) {
-                    const uint4 e = s_seed[threadIdx.x];
+                    const uint4 e = wstage[lane * 4u];
                     SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
                     const BiInt t = seed_unpack(q);
                     seed_ok = !ext_failed(t, a.min_occ);
-                    if (seed_ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; }
+                    if (seed_ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; ++n_seed; }
                 }
                 stepwise = !seed_ok;                          // other bytes / too few occurrences: the walk goes step by step
             }
@@ -329,6 +331,11 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     unsigned long long tot = n_ext;
     for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
     if (lane == 0 && tot) atomicAdd(a.ext_count, tot);
+    if (OP == 0 && seed_k) {
+        unsigned tots = n_seed;
+        for (int o = 16; o; o >>= 1) tots += __shfl_xor_sync(FULL, tots, o);
+        if (lane == 0 && tots) atomicAdd(a.seed_count, (unsigned long long) tots);
+    }
 }
 
 // K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read.
