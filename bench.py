@@ -56,7 +56,7 @@ class ClockSampler(threading.Thread):
     nvidia-smi remains the fallback, on rank 0 only, at a 1 s period."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
     def __init__(self, gpu, rank=0):
-        super().__init__(daemon=True); self.gpu = gpu; self.rank = rank; self.rows = []; self.stop_flag = False; self.h = None; self.nv = None
+        super().__init__(daemon=True); self.gpu = gpu; self.rank = rank; self.rows = []; self.stop_flag = False; self.h = None; self.nv = None; self.extra = []
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -76,6 +76,10 @@ class ClockSampler(threading.Thread):
                  bit("nvmlClocksEventReasonHwThermalSlowdown", "nvmlClocksThrottleReasonHwThermalSlowdown"),
                  bit("nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"),
                  bit("nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap")]
+        try:
+            self.extra.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_MEM), nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0, r))
+        except Exception:
+            pass
         return [str(sm), str(mx)] + ["Active" if (r & f) else "Not Active" for f in flags]
     def run(self):
         while not self.stop_flag:
@@ -94,7 +98,13 @@ class ClockSampler(threading.Thread):
         mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(self.rows)}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(self.rows)}
+        if self.extra:
+            out["mem_mhz"] = float(np.median([e[0] for e in self.extra])); out["power_w_max"] = round(max(e[1] for e in self.extra), 1)
+            m = 0
+            for e in self.extra: m |= e[2]
+            out["reasons_mask_or"] = hex(m)
+        return out
 
 E2E_CALLERS = 3
 
@@ -190,6 +200,21 @@ def main():
     if capi.lib().pgi_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device; the find_mems path has no CPU fallback")
     torch.cuda.set_device(local)
+    # One process per GPU: run on the CPU cores next to this GPU (NVML's affinity mask), so that pinned staging buffers are
+    # allocated on the GPU's own NUMA node and stream synchronisations wake a near core (r01r, 8 GPUs: ranks 0-3 moved
+    # their results at 31 ms per step, ranks 4-7 at 22 ms). The CPU legs widen it again (host_threads).
+    orig_affinity = None
+    if world > 1:
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            orig_affinity = os.sched_getaffinity(0)
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", ""); idx = local
+            if vis and all(x.strip().isdigit() for x in vis.split(",")): idx = int(vis.split(",")[local])
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(idx))
+            if not (os.sched_getaffinity(0) & orig_affinity): os.sched_setaffinity(0, orig_affinity)
+        except Exception as e:
+            log("cpu affinity not set:", e)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -227,13 +252,13 @@ def main():
     sampler = ClockSampler(local, rank); sampler.start()
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0
+    k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0; seed_total = 0
     e0.record(stream); host_gap = []; t_prev = time.perf_counter()
     for i in range(args.steps):
         step_device(args.warmup + i)
         t_now = time.perf_counter(); host_gap.append(1e3 * (t_now - t_prev)); t_prev = t_now      # host wall time of the step (diagnostic)
         ms = batch.stage_ms(); stage += np.array(ms); k1_ms += ms[0]; launches += int(ms[6]) + 0
-        r = batch.device_result(); ext_total += r.extensions; mems_total += r.n_mems; tags_total += r.n_tags
+        r = batch.device_result(); ext_total += r.extensions; mems_total += r.n_mems; tags_total += r.n_tags; seed_total += r.seed_lookups
     e1.record(stream)
     barrier()
     dev_ms = e0.elapsed_time(e1)
@@ -275,6 +300,9 @@ def main():
     total_reads = n * args.steps * world
     value = total_reads / (dev_ms * 1e-3); e2e = total_reads / (e2e_ms * 1e-3)
     # ---- CPU oracle: parity on a sample + work counters + cpu_baseline (rank 0, not timed against the GPU)
+    if orig_affinity:
+        try: os.sched_setaffinity(0, orig_affinity)          # the CPU legs use every host core again
+        except Exception: pass
     import orc
     o = orc.Index(w["ri"], w["tags"], w["layout"])
     reads_np = h_reads[0][: n * L].numpy()
@@ -357,6 +385,8 @@ def main():
             "stage_ms_per_step": {k: round(float(v) / args.steps, 3) for k, v in zip(["fmd_mem_kernel", "mem_order", "tag_plan", "tag_decode_sort", "tag_unique_compact", "run_total"], stage[:6])},
             "roofline": {"bound": "hbm", "kernel": "fmd_mem_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": k1_bytes_per_launch,
+                         "seed_lookups_per_launch": seed_total // args.steps, "executed_extensions_per_launch": (ext_rank0 - seed_total * ix.info["seed_k"]) // args.steps,
+                         "traffic_gbs": (traffic / k1_s / 1e9) if traffic else None, "frac_traffic": (traffic / k1_s / 1e9 / peak) if traffic else None,
                          "bytes_model": "128 B x D, D = distinct reference 10-run blocks touched per extension (oracle: D/E = %.3f) x E = %d extensions per launch (the reference algorithm's count = the oracle's E; with seed_k > 0 the first seed_k extensions of a walk from the full interval are ONE 16-byte table lookup, so the kernel moves fewer bytes than the algorithm names and frac may exceed 1)" % (d_per_e, ext_rank0 // args.steps),
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
             "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",

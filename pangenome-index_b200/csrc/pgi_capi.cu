@@ -381,14 +381,15 @@ extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **
 }
 
 // ------------------------------------------------------------------------------------------ batch context
-enum { EV_START = 0, EV_MEM, EV_ORDER, EV_PLAN, EV_DECODE, EV_END, EV_COUNT };
+enum { EV_START = 0, EV_MEM, EV_ORDER, EV_PLAN, EV_DECODE, EV_END, EV_K1A, EV_K1B, EV_COUNT };   // K1A / K1B: around the K1 launch alone
 
 struct pgi_batch {
     pgi_index *ix = nullptr;
     cudaStream_t stream = nullptr; bool own_stream = false;
     cudaEvent_t ev[EV_COUNT]; bool ev_ok = false;
     // inputs
-    DevBuf d_reads, d_read_off; const uint64_t *reads64 = nullptr; const uint64_t *read_off = nullptr; uint64_t n_reads = 0;
+    DevBuf d_reads, d_read_off; const uint64_t *reads64 = nullptr; const uint64_t *read_off = nullptr; uint64_t n_reads = 0, reads_bytes = 0;
+    DevBuf d_codes, d_read_flags;                            // 2-bit codes of the reads + per-read "other bytes" flags (seed lookups)
     // MEM stage
     DevBuf d_ctr, d_mem_buf, d_mem_key, d_nmems, d_mem_off, d_mems, d_cub;
     // tag stage
@@ -399,7 +400,7 @@ struct pgi_batch {
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
     void release_all() {
-        DevBuf *db[] = {&d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
+        DevBuf *db[] = {&d_codes, &d_read_flags, &d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
                         &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e};
         for (DevBuf *b : db) b->release();
         PinBuf *pb[] = {&h_ctr, &h_mem_off, &h_mems, &h_tag_off, &h_tags, &h_n_runs};
@@ -453,6 +454,7 @@ extern "C" int pgi_batch_upload(pgi_batch *b, const char *reads, const uint64_t 
         CK(cudaMemsetAsync((char *) b->d_reads.p + total, 0, 16, b->stream));
         CK(cudaMemcpyAsync(b->d_read_off.p, read_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, b->stream));
         b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false;
+        b->reads_bytes = total;
         return PGI_OK;
     } catch (const CudaError &e) { return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
 }
@@ -460,7 +462,7 @@ extern "C" int pgi_batch_upload(pgi_batch *b, const char *reads, const uint64_t 
 extern "C" int pgi_batch_set_device_reads(pgi_batch *b, const char *d_reads, const uint64_t *d_read_off, uint64_t n_reads, uint64_t total_bytes) {
     if (!b || !d_read_off || (!d_reads && n_reads)) return fail(PGI_EINVAL, "null argument");
     if (((uintptr_t) d_reads & 7) != 0) return fail(PGI_EINVAL, "device reads must be 8-byte aligned");
-    (void) total_bytes;
+    b->reads_bytes = total_bytes;
     b->reads64 = (const uint64_t *) d_reads; b->read_off = d_read_off; b->n_reads = n_reads; b->has_result = false;
     return PGI_OK;
 }
@@ -524,6 +526,17 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, want_blocks));
     unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
     uint64_t total = 0;
+    if (ix->seed_k && n) {                                   // K0: 2-bit codes + per-read flags for the seed lookups
+        const uint64_t n_words = (b->reads_bytes + 7) / 8;
+        b->d_codes.need(n_words * 2 + 16); b->d_read_flags.need((n / 32 + 1) * 4);
+        CK(cudaMemsetAsync(b->d_read_flags.p, 0, (n / 32 + 1) * 4, b->stream));
+        CK(cudaMemsetAsync((char *) b->d_codes.p + n_words * 2, 0, 16, b->stream));
+        if (n_words) {
+            pack_reads_kernel<<<grid_for(n_words, 256), 256, 0, b->stream>>>(b->reads64, n_words, b->reads_bytes, b->read_off, n,
+                                                                              b->d_codes.as<uint16_t>(), b->d_read_flags.as<uint32_t>());
+            ++launches; CK(cudaGetLastError());
+        }
+    }
     for (;;) {
         b->d_mem_buf.need(cap * 32); b->d_mem_key.need(cap * 8);
         CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
@@ -531,11 +544,13 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
         MemArgs a;
         a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
         a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
-        a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0;
+        a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
         a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
+        CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
         if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
         CK(cudaGetLastError());
+        CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
         peek(b, ctr, 5);
         total = b->h_ctr.as<volatile uint64_t>()[1]; b->extensions = b->h_ctr.as<volatile uint64_t>()[2]; b->seed_lookups = b->h_ctr.as<volatile uint64_t>()[4];
         if (total <= cap) break;
@@ -571,10 +586,12 @@ void run_count_stage(pgi_batch *b, int &launches) {
     CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
-    a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0;
+    a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
     a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = n;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
+    CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
+    CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
     iota_kernel<<<grid_for(n + 1, 256), 256, 0, b->stream>>>(n + 1, b->d_mem_off.as<uint64_t>());
     ++launches; CK(cudaGetLastError());
     b->extensions = read_back(b, ctr + 2); b->seed_lookups = 0;
@@ -676,7 +693,9 @@ static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t m
         }
         CK(cudaEventRecord(b->ev[EV_END], b->stream));
         CK(cudaStreamSynchronize(b->stream));
-        b->stage_ms[0] = ev_ms(b, EV_START, EV_MEM); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
+        // [0] the K1 launch alone (device time between two in-stream events; EV_START..EV_MEM also holds the pre-pass, the
+        // counter read-back and the host's wake-up from it, which is host time on a busy multi-GPU box)
+        b->stage_ms[0] = ev_ms(b, EV_K1A, EV_K1B); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
         b->stage_ms[3] = ev_ms(b, EV_PLAN, EV_DECODE); b->stage_ms[4] = ev_ms(b, EV_DECODE, EV_END); b->stage_ms[5] = ev_ms(b, EV_START, EV_END);
         b->stage_ms[6] = launches; b->stage_ms[7] = reruns;
         b->has_result = true;

@@ -353,27 +353,28 @@ PGI_HD BiInt seed_unpack(const SeedWord &e) {
     return b;
 }
 PGI_HD uint8_t seed_symbol(uint32_t code) { return (uint8_t) ("ACTG"[code & 3u]); }
-// w0, w1, w2: the aligned 8-byte words holding the window (w1 / w2 may be anything when the window does not reach
-// them), sh = 8 * (lo & 7). Returns false when one of the K bytes is not exactly 'A', 'C', 'G' or 'T'.
-PGI_HD bool seed_index(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t sh, uint32_t K, uint32_t &idx) {
-    const uint64_t lo = sh ? (w0 >> sh) | (w1 << (64u - sh)) : w0;
-    const uint32_t hi = (uint32_t) (sh ? (w1 >> sh) | (w2 << (64u - sh)) : w1);
-    uint32_t bad = 0, id = 0;
-#pragma unroll
-    for (uint32_t g = 0; g < 3; ++g) {
-        const uint32_t v = g == 0 ? (uint32_t) lo : g == 1 ? (uint32_t) (lo >> 32) : hi;
-        const uint32_t c = (v >> 1) & 0x03030303u;
-        const uint32_t tf = (c >> 1) & ~c & 0x01010101u;                              // 'T' (code 2) is the one with bit 0 clear and bit 4 set
-        const uint32_t e = 0x40404040u | c << 1 | (tf ^ 0x01010101u) | tf << 4;       // the byte each code stands for
-        const uint32_t nb = K > 4u * g ? K - 4u * g : 0u;                             // bytes of this word inside the window
-        const uint32_t bm = nb >= 4u ? 0xFFFFFFFFu : (1u << (8u * nb)) - 1u;
-        bad |= (e ^ v) & bm;
-        uint32_t x = (c | c >> 6) & 0x000F000Fu;
-        x = (x | x >> 12) & 0xFFu;
-        id |= x << (8u * g);
-    }
-    idx = K >= 16u ? id : id & ((1u << (2u * K)) - 1u);
-    return bad == 0;
+// The reads of a batch are packed once by a streaming pass (pack_reads_kernel): 2 bits per byte, byte p of the reads
+// buffer at bits [2p, 2p + 2) of a little-endian bit stream (one 16-bit unit per aligned 8-byte word), plus one flag per
+// read that holds a byte other than 'A', 'C', 'G', 'T' (such a read never uses the table). The index of a window is then
+// two 32-bit loads and a funnel shift.
+// Codes of the 8 bytes of a word; bad_bytes bit i = byte i is not exactly 'A', 'C', 'G' or 'T'.
+PGI_HD uint32_t seed_pack8(uint64_t w, uint32_t &bad_bytes) {
+    const uint64_t c = (w >> 1) & 0x0303030303030303ull;
+    const uint64_t tf = (c >> 1) & ~c & 0x0101010101010101ull;                         // 'T' (code 2): bit 0 clear, bit 4 set
+    const uint64_t e = 0x4040404040404040ull | c << 1 | (tf ^ 0x0101010101010101ull) | tf << 4;   // the byte each code stands for
+    uint64_t d = e ^ w;
+    d |= d >> 4; d |= d >> 2; d |= d >> 1; d &= 0x0101010101010101ull;
+    bad_bytes = (uint32_t) ((d * 0x0102040810204080ull) >> 56);
+    uint64_t x = (c | c >> 6) & 0x000F000F000F000Full;
+    x = (x | x >> 12) & 0x000000FF000000FFull;
+    x = (x | x >> 24) & 0xFFFFull;
+    return (uint32_t) x;
+}
+// Index of the window starting at byte lo of the reads buffer: c0, c1 = the 32-bit units (2 lo) >> 5 and the next one.
+PGI_HD uint32_t seed_index_packed(uint32_t c0, uint32_t c1, uint64_t lo, uint32_t K) {
+    const uint32_t sh = (uint32_t) (2u * lo) & 31u;
+    const uint32_t v = sh ? (c0 >> sh) | (c1 << (32u - sh)) : c0;
+    return K >= 16u ? v : v & ((1u << (2u * K)) - 1u);
 }
 // Does the extension lane_settle just asked for start from the full interval with K symbols in reach?
 PGI_HD bool lane_seed_ready(const MemLane &L, uint32_t K, uint64_t n) {

@@ -31,6 +31,8 @@ struct MemArgs {
     uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
     uint64_t *mem_key;             // read id << 32 | index of the MEM within its read
     uint64_t *read_nmems;          // n_reads (+1) MEM counts per read
+    const uint32_t *codes32;       // 2-bit codes of the reads buffer (pack_reads_kernel), viewed as 32-bit units
+    const uint32_t *read_flags;    // bit r: read r holds a byte other than A / C / G / T (no seed lookups for it)
     const uint4 *seed;             // seed table (pgi_core.cuh): 4^seed_k entries of 16 bytes, or nullptr
     uint32_t seed_k, pad;          // 0: no table (OP 1, indexes with a quirk slot, PGI_SEEDK=0)
 };
@@ -109,7 +111,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0, n_seed = 0;
     bool exhausted = false, have = false;
-    bool stepwise = false;                       // the seed lookup of the pending walk was tried and is not usable: extend step by step
+    // 1: the seed lookup of the pending walk was tried and its entry fails the occurrence test: extend step by step;
+    // 2: the read holds a byte other than A / C / G / T: no lookups at all (until the next read)
+    uint32_t stepwise = 0;
     const uint32_t seed_k = OP == 0 ? a.seed_k : 0u;
     for (;;) {
         // ---- hand out reads to idle lanes
@@ -127,6 +131,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 const uint32_t id = wq_next + __popc(m & lt_mask);
                 if (id < wq_end) {
                     rd = id; have = true; nm = 0;
+                    if (OP == 0 && seed_k) stepwise = ((__ldg(a.read_flags + (id >> 5)) >> (id & 31u)) & 1u) ? 2u : 0u;
                     const uint64_t o0 = __ldcs(a.read_off + id), o1 = __ldcs(a.read_off + id + 1);
                     base = o0;
                     if (OP == 0) lane_begin(L, o1 - o0, min_len, a.ix.n);
@@ -137,6 +142,10 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     }
                     const char *rp = reinterpret_cast<const char *>(a.reads64) + base;      // pull the read towards L2
                     for (uint32_t o = 0; o < L.len && o < 512; o += 128) prefetch_l2(rp + o);
+                    if (OP == 0 && seed_k && !stepwise) {                   // and its 2-bit codes (a quarter of the bytes): the seed lookups read them
+                        const char *cp = reinterpret_cast<const char *>(a.codes32) + (base >> 2);
+                        for (uint32_t o = 0; o < (L.len >> 2) + 4u && o < 1024; o += 128) prefetch_l2(cp + o);
+                    }
                 }
             }
             const uint32_t adv = wq_next + __popc(m);
@@ -179,16 +188,13 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         // reach fetches ONE table entry in this trip instead of its run blocks and advances seed_k steps at once. The
         // window of the read is requested here; the index is formed and the entry's cp.async joins the block fetch's
         // group below, so the lookup costs no dependent latency beyond the one the trip pays anyway.
-        bool cand = false; uint64_t sw0 = 0, sw1 = 0, sw2 = 0; uint32_t ssh = 0;
+        bool cand = false; uint32_t sc0 = 0, sc1 = 0;
         if (OP == 0 && seed_k) {
             cand = need && !stepwise && lane_seed_ready(L, seed_k, a.ix.n);
             if (cand) {
-                const uint64_t lo = base + L.j + 1u - seed_k; const uint32_t o = (uint32_t) lo & 7u;
-                const uint64_t *p = a.reads64 + (lo >> 3);
-                sw0 = __ldg(p);
-                if (o + seed_k > 8u) sw1 = __ldg(p + 1);                  // words the window does not reach are not touched
-                if (o + seed_k > 16u) sw2 = __ldg(p + 2);
-                ssh = o * 8u;
+                const uint64_t slo = base + L.j + 1u - seed_k;           // first byte of the window
+                const uint32_t *p = a.codes32 + (slo >> 4);              // bit 2 lo of the code stream
+                sc0 = __ldg(p); sc1 = __ldg(p + 1);
                 need = false;                                             // no run blocks for this lane in this trip
             }
         }
@@ -204,19 +210,19 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         }
         if (MODE == 0 && has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
         if (MODE == 0 && OP == 0 && cand) {
-            uint32_t sidx = 0; bool ok = seed_index(sw0, sw1, sw2, ssh, seed_k, sidx);
-            if (ok) {
-                const uint4 e = __ldg(a.seed + sidx);
+            bool ok = true;
+            {
+                const uint4 e = __ldg(a.seed + seed_index_packed(sc0, sc1, base + L.j + 1u - seed_k, seed_k));
                 SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
                 const BiInt t = seed_unpack(q);
                 ok = !ext_failed(t, a.min_occ);
                 if (ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; ++n_seed; }
             }
-            stepwise = !ok;
+            stepwise = ok ? 0u : 1u;
         }
         if (MODE == 0) {
             if (need) {
-                stepwise = false;
+                stepwise &= 2u;
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
                 t = extend_desc(a.ix, t, s_desc[(fwd ? 256u : 0u) + sym]);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
@@ -257,8 +263,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             bool seed_ok = false;
             if (OP == 0 && seed_k && __any_sync(FULL, cand)) {
                 if (cand) {
-                    uint32_t sidx = 0;
-                    seed_ok = seed_index(sw0, sw1, sw2, ssh, seed_k, sidx);
+                    const uint32_t sidx = seed_index_packed(sc0, sc1, base + L.j + 1u - seed_k, seed_k);
+                    seed_ok = true;
                     // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
                     // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
                     cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + lane * 4u), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
@@ -313,7 +319,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 if (OP == 0) lane_after_ext(L, u, min_len, a.min_occ, a.ix.n);
                 else if (ext_failed(u, 0)) L.phase = PH_DONE;                            // LF returned {1, 0}: stays empty
                 else { L.b = u; --L.j; }
-                stepwise = false;                             // whatever walk comes next may use the table again
+                stepwise &= 2u;                               // whatever walk comes next may use the table again
             }
             if (OP == 0 && cand) {
                 if (seed_ok) {
@@ -323,7 +329,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     seed_ok = !ext_failed(t, a.min_occ);
                     if (seed_ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; ++n_seed; }
                 }
-                stepwise = !seed_ok;                          // other bytes / too few occurrences: the walk goes step by step
+                stepwise = seed_ok ? 0u : 1u;                 // too few occurrences: the walk goes step by step
             }
             __syncwarp();                                     // the staging area is rewritten by the next trip
         }
@@ -335,6 +341,25 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         unsigned tots = n_seed;
         for (int o = 16; o; o >>= 1) tots += __shfl_xor_sync(FULL, tots, o);
         if (lane == 0 && tots) atomicAdd(a.seed_count, (unsigned long long) tots);
+    }
+}
+
+// K0. Streaming pre-pass for the seed lookups (pgi_core.cuh "seed table"): one thread per aligned 8-byte word of the reads
+// buffer writes the word's eight 2-bit codes; a byte other than A / C / G / T (rare: N, lower case) flags the read that
+// holds it (binary search over read_off, only then). codes16 has n_words + 4 units (the lookups load two 32-bit units).
+__global__ void pack_reads_kernel(const uint64_t *reads64, uint64_t n_words, uint64_t n_bytes, const uint64_t *read_off, uint64_t n_reads,
+                                  uint16_t *codes16, uint32_t *read_flags) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n_words) return;
+    uint32_t bad;
+    codes16[i] = (uint16_t) seed_pack8(__ldcs(reads64 + i), bad);
+    while (bad) {
+        const uint32_t bi = __ffs(bad) - 1u; bad &= bad - 1u;
+        const uint64_t pos = 8u * i + bi;
+        if (pos >= n_bytes) break;                                       // padding behind the last read
+        uint64_t lo = 0, hi = n_reads;                                   // last r with read_off[r] <= pos
+        while (hi - lo > 1) { const uint64_t mid = (lo + hi) >> 1; if (__ldg(read_off + mid) <= pos) lo = mid; else hi = mid; }
+        atomicOr(read_flags + (lo >> 5), 1u << (lo & 31u));
     }
 }
 

@@ -77,7 +77,15 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
     const uint64_t base = (len * 7 + 3) % 29;
     std::vector<uint64_t> words((base + len) / 8 + 2, 0x5A5A5A5A5A5A5A5Aull);
     std::memcpy((char *) words.data() + base, read, len);
-    bool stepwise = false; const uint32_t K = s->seed_k;
+    const uint32_t K = s->seed_k;
+    // pack_reads_kernel, word for word: 2-bit codes (16 per 32-bit unit) and the "other bytes" flag of this read
+    std::vector<uint32_t> codes(words.size() / 2 + 2, 0); bool other_bytes = false;
+    for (size_t i = 0; i < words.size(); ++i) {
+        uint32_t bad; const uint32_t c = seed_pack8(words[i], bad);
+        codes[i / 2] |= c << (16 * (i & 1));
+        for (uint32_t bi = 0; bi < 8; ++bi) if (((bad >> bi) & 1u) && 8 * i + bi >= base && 8 * i + bi < base + len) other_bytes = true;
+    }
+    uint32_t stepwise = other_bytes ? 2u : 0u;
     for (;;) {
         const int st = lane_settle(L, (uint32_t) min_len, s->rd.n);
         if (st == LANE_EMIT) {
@@ -86,19 +94,14 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
         }
         if (st != LANE_EXTEND) break;
         if (K && !stepwise && lane_seed_ready(L, K, s->rd.n)) {                     // fmd_mem_kernel's seed lookup, trip for trip
-            const uint64_t lo = base + L.j + 1u - K; const uint32_t o = (uint32_t) lo & 7u;
-            const uint64_t *p = words.data() + (lo >> 3);
-            const uint64_t w0 = p[0], w1 = o + K > 8u ? p[1] : 0, w2 = o + K > 16u ? p[2] : 0;
-            uint32_t idx = 0; bool ok = seed_index(w0, w1, w2, o * 8u, K, idx);
-            if (ok) {
-                const BiInt t = seed_unpack(s->seed[idx]);
-                ok = !ext_failed(t, min_occ);
-                if (ok) { lane_seed_apply(L, t, K, (uint32_t) min_len); ext += K; }
-            }
-            stepwise = !ok;
+            const uint64_t lo = base + L.j + 1u - K;
+            const BiInt t = seed_unpack(s->seed[seed_index_packed(codes[lo >> 4], codes[(lo >> 4) + 1], lo, K)]);
+            const bool ok = !ext_failed(t, min_occ);
+            if (ok) { lane_seed_apply(L, t, K, (uint32_t) min_len); ext += K; }
+            stepwise = ok ? 0u : 1u;
             continue;
         }
-        stepwise = false;
+        stepwise &= 2u;
         const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
         BiInt t = L.b;
         if (L.phase == PH_P2) { std::swap(t.k, t.kp); t = extend_desc(s->rd, t, s->ri.k.desc_f[a]); std::swap(t.k, t.kp); }
