@@ -77,7 +77,13 @@ class ClockSampler(threading.Thread):
                  bit("nvmlClocksEventReasonSwThermalSlowdown", "nvmlClocksThrottleReasonSwThermalSlowdown"),
                  bit("nvmlClocksEventReasonSwPowerCap", "nvmlClocksThrottleReasonSwPowerCap")]
         try:
-            self.extra.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_MEM), nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0, r))
+            temp = nv.nvmlDeviceGetTemperature(self.h, nv.NVML_TEMPERATURE_GPU); mtemp = None
+            try:
+                fv = nv.nvmlDeviceGetFieldValues(self.h, [nv.NVML_FI_DEV_MEMORY_TEMP])[0]
+                if fv.nvmlReturn == 0: mtemp = int(fv.value.uiVal)
+            except Exception:
+                pass
+            self.extra.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_MEM), nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0, r, temp, mtemp))
         except Exception:
             pass
         return [str(sm), str(mx)] + ["Active" if (r & f) else "Not Active" for f in flags]
@@ -104,6 +110,9 @@ class ClockSampler(threading.Thread):
             m = 0
             for e in self.extra: m |= e[2]
             out["reasons_mask_or"] = hex(m)
+            out["gpu_temp_c_max"] = max(e[3] for e in self.extra)
+            mt = [e[4] for e in self.extra if e[4] is not None]
+            out["hbm_temp_c_max"] = max(mt) if mt else None
         return out
 
 E2E_CALLERS = 3
@@ -249,7 +258,8 @@ def main():
 
     # ---- device-resident timing (value)
     for i in range(args.warmup): step_device(i)
-    sampler = ClockSampler(local, rank); sampler.start()
+    sampler = ClockSampler(local, rank)
+    if not os.environ.get("PGI_BENCH_NOSAMPLER"): sampler.start()          # diagnostic switch (tools/placement_probe.py)
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0; seed_total = 0
@@ -283,7 +293,8 @@ def main():
     barrier()
     e2e_ms, d2h = e2e_pass(args.steps, args.warmup)
     barrier()
-    sampler.stop_flag = True; sampler.join(timeout=2)
+    sampler.stop_flag = True
+    if sampler.is_alive(): sampler.join(timeout=2)
     # ---- max over ranks
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([launches, ext_total, mems_total, tags_total], dtype=torch.float64, device="cuda")

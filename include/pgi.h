@@ -186,7 +186,8 @@ int pgi_batch_create(pgi_index *, void *cuda_stream /* or NULL */, pgi_batch **o
 void pgi_batch_free(pgi_batch *);
 /* Asynchronously stage host reads into the batch's device buffers (pinned source recommended). */
 int pgi_batch_upload(pgi_batch *, const char *reads, const uint64_t *read_off, uint64_t n_reads);
-/* Use reads already resident in device memory (d_reads must be readable up to the next multiple of 8 bytes). */
+/* Use reads already resident in device memory (d_reads: 8-byte aligned and readable up to the next multiple of 8 bytes;
+ * total_bytes = d_read_off[n_reads], the byte length of the reads -- the seed pre-pass packs exactly that many bytes). */
 int pgi_batch_set_device_reads(pgi_batch *, const char *d_reads, const uint64_t *d_read_off,
                                uint64_t n_reads, uint64_t total_bytes);
 /* Run MEM finding + tag lookup on the staged reads; results stay in HBM. Returns after the last kernel

@@ -513,6 +513,24 @@ const K1Variant &k1_variant() {
     return table[0];
 }
 
+// The persistent grid is sized for the occupancy the kernel's static shared memory allows (4 CTAs x 43 KB per SM). With the
+// default carve-out preference the driver chooses the shared-memory configuration itself; asking for the smallest one that
+// holds all those CTAs makes the occupancy the grid was sized for a fact instead of a heuristic. (Measured: no difference
+// to the driver's default on the boxes tried; the 8.8 <-> 10.7 ms spread of this kernel between GPUs, processes and even
+// launches -- DESIGN.md section 6 -- is NOT caused by the carve-out: it appears with every setting.)
+static void prefer_max_shared(void (*fn)(const MemArgs)) {
+    // the smallest configuration that holds every CTA the other limits allow (PGI_CARVEOUT=<percent> overrides, -1 = driver default)
+    const void *f = reinterpret_cast<const void *>(fn);
+    cudaFuncAttributes at; CK(cudaFuncGetAttributes(&at, f));
+    int dev = 0, smem_sm = 0, blocks = 0; CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks, f, at.maxThreadsPerBlock, 0));
+    int pct = (int) ((100.0 * blocks * (double) (at.sharedSizeBytes + 1024)) / (double) smem_sm) + 1;
+    if (const char *e = std::getenv("PGI_CARVEOUT")) pct = std::atoi(e);
+    if (pct > 100) pct = 100;
+    CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+}
+
 // MEM finding: K1 (+ re-run with a larger append buffer if it overflowed), scan, scatter.
 void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launches, int &reruns) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
@@ -520,6 +538,7 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     uint64_t cap = std::max<uint64_t>(1024, (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
     int blocks_per_sm = 0;
     const K1Variant &k1 = k1_variant();
+    prefer_max_shared(k1.fn);
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k1.fn, (int) k1.threads, 0));
     if (blocks_per_sm < 1) blocks_per_sm = 1;
     const uint64_t want_blocks = (n + k1.threads - 1) / k1.threads;
@@ -578,6 +597,7 @@ void run_count_stage(pgi_batch *b, int &launches) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
     b->d_mem_off.need((n + 1) * 8); b->d_mems.need(std::max<uint64_t>(1, n) * 32);
     void (*fn)(const MemArgs) = fmd_mem_kernel<1, 256, 4, 1>; const unsigned threads = 256;
+    prefer_max_shared(fn);
     int blocks_per_sm = 0;
     CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fn, (int) threads, 0));
     if (blocks_per_sm < 1) blocks_per_sm = 1;
