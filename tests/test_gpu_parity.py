@@ -272,6 +272,10 @@ def test_seed_table_is_invisible(capi, K, monkeypatch):
         G = g.find_mems(reads, off, ml, mo); R = o.find_mems(reads, off, ml, mo, count_work=True)
         compare(G, R, True)
         assert G["extensions"] == R["counters"]["E"], (ml, mo)
+        # the lookup counter: none without a table; with one, every lookup stood for k of the algorithm's extensions
+        assert G["seed_lookups"] * k <= G["extensions"]
+        if k == 0 or ml < k: assert G["seed_lookups"] == 0 or ml < k
+        if 0 < k <= ml and mo == 1: assert G["seed_lookups"] > 0
     rs = datasets.ragged_reads(c["text"], seed=8); r2, o2 = orc.pack_reads(rs)
     compare(g.find_mems(r2, o2, 3, 1), o.find_mems(r2, o2, 3, 1), True)
     compare(g.find_mems(r2, o2, 13, 1), o.find_mems(r2, o2, 13, 1), True)
