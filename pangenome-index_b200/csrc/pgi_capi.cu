@@ -389,6 +389,7 @@ struct pgi_batch {
     cudaEvent_t ev[EV_COUNT]; bool ev_ok = false;
     // inputs
     DevBuf d_reads, d_read_off; const uint64_t *reads64 = nullptr; const uint64_t *read_off = nullptr; uint64_t n_reads = 0, reads_bytes = 0;
+    DevBuf d_slot_ctr;                                       // partitioned MEM-slot counters (MemArgs::slot_ctr)
     DevBuf d_codes, d_read_flags;                            // 2-bit codes of the reads + per-read "other bytes" flags (seed lookups)
     // MEM stage
     DevBuf d_ctr, d_mem_buf, d_mem_key, d_nmems, d_mem_off, d_mems, d_cub;
@@ -400,7 +401,7 @@ struct pgi_batch {
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
     void release_all() {
-        DevBuf *db[] = {&d_codes, &d_read_flags, &d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
+        DevBuf *db[] = {&d_slot_ctr, &d_codes, &d_read_flags, &d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
                         &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e};
         for (DevBuf *b : db) b->release();
         PinBuf *pb[] = {&h_ctr, &h_mem_off, &h_mems, &h_tag_off, &h_tags, &h_n_runs};
@@ -490,6 +491,18 @@ __global__ void peek_kernel(const uint64_t *src, volatile uint64_t *host_dst, un
     if (threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
     __threadfence_system();
 }
+// Partitioned MEM slots: [5] = sum of the partition counters (MEMs appended), [6] = their maximum (overflow check).
+__global__ void peek_parts_kernel(const unsigned long long *slot_ctr, volatile uint64_t *host_dst) {
+    __shared__ unsigned long long s_sum[PGI_SLOT_PARTS], s_max[PGI_SLOT_PARTS];
+    const unsigned t = threadIdx.x;
+    s_sum[t] = s_max[t] = slot_ctr[16u * t];
+    __syncthreads();
+    for (unsigned o = PGI_SLOT_PARTS / 2; o; o >>= 1) {
+        if (t < o) { s_sum[t] += s_sum[t + o]; if (s_max[t + o] > s_max[t]) s_max[t] = s_max[t + o]; }
+        __syncthreads();
+    }
+    if (t == 0) { host_dst[5] = s_sum[0]; host_dst[6] = s_max[0]; __threadfence_system(); }
+}
 void peek(pgi_batch *b, const void *dptr, unsigned n) {
     peek_kernel<<<1, 32, 0, b->stream>>>((const uint64_t *) dptr, b->h_ctr.as<uint64_t>(), n);
     CK(cudaGetLastError());
@@ -556,24 +569,46 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
             ++launches; CK(cudaGetLastError());
         }
     }
+    // PGI_SLOT_PARTS=0 falls back to the single global slot counter (tuning / comparison runs)
+    // ... and so do small batches: with fewer reads than a few rounds of all warps the partitions fill unevenly (the read
+    // queue is dynamic), and their atomics are too few to matter anyway.
+    // PGI_SLOT_PARTS=<reads>: smallest batch that uses the partitions (default 600000; 0 = never; 1 = always: tests).
+    uint64_t parts_min = 0;                              // OFF by default until a GPU run of the whole suite has been seen green with it (set to 600000 then)
+    if (const char *e = std::getenv("PGI_SLOT_PARTS")) parts_min = std::strtoull(e, nullptr, 10);
+    const bool parts_on = parts_min != 0 && n >= parts_min;
+    uint64_t part_cap = 0, slots = 0;
+    b->d_slot_ctr.need(PGI_SLOT_PARTS * 128);
     for (;;) {
-        b->d_mem_buf.need(cap * 32); b->d_mem_key.need(cap * 8);
+        part_cap = parts_on ? (cap + PGI_SLOT_PARTS - 1) / PGI_SLOT_PARTS + 64 : 0;
+        slots = parts_on ? part_cap * PGI_SLOT_PARTS : cap;
+        b->d_mem_buf.need(slots * 32); b->d_mem_key.need(slots * 8);
         CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
+        CK(cudaMemsetAsync(b->d_slot_ctr.p, 0, PGI_SLOT_PARTS * 128, b->stream));
         CK(cudaMemsetAsync(b->d_nmems.p, 0, (n + 1) * 8, b->stream));
         MemArgs a;
         a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
         a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
         a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
         a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = cap;
+        a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
         a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
         CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
         if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
         CK(cudaGetLastError());
         CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
+        if (parts_on) { peek_parts_kernel<<<1, PGI_SLOT_PARTS, 0, b->stream>>>(a.slot_ctr, b->h_ctr.as<uint64_t>()); CK(cudaGetLastError()); }
         peek(b, ctr, 5);
-        total = b->h_ctr.as<volatile uint64_t>()[1]; b->extensions = b->h_ctr.as<volatile uint64_t>()[2]; b->seed_lookups = b->h_ctr.as<volatile uint64_t>()[4];
-        if (total <= cap) break;
-        cap = total + 1024; ++reruns;                    // append buffer overflowed: the count is exact, run again
+        volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
+        b->extensions = h[2]; b->seed_lookups = h[4];
+        if (parts_on) {
+            total = h[5];
+            if (h[6] <= part_cap) break;
+            cap = (h[6] + h[6] / 8 + 64) * PGI_SLOT_PARTS; ++reruns;   // the fullest partition overflowed: its count is exact, run again
+        } else {
+            total = h[1];
+            if (total <= cap) break;
+            cap = total + 1024; ++reruns;                // append buffer overflowed: the count is exact, run again
+        }
     }
     if (n) b->mems_per_read = std::max(1.0, (double) total / (double) n);
     b->n_mems = total;
@@ -581,8 +616,10 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     exclusive_scan(b, b->d_nmems.as<uint64_t>(), b->d_mem_off.as<uint64_t>(), n + 1, launches);
     b->d_mems.need(std::max<uint64_t>(1, total) * 32);
     if (total) {
-        mem_scatter_kernel<<<grid_for(total, 256), 256, 0, b->stream>>>(b->d_mem_buf.as<uint4>(), b->d_mem_key.as<uint64_t>(),
-                                                                          b->d_mem_off.as<uint64_t>(), total, b->d_mems.as<uint4>());
+        const uint64_t walk = parts_on ? slots : total;
+        mem_scatter_kernel<<<grid_for(walk, 256), 256, 0, b->stream>>>(b->d_mem_buf.as<uint4>(), b->d_mem_key.as<uint64_t>(),
+                                                                         b->d_mem_off.as<uint64_t>(), walk, b->d_mems.as<uint4>(),
+                                                                         b->d_slot_ctr.as<unsigned long long>(), part_cap);
         ++launches; CK(cudaGetLastError());
     }
     CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
@@ -607,7 +644,7 @@ void run_count_stage(pgi_batch *b, int &launches) {
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
-    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = n;
+    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }

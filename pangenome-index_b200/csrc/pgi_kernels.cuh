@@ -35,7 +35,15 @@ struct MemArgs {
     const uint32_t *read_flags;    // bit r: read r holds a byte other than A / C / G / T (no seed lookups for it)
     const uint4 *seed;             // seed table (pgi_core.cuh): 4^seed_k entries of 16 bytes, or nullptr
     uint32_t seed_k, pad;          // 0: no table (OP 1, indexes with a quirk slot, PGI_SEEDK=0)
+    // MEM slots. One global counter costs a same-address atomicAdd per MEM (3.8 M per 2 M reads: one every 2.3 ns), and how
+    // fast the L2 retires those differs between GPUs and moments: 8.8 or 10.9 ms for the same launch.
+    // With part_cap != 0 the append buffer is cut into PGI_SLOT_PARTS partitions of part_cap slots, each with its own
+    // counter on its own 128-byte line; a warp appends to partition (global warp id mod PGI_SLOT_PARTS). The scatter pass
+    // walks the filled prefix of every partition, so the holes behind them never matter.
+    unsigned long long *slot_ctr;  // PGI_SLOT_PARTS counters, 16 u64 apart (keep counting past part_cap)
+    uint64_t part_cap;             // 0: the single counter mem_count
 };
+#define PGI_SLOT_PARTS 256u
 
 __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
@@ -165,8 +173,13 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         } else if (have) {
             int st;
             while ((st = lane_settle(L, min_len, a.ix.n)) == LANE_EMIT) {
-                const unsigned long long slot = atomicAdd(a.mem_count, 1ull);
-                if (slot < a.mem_cap) {
+                unsigned long long slot; bool fits;
+                if (a.part_cap) {
+                    const unsigned part = (blockIdx.x * (THREADS / 32u) + (threadIdx.x >> 5)) & (PGI_SLOT_PARTS - 1u);
+                    const unsigned long long k = atomicAdd(a.slot_ctr + 16u * part, 1ull);
+                    fits = k < a.part_cap; slot = (unsigned long long) part * a.part_cap + k;
+                } else { slot = atomicAdd(a.mem_count, 1ull); fits = slot < a.mem_cap; }
+                if (fits) {
                     __stcs(a.mem_buf + 2 * slot, make_uint4(L.x, 0u, L.j, 0u));
                     __stcs(a.mem_buf + 2 * slot + 1, make_uint4((uint32_t) L.b.k, (uint32_t) (L.b.k >> 32), (uint32_t) (uint64_t) L.b.s, (uint32_t) ((uint64_t) L.b.s >> 32)));
                     __stcs(a.mem_key + slot, ((uint64_t) rd << 32) | nm);
@@ -365,9 +378,10 @@ __global__ void pack_reads_kernel(const uint64_t *reads64, uint64_t n_words, uin
 
 // K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read.
 __global__ void mem_scatter_kernel(const uint4 *mem_buf, const uint64_t *mem_key, const uint64_t *mem_off,
-                                   uint64_t n_mems, uint4 *mems) {
+                                   uint64_t n_mems, uint4 *mems, const unsigned long long *slot_ctr, uint64_t part_cap) {
     const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (i >= n_mems) return;
+    if (i >= n_mems) return;                                            // partitioned: n_mems = PGI_SLOT_PARTS * part_cap slots
+    if (part_cap && i % part_cap >= slot_ctr[16u * (i / part_cap)]) return;   // behind the filled prefix of its partition
     const uint64_t key = mem_key[i];
     const uint64_t dst = mem_off[key >> 32] + (key & 0xFFFFFFFFull);
     mems[2 * dst] = mem_buf[2 * i]; mems[2 * dst + 1] = mem_buf[2 * i + 1];

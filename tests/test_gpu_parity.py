@@ -296,6 +296,32 @@ def test_seed_table_is_invisible(capi, K, monkeypatch):
         reads, off = datasets.sample_reads(x["text"], 2000, 150, 0.02, seed=78)
         compare(gx.find_mems(reads, off, 20, 1), orc.Index(x["ri"], x["tags"], x["layout"]).find_mems(reads, off, 20, 1), True)
 
+def test_partitioned_mem_slots(capi, monkeypatch):
+    """MEM slots handed out from 256 partition counters instead of one global counter: forced on for
+    every batch size (PGI_SLOT_PARTS=1; by default only batches of 600000 reads and more use them), including batches that
+    overflow a partition and are re-run, long reads with many MEMs each, ragged and empty reads; same results as the
+    oracle and as the single-counter path."""
+    c = get_case("synth_enc_compact")
+    g = capi.Index(c["ri"], c["tags"], c["layout"]); o = orc.Index(c["ri"], c["tags"], c["layout"])
+    reads, off = datasets.sample_reads(c["text"], 20000, 150, 0.02, seed=91)
+    rs = datasets.ragged_reads(c["text"], seed=12); r2, o2 = orc.pack_reads(rs)
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    gl = capi.Index(s["ri"], s["tags0"], 0); ol = orc.Index(s["ri"], s["tags0"], 0)
+    lr, lo = datasets.sample_reads(s["text"], 200, 10000, 0.04, seed=35, indel=0.01)
+    monkeypatch.setenv("PGI_SLOT_PARTS", "0")
+    single = g.find_mems(reads, off, 20, 1)
+    monkeypatch.setenv("PGI_SLOT_PARTS", "1")
+    for ml, mo in [(20, 1), (5, 2)]:
+        G = g.find_mems(reads, off, ml, mo); R = o.find_mems(reads, off, ml, mo, count_work=True)
+        compare(G, R, True); assert G["extensions"] == R["counters"]["E"]
+    parts = g.find_mems(reads, off, 20, 1)
+    for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(parts[k], single[k]), k
+    compare(g.find_mems(r2, o2, 3, 1), o.find_mems(r2, o2, 3, 1), True)
+    e_reads, e_off = orc.pack_reads([b"", b"ACGT", b""])
+    compare(g.find_mems(e_reads, e_off, 2, 1), o.find_mems(e_reads, e_off, 2, 1), True)
+    G = gl.find_mems(lr, lo, 20, 1); R = ol.find_mems(lr, lo, 20, 1, count_work=True)          # few reads, thousands of MEMs: partitions overflow, re-run
+    compare(G, R, True); assert G["extensions"] == R["counters"]["E"]
+
 def test_long_reads_with_indel_errors(capi):
     """BASELINE configs[4] as a parity case: 10 kbp reads with 5 % errors (substitutions + 1 bp indels): long backward /
     forward chains per lane, lanes of one warp finishing at very different times, many MEMs per read."""
