@@ -573,7 +573,7 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
     // ... and so do small batches: with fewer reads than a few rounds of all warps the partitions fill unevenly (the read
     // queue is dynamic), and their atomics are too few to matter anyway.
     // PGI_SLOT_PARTS=<reads>: smallest batch that uses the partitions (default 600000; 0 = never; 1 = always: tests).
-    uint64_t parts_min = 0;                              // OFF by default until a GPU run of the whole suite has been seen green with it (set to 600000 then)
+    uint64_t parts_min = 600000;
     if (const char *e = std::getenv("PGI_SLOT_PARTS")) parts_min = std::strtoull(e, nullptr, 10);
     const bool parts_on = parts_min != 0 && n >= parts_min;
     uint64_t part_cap = 0, slots = 0;
