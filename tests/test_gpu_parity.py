@@ -20,6 +20,8 @@ def cases():
         out["synth_%s_compact" % ("enc" if enc else "leg")] = dict(ri=s["ri"], tags=s["tags0"], layout=0, text=s["text"])
     s = datasets.synth_index(encoded=True)
     out["synth_enc_bytecode"] = dict(ri=s["ri"], tags=s["tags1"], layout=1, text=s["text"])
+    import refcases
+    out["x_encoded_sigma5"] = refcases.x_index()              # BASELINE config 1: encoded, forward-only, sigma = 5
     return out
 
 CASES = None
@@ -27,7 +29,7 @@ def get_case(name):
     global CASES
     if CASES is None: CASES = cases()
     return CASES[name]
-NAMES = ["xy_legacy_bytecode", "two_contig_legacy", "synth_enc_compact", "synth_leg_compact", "synth_enc_bytecode"]
+NAMES = ["xy_legacy_bytecode", "two_contig_legacy", "synth_enc_compact", "synth_leg_compact", "synth_enc_bytecode", "x_encoded_sigma5"]
 
 def compare(g, o, with_tags):
     assert g["n_mems"] == o["n_mems"]
@@ -38,6 +40,43 @@ def compare(g, o, with_tags):
         assert np.array_equal(g["tag_off"], o["tag_off"])
         assert np.array_equal(g["tags"], o["tags"])
     assert g["text"] == o["text"]
+
+# ---- against the REFERENCE'S OWN CODE: its stdout on the cases of tests/refcases.py, committed as tests/golden/ref_find_mems.json
+# by tests/golden/make_ref_golden.py (oracle/_ref/libpgiref.so = src/r-index.cpp + src/tag_arrays.cpp + find_all_mems + main loop)
+import hashlib, json, os, refcases
+REF_GOLD = json.load(open(os.path.join(datasets.GOLD, "ref_find_mems.json")))
+_REF_IX = None
+def ref_index(name):
+    global _REF_IX
+    if _REF_IX is None: _REF_IX = refcases.indexes()
+    return _REF_IX[name]
+
+@pytest.mark.parametrize("case", refcases.CASES, ids=refcases.case_key)
+def test_gpu_stdout_equals_reference_golden(capi, case):
+    ix = ref_index(case[0]); gold = REF_GOLD["find_mems"][refcases.case_key(case)]
+    rs = refcases.reads_of(ix, case[1]); assert len(rs) == gold["n_reads"]
+    reads, off = orc.pack_reads(rs)
+    g = capi.Index(ix["ri"], ix["tags"], ix["layout"])
+    text = g.find_mems(reads, off, case[2], case[3])["text"]
+    assert len(text) == gold["stdout_bytes"] and hashlib.sha256(text).hexdigest() == gold["stdout_sha256"]
+    if orc.ref_available():                                   # the prebuilt reference library travels to the GPU box: compare live as well
+        R = orc.Index(ix["ri"], ix["tags"], ix["layout"], impl="ref")
+        assert text == R.ref_text(b"\n".join(rs) + b"\n", case[2], case[3])
+
+@pytest.mark.parametrize("name", sorted(REF_GOLD["extend_rank"]))
+def test_gpu_extend_rank_equal_reference_golden(capi, name):
+    from test_ref_pin import _vectors
+    ix = ref_index(name); g = capi.Index(ix["ri"]); gold = REF_GOLD["extend_rank"][name]
+    iv, sym, d, pos = _vectors(g.info["n"])
+    assert hashlib.sha256(g.extend_batch(iv, sym, d).tobytes()).hexdigest() == gold["extend_sha256"]
+    assert hashlib.sha256(g.rank_batch(pos).tobytes()).hexdigest() == gold["rank_sha256"]
+
+@pytest.mark.parametrize("name", sorted(REF_GOLD["query_tags"]))
+def test_gpu_query_tags_stdout_equals_reference_golden(capi, name):
+    ix = ref_index(name); g = capi.Index(ix["ri"], ix["tags"], 0); gold = REF_GOLD["query_tags"][name]
+    reads, off = orc.pack_reads(refcases.reads_of(ix, ("sample", 400, 40, 0.01, 12)))
+    text = g.query_tags(reads, off)["text"]
+    assert len(text) == gold["stdout_bytes"] and hashlib.sha256(text).hexdigest() == gold["stdout_sha256"]
 
 @pytest.mark.parametrize("name", NAMES)
 def test_extend_and_rank(capi, name):
