@@ -236,7 +236,7 @@ def compare_query_tags(G, R, with_tags):
         assert np.array_equal(G["n_runs"], R["n_runs"]) and np.array_equal(G["tag_off"], R["tag_off"]) and np.array_equal(G["tags"], R["tags"])
         assert G["text"] == R["text"]
 
-@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("name", [n for n in NAMES if n != "x_encoded_sigma5"])   # encoded without N: refused (test_query_tags_large_and_refusal)
 def test_query_tags(capi, name):
     """count_encoded / count + tag query of the final range (src/query_tags.cpp:87-109), bit-exact."""
     c = get_case(name)
