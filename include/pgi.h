@@ -92,6 +92,24 @@ int pgi_device_count(void);   /* number of CUDA devices (0 when none / no driver
  * TagArray facade: only pgi_tag_query_batch works on it). The input buffers are not retained. */
 int pgi_index_create(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len,
                      int tag_layout, int device, pgi_index **out);
+/* GPU-side construction. Replaces, for an index that already exists as run-length arrays, the chain
+ * FastLocate(rlbwt) constructor (block part, src/r-index.cpp:778-958) -> serialize_encoded (:297-376) -> load_encoded
+ * (:406-459) and TagArray's compressed writers (src/tag_arrays.cpp:622-654, 940-974) -> load_compressed_tags_compact
+ * (:766-776): the device index is built ON THE GPU from
+ *   sym[i], len[i]          i < n_runs      the run-length BWT (symbol byte in {'\n','A','C','G','N','T'}, length > 0; what a
+ *                                           .rl_bwt file holds, deps/grlBWT/include/bwt_io.h:40-58), in BWT order
+ *   tag_val[j], tag_len[j]  j < n_tag_runs  the run-length tag array (encoded graph position node<<11|rev<<10|off, length > 0;
+ *                                           runs longer than 511 are split as tag_arrays.cpp:942-957 does), or n_tag_runs = 0
+ * device_pointers != 0: the four arrays are DEVICE pointers on GPU `device` (they are not modified and not retained).
+ * The result equals pgi_index_create on the files the reference's writers emit for these runs (encoded .ri without
+ * suffix-array samples -- so no pgi_locate_batch -- and sdsl-compact tags), answer for answer. No host copy of the index
+ * is made. Limits of the device layout (both constructions): n < 2^40, fewer than 2^32 end markers and 'N's, fewer than
+ * 2^32 - 1 run blocks of 2^bucket_shift BWT positions each (64 bytes per block: the index takes n / 2^bucket_shift * 64
+ * bytes of HBM, bucket_shift <= 8, i.e. at least n / 4 bytes -- an index whose BWT is longer than about 4x the free HBM
+ * does not fit one GPU; out-of-core operation is not built). */
+int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *len, uint64_t n_runs,
+                               const uint64_t *tag_val, const uint64_t *tag_len, uint64_t n_tag_runs,
+                               int device_pointers, int device, pgi_index **out);
 /* Replica of an index on another GPU (device-to-device copy over NVLink; no host round trip). */
 int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **out);
 void pgi_index_free(pgi_index *);

@@ -8,3 +8,10 @@ The directory name contains a hyphen, so import it through `__graft_entry__.load
 tests/conftest.py), which registers it as the module `pangenome_index_b200`.
 """
 from . import capi, prep, sharding  # noqa: F401
+
+def __getattr__(name):
+    # synth / pangraph import torch (data prep for the synthetic workloads); loaded on first use only
+    if name in ("synth", "pangraph"):
+        import importlib
+        return importlib.import_module("." + name, __name__)
+    raise AttributeError(name)

@@ -11,7 +11,7 @@ SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
            "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
-           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image"]
+           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -50,6 +50,7 @@ def lib():
         vp, u64, i32 = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int
         L.pgi_index_create.argtypes = [vp, ctypes.c_size_t, vp, ctypes.c_size_t, i32, i32, ctypes.POINTER(vp)]
         L.pgi_index_clone_to.argtypes = [vp, i32, ctypes.POINTER(vp)]
+        L.pgi_index_create_from_runs.argtypes = [vp, vp, u64, vp, vp, u64, i32, i32, ctypes.POINTER(vp)]
         L.pgi_index_free.argtypes = [vp]
         L.pgi_index_info.argtypes = [vp, ctypes.POINTER(IndexInfo)]
         L.pgi_extend_batch.argtypes = [vp, u64, vp, vp, vp, vp]
@@ -123,6 +124,25 @@ class Index:
         _ck(lib().pgi_index_open_image(os.fsencode(path), device, chunk_bytes, int(verify), ctypes.byref(h), ctypes.byref(f)))
         ix = cls(None, device=device, _handle=h); ix.image = {k: getattr(f, k) for k, _ in ImageInfo._fields_}
         return ix
+    @classmethod
+    def from_runs(cls, sym, length, tag_val=None, tag_len=None, device=0):
+        """GPU-side construction from the run-length BWT (+ run-length tags). numpy arrays (host) or objects with
+        .data_ptr() (torch CUDA tensors: uint8 / int64 / int64 / int64 on `device`)."""
+        h = ctypes.c_void_p(); dev_ptrs = hasattr(sym, "data_ptr")
+        if dev_ptrs:
+            import torch
+            assert sym.dtype == torch.uint8 and length.dtype == torch.int64 and sym.is_contiguous() and length.is_contiguous()
+            a, b, n = sym.data_ptr(), length.data_ptr(), sym.numel()
+            c = tag_val.data_ptr() if tag_val is not None else None; d = tag_len.data_ptr() if tag_val is not None else None
+            nt = tag_val.numel() if tag_val is not None else 0
+        else:
+            sym = np.ascontiguousarray(sym, dtype=np.uint8); length = np.ascontiguousarray(length, dtype=np.uint64)
+            a, b, n = sym.ctypes.data, length.ctypes.data, len(sym); c = d = None; nt = 0
+            if tag_val is not None:
+                tag_val = np.ascontiguousarray(tag_val, dtype=np.uint64); tag_len = np.ascontiguousarray(tag_len, dtype=np.uint64)
+                c, d, nt = tag_val.ctypes.data, tag_len.ctypes.data, len(tag_val)
+        _ck(lib().pgi_index_create_from_runs(a, b, n, c, d, nt, int(dev_ptrs), device, ctypes.byref(h)))
+        return cls(None, device=device, _handle=h)
     def __init__(self, ri: bytes, tags: bytes = None, tag_layout=0, device=0, _handle=None):
         L = lib(); self.device = device
         if _handle is not None:

@@ -14,6 +14,7 @@
 #include "pgi_flatten.hpp"
 #include "pgi_image.hpp"
 #include "pgi_tag_kernels.cuh"
+#include "pgi_build.cuh"
 
 using namespace pgi;
 
@@ -272,6 +273,200 @@ extern "C" int pgi_index_create(const void *ri_bytes, size_t ri_len, const void 
         *out = upload_view(v, device, 0, nullptr);
         return PGI_OK;
     } PGI_CATCH_ALL
+}
+
+// ------------------------------------------------------------------------------------------ GPU-side construction
+namespace {
+template <typename T> T *dev_alloc(uint64_t n, std::vector<void *> &owned, uint64_t &bytes, bool zero = false) {
+    void *d = nullptr; const size_t b = (size_t) std::max<uint64_t>(1, n) * sizeof(T);
+    CK(cudaMalloc(&d, b)); owned.push_back(d); bytes += b;
+    if (zero) CK(cudaMemset(d, 0, b));
+    return (T *) d;
+}
+struct Tmp {                        // scratch device buffers of one construction, freed on scope exit
+    std::vector<void *> v;
+    template <typename T> T *get(uint64_t n) { void *d = nullptr; CK(cudaMalloc(&d, (size_t) std::max<uint64_t>(1, n) * sizeof(T))); v.push_back(d); return (T *) d; }
+    void drop(const void *p) { for (auto &x : v) if (x == p) { cudaFree(x); x = nullptr; } }
+    ~Tmp() { for (void *x : v) if (x) cudaFree(x); }
+};
+inline unsigned grid_of(uint64_t n, unsigned threads) { return (unsigned) std::max<uint64_t>(1, (n + threads - 1) / threads); }
+
+// The descriptor banks + seed table + info of an index whose device arrays are in place (shared by both constructions).
+void finish_index(pgi_index *ix, const ImageMeta &m, uint64_t &bytes) {
+    std::vector<uint32_t> desc(PGI_DESC_WORDS);
+    auto bank = [&](const uint32_t *b, const uint32_t *f) {
+        for (int i = 0; i < 256; ++i) { desc[i] = b[i]; desc[256 + i] = f[i]; }
+        for (int i = 0; i < 512; ++i) { const ScanTab t = scan_tab(desc[i] & 0xFFFFFFu); desc[512 + 4 * i] = t.x; desc[512 + 4 * i + 1] = t.y; desc[512 + 4 * i + 2] = t.z; desc[512 + 4 * i + 3] = t.w; }
+        return upload(desc, ix->owned, bytes);
+    };
+    ix->d_desc = bank(m.k.desc_b, m.k.desc_f);
+    ix->d_desc_c = bank(m.k.desc_c, m.k.desc_c);
+    build_seed_table(ix, choose_seed_k(m), bytes);
+    fill_info(ix, m, bytes);
+}
+} // namespace
+
+extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *len, uint64_t n_runs,
+                                          const uint64_t *tag_val, const uint64_t *tag_len, uint64_t n_tag_runs,
+                                          int device_pointers, int device, pgi_index **out) {
+    if (!sym || !len || !n_runs || !out || (n_tag_runs && (!tag_val || !tag_len))) return fail(PGI_EINVAL, "null argument");
+    if (int rc = check_device(device)) return rc;
+    if (n_runs >> 32) return fail(PGI_EINVAL, "more than 2^32 BWT runs");
+    pgi_index *ix = nullptr;
+    try {
+        DeviceGuard g(device);
+        namespace B = pgi::build;
+        auto pol = thrust::device;
+        Tmp tmp;
+        ix = new pgi_index(); ix->device = device;
+        cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
+        uint64_t bytes = 0;
+        ImageMeta m; std::memset(&m, 0, sizeof(m));
+        // ---- inputs on the device
+        const uint8_t *d_sym = sym; const uint64_t *d_len = len, *d_tv = tag_val, *d_tl = tag_len;
+        if (!device_pointers) {
+            uint8_t *a = tmp.get<uint8_t>(n_runs); uint64_t *b = tmp.get<uint64_t>(n_runs);
+            CK(cudaMemcpy(a, sym, n_runs, cudaMemcpyHostToDevice)); CK(cudaMemcpy(b, len, n_runs * 8, cudaMemcpyHostToDevice)); d_sym = a; d_len = b;
+            if (n_tag_runs) {
+                uint64_t *c = tmp.get<uint64_t>(n_tag_runs), *d = tmp.get<uint64_t>(n_tag_runs);
+                CK(cudaMemcpy(c, tag_val, n_tag_runs * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(d, tag_len, n_tag_runs * 8, cudaMemcpyHostToDevice)); d_tv = c; d_tl = d;
+            }
+        }
+        thrust::counting_iterator<uint64_t> idx(0);
+        // ---- symbol codes, validation, totals, logical runs (an end marker record of length f is f runs, r-index.cpp:840-848)
+        uint8_t *code0 = tmp.get<uint8_t>(n_runs);
+        thrust::transform(pol, d_sym, d_sym + n_runs, code0, B::CodeOf());
+        if (thrust::transform_reduce(pol, idx, idx + n_runs, B::BadRun{code0, d_len}, 0ull, thrust::plus<uint64_t>()))
+            throw FormatError("BWT run with a symbol outside {\\n,A,C,G,N,T} or of length 0");
+        uint64_t totals[6];
+        for (uint8_t c = 0; c < 6; ++c) totals[c] = thrust::transform_reduce(pol, idx, idx + n_runs, B::LenIfCode{c, code0, d_len}, 0ull, thrust::plus<uint64_t>());
+        const uint64_t logical_runs = thrust::transform_reduce(pol, idx, idx + n_runs, B::LogicalRuns{code0, d_len}, 0ull, thrust::plus<uint64_t>());
+        uint64_t n = 0; for (uint64_t t : totals) n += t;
+        if (totals[1] >> 40 || totals[2] >> 40 || totals[3] >> 40 || totals[5] >> 40) throw FormatError("index longer than 2^40 positions is not supported by the device layout");
+        if (totals[0] >> 32 || totals[4] >> 32) throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
+        // ---- maximal runs and their start positions
+        uint8_t *code = tmp.get<uint8_t>(n_runs); uint64_t *rlen = tmp.get<uint64_t>(n_runs);
+        const uint64_t r = (uint64_t) (thrust::reduce_by_key(pol, code0, code0 + n_runs, d_len, code, rlen).first - code);
+        tmp.drop(code0);
+        uint64_t *starts = tmp.get<uint64_t>(r + 1);
+        thrust::exclusive_scan(pol, rlen, rlen + r, starts);
+        CK(cudaMemcpy(starts + r, &n, 8, cudaMemcpyHostToDevice));
+        // ---- bucket shift: the largest s <= 8 with at most 1/64 of the buckets crowded (pgi_flatten.hpp build_buckets)
+        unsigned S = PGI_MAX_BSHIFT; bool forced = false;
+        if (const char *e = std::getenv("PGI_BSHIFT")) {
+            S = (unsigned) std::atoi(e); forced = true;
+            if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 8]");
+        }
+        unsigned long long *d_ctr = tmp.get<unsigned long long>(1);
+        uint32_t *frun = nullptr; uint64_t nb = 0; unsigned long long n_crowded = 0;
+        for (;; --S) {
+            nb = (n >> S) + 1;
+            if (frun) tmp.drop(frun);
+            frun = tmp.get<uint32_t>(nb + 1);
+            // frun[b] = (number of run starts <= b << S) - 1: the run holding the first position of bucket b
+            auto q = thrust::make_transform_iterator(idx, B::ShiftLeft{S});
+            thrust::upper_bound(pol, starts, starts + r, q, q + nb, frun);
+            thrust::transform(pol, frun, frun + nb, frun, B::MinusOne());
+            CK(cudaMemset(d_ctr, 0, 8));
+            B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, nb, S, r, n, nullptr, d_ctr);
+            CK(cudaGetLastError());
+            CK(cudaMemcpy(&n_crowded, d_ctr, 8, cudaMemcpyDeviceToHost));
+            if (forced || S == PGI_MIN_BSHIFT || n_crowded <= ((n >> S) + 1) / 64) break;
+        }
+        uint32_t *n_chunks = tmp.get<uint32_t>(nb + 1); uint64_t *chunk_base = tmp.get<uint64_t>(nb + 1);
+        CK(cudaMemset(n_chunks, 0, (nb + 1) * 4)); CK(cudaMemset(d_ctr, 0, 8));
+        B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, nb, S, r, n, n_chunks, d_ctr);
+        CK(cudaGetLastError());
+        thrust::exclusive_scan(pol, thrust::make_transform_iterator(n_chunks, B::Widen()), thrust::make_transform_iterator(n_chunks, B::Widen()) + nb + 1, chunk_base);
+        uint64_t total_chunks = 0; CK(cudaMemcpy(&total_chunks, chunk_base + nb, 8, cudaMemcpyDeviceToHost));
+        const uint64_t n_blocks = nb + total_chunks;
+        if (n_blocks >= 0xFFFFFFFFull) throw FormatError("too many run blocks (>= 2^32 - 1) for the 32-bit block indices of the MEM kernel");
+        uint32_t *blocks = dev_alloc<uint32_t>(n_blocks * PGI_BLOCK_U32, ix->owned, bytes);
+        B::bucket_kernel<<<grid_of(nb, 128), 128>>>(frun, starts, rlen, code, nb, S, r, n, n_chunks, chunk_base, blocks);
+        CK(cudaGetLastError());
+        {   // cumulative headers: field by field, the in-bucket totals sit in the primary blocks themselves
+            uint64_t *before = tmp.get<uint64_t>(nb);
+            for (unsigned field = 1; field <= 6; ++field) {
+                auto in = thrust::make_transform_iterator(idx, B::FieldOfBlock{blocks, field});
+                thrust::exclusive_scan(pol, in, in + nb, before);
+                B::header_kernel<<<grid_of(nb, 256), 256>>>(blocks, before, nb, field, n_chunks, chunk_base);
+                CK(cudaGetLastError());
+            }
+            CK(cudaDeviceSynchronize());
+            tmp.drop(before);
+        }
+        tmp.drop(frun); tmp.drop(n_chunks); tmp.drop(chunk_base); tmp.drop(starts); tmp.drop(code); tmp.drop(rlen);
+        // ---- scalars and tables, as FastLocate::calculate_C (r-index.hpp:440-482) + serialize_encoded / load_encoded leave them
+        RiImage im; RiConsts &k = im.k; std::memset(&k, 0, sizeof(k));
+        bool present[6]; unsigned sigma = 0;
+        for (unsigned c = 0; c < 6; ++c) { present[c] = totals[c] != 0; if (present[c]) { k.sym_map[kNuc[c]] = (uint8_t) sigma; k.C[sigma] = 0; ++sigma; } }
+        { uint64_t acc = 0; unsigned j = 0; for (unsigned c = 0; c < 6; ++c) if (present[c]) { k.C[j++] = acc; acc += totals[c]; } }
+        if (!present[0]) throw FormatError("a BWT without end markers is not a multi-string BWT");
+        if (sigma != (present[4] ? 6u : 5u)) throw FormatError("encoded r-index whose alphabet size disagrees with its N flag (unreadable by the reference too)");
+        k.n = n; k.sigma = sigma; k.n_blocks = n_blocks; k.bshift = S; k.n_buckets = nb; k.n_dir_blocks = n_crowded; k.n_quirk = 0; k.mem_tail = 0; k.max_length = 1;
+        build_descriptors(im, present, false);
+        k.locate_ok = 0;
+        m.k = k; m.n_file_runs = logical_runs; m.n_ref_blocks = logical_runs / 10 + (logical_runs % 10 != 0); m.encoded = 1; m.has_ri = 1;
+        ix->consts = k; ix->has_ri = true; ix->n_block_words = n_blocks * PGI_BLOCK_WORDS;
+        RiDev &d = ix->ri; std::memset(&d, 0, sizeof(d));
+        d.blocks = (const uint64_t *) blocks; d.q_start = dev_alloc<uint64_t>(1, ix->owned, bytes, true); d.q_val = dev_alloc<uint64_t>(1, ix->owned, bytes, true);
+        d.n = n; d.n_blocks = n_blocks; d.n_quirk = 0; d.bshift = S; d.has_quirk = 0;
+        for (int i = 0; i < 8; ++i) d.C[i] = k.C[i];
+        std::memset(&ix->loc, 0, sizeof(ix->loc)); std::memset(&ix->tg, 0, sizeof(ix->tg));
+        // ---- tag arrays (sdsl-compact semantics: prep_tags_from_runs / merge_tags' writer + load_compressed_tags_compact)
+        if (n_tag_runs) {
+            if (thrust::transform_reduce(pol, idx, idx + n_tag_runs, B::ZeroLen{d_tl}, 0ull, thrust::plus<uint64_t>())) throw FormatError("tag run of length 0");
+            uint64_t *run_start = tmp.get<uint64_t>(n_tag_runs + 1), *item_off = tmp.get<uint64_t>(n_tag_runs + 1);
+            thrust::exclusive_scan(pol, d_tl, d_tl + n_tag_runs, run_start);
+            auto pc = thrust::make_transform_iterator(idx, B::Pieces{d_tl});
+            thrust::exclusive_scan(pol, pc, pc + n_tag_runs, item_off);
+            const uint64_t total_len = thrust::reduce(pol, d_tl, d_tl + n_tag_runs, 0ull, thrust::plus<uint64_t>());
+            const uint64_t n_items = thrust::reduce(pol, pc, pc + n_tag_runs, 0ull, thrust::plus<uint64_t>());
+            auto nd = thrust::make_transform_iterator(idx, B::NodeOf{d_tv});
+            const uint64_t max_node = thrust::reduce(pol, nd, nd + n_tag_runs, 0ull, thrust::maximum<uint64_t>());
+            unsigned hi = 0; while (hi < 63 && (max_node >> (hi + 1))) ++hi;
+            const unsigned width = 11 + hi + 1;
+            if (width > 64) throw FormatError("tag item width outside [1,64]");
+            uint64_t *item_val = tmp.get<uint64_t>(n_items), *item_pos = tmp.get<uint64_t>(n_items);
+            B::tag_items_kernel<<<grid_of(n_tag_runs, 256), 256>>>(d_tv, d_tl, run_start, item_off, n_tag_runs, item_val, item_pos);
+            CK(cudaGetLastError());
+            tmp.drop(run_start); tmp.drop(item_off);
+            const uint64_t nw = (n_items * width + 63) / 64;
+            uint64_t *words = dev_alloc<uint64_t>(nw + 2, ix->owned, bytes, true);
+            B::pack_items_kernel<<<grid_of(nw, 256), 256>>>(item_val, n_items, width, nw, words);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+            tmp.drop(item_val);
+            // bwt_intervals: universe total_len + 1, one 1 at the first BWT position of every item (build_sparse_rank_from)
+            SparseRankConsts &sk = m.iv_k; std::memset(&sk, 0, sizeof(sk));
+            sk.size = total_len + 1; sk.m = n_items;
+            unsigned sh = 0; while (sh < 62 && (sk.size >> sh) > n_items / 4 + 1) ++sh;
+            sk.shift = sh; sk.low_bytes = sh <= 8 ? 1 : sh <= 16 ? 2 : sh <= 32 ? 4 : 8; sk.n_buckets = (sk.size >> sh) + 1;
+            uint64_t *dir = dev_alloc<uint64_t>(sk.n_buckets + 1, ix->owned, bytes);
+            auto qb = thrust::make_transform_iterator(idx, B::ShiftLeft{sh});
+            thrust::lower_bound(pol, item_pos, item_pos + n_items, qb, qb + sk.n_buckets + 1, dir);       // dir[b] = items starting before b << shift
+            uint8_t *low = dev_alloc<uint8_t>(n_items * sk.low_bytes + 16, ix->owned, bytes, true);
+            B::low_parts_kernel<<<grid_of(n_items, 256), 256>>>(item_pos, n_items, sh, sk.low_bytes, low);
+            CK(cudaGetLastError());
+            const uint64_t n_starts = (n_items + 9) / 10;
+            uint64_t *st = dev_alloc<uint64_t>(n_starts, ix->owned, bytes);
+            B::iota10_kernel<<<grid_of(n_starts, 256), 256>>>(n_starts, st);
+            CK(cudaGetLastError()); CK(cudaDeviceSynchronize());
+            tmp.drop(item_pos);
+            TagDev &t = ix->tg; ix->has_tags = true; ix->ivk = sk;
+            t.iv.dir = dir; t.iv.low = low; t.iv.size = sk.size; t.iv.m = sk.m; t.iv.shift = sk.shift; t.iv.low_bytes = sk.low_bytes;
+            t.starts = st; t.n_starts = n_starts; t.words = words; t.stream = dev_alloc<uint8_t>(1, ix->owned, bytes, true);
+            t.n_items = n_items; t.width = width; t.layout = 0; t.starts_regular = 1; t.pad = 0;
+            ix->n_iv_dir = sk.n_buckets + 1; ix->n_iv_low = n_items * sk.low_bytes + 16; ix->n_starts = n_starts; ix->n_words = nw + 2; ix->n_stream = 1;
+            m.has_tags = 1; m.tag_layout = 0; m.tag_n_items = n_items; m.tag_width = width; m.tag_starts_regular = 1;
+        }
+        ix->n_quirk = 1;
+        finish_index(ix, m, bytes);
+        CK(cudaDeviceSynchronize());
+        *out = ix; return PGI_OK;
+    } catch (const FormatError &e) { pgi_index_free(ix); return fail(PGI_EFORMAT, e.what()); }
+      catch (const CudaError &e) { pgi_index_free(ix); return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
+      catch (const std::bad_alloc &) { pgi_index_free(ix); return fail(PGI_ENOMEM, "out of memory while building the index"); }
+      catch (const std::exception &e) { pgi_index_free(ix); return fail(PGI_EINVAL, e.what()); }
 }
 
 // ------------------------------------------------------------------------------------------ cached device image

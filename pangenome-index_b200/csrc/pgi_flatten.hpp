@@ -253,7 +253,7 @@ inline void build_buckets(RiImage &im, const std::vector<uint32_t> &runs, uint64
     }
     if (pos != n || carry_len || ri != runs.size()) throw FormatError("run lengths do not add up to the BWT size");
     im.k.n_blocks = im.blocks.size() / PGI_BLOCK_WORDS; im.k.n_dir_blocks = n_dir;
-    if (im.k.n_blocks >> 30) throw FormatError("too many run blocks (>= 2^30) for the 16-byte-unit fetch indices");
+    if (im.k.n_blocks >= 0xFFFFFFFFull) throw FormatError("too many run blocks (>= 2^32 - 1) for the 32-bit block indices of the MEM kernel");
     for (unsigned c = 0; c < 6; ++c) totals[c] = cum[c];
 }
 

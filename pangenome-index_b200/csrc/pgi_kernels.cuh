@@ -259,16 +259,16 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             const unsigned part = lane & 3u;
             const char *const blk_bytes = reinterpret_cast<const char *>(a.ix.blocks);
             // slot 8 r + q, part p lands at byte 512 r + 64 q + 16 (p ^ swizzle(q)): the swizzle does not depend on r.
-            // Block indices travel in units of 16 bytes (4 b; n_blocks < 2^30 is checked at load) so that the receiving
-            // lane adds its part number and needs one multiply-add for the address.
+            // Block indices travel as 32-bit block numbers (n_blocks < 2^32 - 1 is checked at load: 256 GB of run blocks,
+            // more than the HBM holds); the receiving lane forms the address of its 16-byte part with one 64-bit multiply-add.
+            const char *const part_bytes = blk_bytes + part * 16u;
             auto coop_issue = [&](uint32_t i1, uint32_t i2) {
-                const uint32_t q1 = i1 == PGI_NOBLK ? PGI_NOBLK : i1 << 2, q2 = i2 == PGI_NOBLK ? PGI_NOBLK : i2 << 2;
 #pragma unroll
                 for (unsigned r = 0; r < 4; ++r) {
                     const unsigned src = 8u * r + (lane >> 2);
-                    const uint32_t x1 = __shfl_sync(FULL, q1, src), x2 = __shfl_sync(FULL, q2, src);
-                    cp_async16_if(st_dst + 512u * r, blk_bytes + (uint64_t) (x1 + part) * 16u, x1);
-                    cp_async16_if(st_dst + 2048u + 512u * r, blk_bytes + (uint64_t) (x2 + part) * 16u, x2);
+                    const uint32_t x1 = __shfl_sync(FULL, i1, src), x2 = __shfl_sync(FULL, i2, src);
+                    cp_async16_if(st_dst + 512u * r, part_bytes + (uint64_t) x1 * 64u, x1);
+                    cp_async16_if(st_dst + 2048u + 512u * r, part_bytes + (uint64_t) x2 * 64u, x2);
                 }
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };

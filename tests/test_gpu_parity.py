@@ -414,3 +414,53 @@ def test_locate_batch(capi, name):
         for j, i in enumerate(np.nonzero(hit)[0][:100]):
             rd = reads[i * 25:(i + 1) * 25].tobytes()
             assert list(li[lo[j]:lo[j + 1]]) == [s for s in range(len(seqs)) if rd in seqs[s]], i
+
+# ---- GPU-side construction: pgi_index_create_from_runs == pgi_index_create on the files prep writes for the same runs
+def _runs_of_rlbwt(rl):
+    sb, fb = np.frombuffer(rl[:16], dtype=np.uint64); rec = np.frombuffer(rl[16:], dtype=np.uint8).reshape(-1, int(sb + fb))
+    ln = np.zeros(len(rec), dtype=np.uint64)
+    for i in range(int(fb)): ln |= rec[:, 1 + i].astype(np.uint64) << np.uint64(8 * i)
+    return rec[:, 0].copy(), ln
+
+@pytest.mark.parametrize("shift", [None, "4", "6"])
+def test_create_from_runs_equals_create_from_files(capi, shift, monkeypatch):
+    if shift: monkeypatch.setenv("PGI_BSHIFT", shift)
+    prep = load_package().prep
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    sym, ln = _runs_of_rlbwt(s["rl_bwt"])
+    val = s["row_val"]; cut = np.nonzero(np.concatenate([[True], val[1:] != val[:-1]]))[0]
+    tv = val[cut]; tl = np.diff(np.concatenate([cut, [len(val)]])).astype(np.uint64)
+    tl_long = tl.copy(); tags_file, _ = prep.tags_from_runs(tv, tl_long, 0)
+    a = capi.Index(s["ri"], tags_file, 0); b = capi.Index.from_runs(sym, ln, tv, tl_long)
+    for k in ("n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift", "has_quirk_slot", "has_tags", "tag_layout",
+              "tag_runs", "tag_items", "tag_item_width", "tag_universe", "n_crowded_buckets", "seed_k"):
+        assert a.info[k] == b.info[k], k
+    assert a.C == b.C and a.sym_map == b.sym_map
+    if shift == "4": assert b.info["n_crowded_buckets"] > 0
+    pos = np.arange(0, a.n + 1, dtype=np.uint64)
+    assert np.array_equal(a.rank_batch(pos), b.rank_batch(pos))
+    reads, off = datasets.sample_reads(s["text"], 4000, 150, 0.01, seed=3)
+    for ml, mo in ((20, 1), (4, 1)):
+        compare(b.find_mems(reads, off, ml, mo), a.find_mems(reads, off, ml, mo), True)
+    o = orc.Index(s["ri"], tags_file, 0)
+    compare(b.find_mems(reads, off, 20, 1), o.find_mems(reads, off, 20, 1), True)
+    st = np.arange(0, a.n - 8, 7, dtype=np.uint64); en = st + np.uint64(5)
+    A = a.tag_query_batch(st, en); Bq = b.tag_query_batch(st, en)
+    for k in ("n_runs", "tag_off", "tags"): assert np.array_equal(A[k], Bq[k]), k
+
+def test_create_from_runs_long_tag_runs_and_errors(capi):
+    """Tag runs longer than 511 are split (tag_arrays.cpp:942-957); bad symbols / zero lengths are refused."""
+    prep = load_package().prep
+    sym = np.frombuffer(b"\nACGT" * 40, dtype=np.uint8); ln = np.tile(np.array([1, 700, 30, 1200, 5], dtype=np.uint64), 40)
+    n = int(ln.sum())
+    tv = (np.arange(1, 41, dtype=np.uint64) << np.uint64(11)) | np.uint64(3); tl = np.full(40, n // 40, dtype=np.uint64); tl[-1] += n - int(tl.sum())
+    ri, _ = prep.rindex_from_rlbwt(prep.rlbwt_from_runs(sym, ln), encoded=True, with_samples=False)
+    tags_file, n_items = prep.tags_from_runs(tv, tl, 0)
+    a = capi.Index(ri, tags_file, 0); b = capi.Index.from_runs(sym, ln, tv, tl)
+    assert b.info["tag_items"] == n_items == a.info["tag_items"] and n_items > 40
+    st = np.arange(0, n - 600, 13, dtype=np.uint64); en = st + np.uint64(590)
+    A = a.tag_query_batch(st, en); Bq = b.tag_query_batch(st, en)
+    for k in ("n_runs", "tag_off", "tags"): assert np.array_equal(A[k], Bq[k]), k
+    pos = np.arange(0, n + 1, dtype=np.uint64); assert np.array_equal(a.rank_batch(pos), b.rank_batch(pos))
+    with pytest.raises(capi.PgiError): capi.Index.from_runs(np.frombuffer(b"\nAXC", dtype=np.uint8), np.ones(4, dtype=np.uint64))
+    with pytest.raises(capi.PgiError): capi.Index.from_runs(np.frombuffer(b"\nACG", dtype=np.uint8), np.array([1, 0, 2, 3], dtype=np.uint64))
