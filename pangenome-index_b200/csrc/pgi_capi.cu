@@ -591,7 +591,9 @@ struct pgi_batch {
     // tag stage
     DevBuf d_n_runs, d_cnt, d_raw_off, d_first, d_skip, d_raw, d_raw2, d_ucnt, d_tag_off, d_tags, d_large, d_seg_b, d_seg_e;
     PinBuf h_ctr, h_mem_off, h_mems, h_tag_off, h_tags, h_n_runs;
-    double mems_per_read = 4.0;
+    double mems_per_read = 4.0, raw_per_mem = 2.0;         // running estimates that size the next step's buffers
+    uint64_t mem_cap_hint = 0, raw_cap_hint = 0, large_cap_hint = 0;   // raised when a step did not fit (collect_and_check)
+    uint64_t mems_cap = 0, mem_slots = 0, part_cap = 0, raw_cap = 0, large_cap = 0;   // capacities the current step was launched with
     uint64_t n_mems = 0, n_tags = 0, extensions = 0, seed_lookups = 0;
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
@@ -634,7 +636,7 @@ extern "C" int pgi_batch_create(pgi_index *ix, void *cuda_stream, pgi_batch **ou
         else { CK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking)); b->own_stream = true; }
         for (int i = 0; i < EV_COUNT; ++i) CK(cudaEventCreate(&b->ev[i]));
         b->ev_ok = true;
-        b->d_ctr.need(64); b->h_ctr.need(64);
+        b->d_ctr.need(256); b->h_ctr.need(256);
         *out = b; return PGI_OK;
     } catch (const CudaError &e) { if (b) { b->ix = ix; pgi_batch_free(b); } return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
 }
@@ -677,35 +679,56 @@ void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_
     (void) launches;                                  // library (CUB) launches are not counted as ours
 }
 
-// counters in d_ctr / h_ctr (u64): [0] cursor, [1] mem_count, [2] ext_count, [3] large_count, [4] seed_count
-// A counter the host needs in the middle of a run is WRITTEN INTO PINNED HOST MEMORY BY A KERNEL (unified addressing: a
-// cudaHostAlloc pointer is valid on the device), not fetched with cudaMemcpyAsync: a copy, however small, queues on the
-// device-to-host copy engine behind the 200+ MB result download of whichever pgi_find_mems call finished just before, and
-// the compute token would be held idle for that long (concurrent callers, pgi_find_mems). Kernels do not queue there.
-__global__ void peek_kernel(const uint64_t *src, volatile uint64_t *host_dst, unsigned n) {
-    if (threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
-    __threadfence_system();
-}
-// Partitioned MEM slots: [5] = sum of the partition counters (MEMs appended), [6] = their maximum (overflow check).
-__global__ void peek_parts_kernel(const unsigned long long *slot_ctr, volatile uint64_t *host_dst) {
+// ---- One find_mems step is ONE stream-ordered sequence of launches with ONE host synchronisation at its end.
+// Every size a later stage needs (MEMs found, items to decode, long lists, unique tags) stays on the device: kernels are
+// launched over the CAPACITY of their buffers and read the count from the state words below; capacities come from the
+// previous steps on the same batch context (grow-only, with head-room), and the rare step that does not fit is detected
+// from the counters fetched at the end and run again with larger buffers. (Five host round trips per step -- sizing each
+// stage from the previous one's count -- exposed every step to five scheduler wake-ups; on a box with 8 ranks that was the
+// limiter of the device-resident rate: one rank at 15.6 ms per step beside seven at 9.5 ms, SCALE_r01.)
+//
+// device state words (d_ctr, u64): [0] read cursor  [1] MEM slots taken (single counter)  [2] FMD extensions  [4] seed lookups
+//   [8] MEMs found (exact even after an overflow)   [9] slots the fullest partition asked for   [10] MEMs the later stages
+//   see (= [8] clamped to the capacity of the ordered MEM buffer)   [12] long tag lists queued   [13] raw buffer too small
+// host mirror (h_ctr, pinned; written by collect_kernel): [0] = [8], [1] = [9], [2] extensions, [3] seed lookups,
+//   [4] items to decode (raw_off[nm]), [5] long lists, [6] raw overflow flag, [7] unique tags (tag_off[nm])
+// A counter reaches the host through a KERNEL writing pinned memory (unified addressing), not a cudaMemcpyAsync: a copy,
+// however small, queues on the device-to-host copy engine behind the result download of whichever call finished before.
+enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
+
+__global__ void mem_finalize_kernel(unsigned long long *st, const unsigned long long *slot_ctr, uint64_t part_cap, uint64_t mems_cap) {
     __shared__ unsigned long long s_sum[PGI_SLOT_PARTS], s_max[PGI_SLOT_PARTS];
     const unsigned t = threadIdx.x;
-    s_sum[t] = s_max[t] = slot_ctr[16u * t];
+    s_sum[t] = s_max[t] = part_cap ? slot_ctr[16u * t] : 0ull;
     __syncthreads();
     for (unsigned o = PGI_SLOT_PARTS / 2; o; o >>= 1) {
         if (t < o) { s_sum[t] += s_sum[t + o]; if (s_max[t + o] > s_max[t]) s_max[t] = s_max[t + o]; }
         __syncthreads();
     }
-    if (t == 0) { host_dst[5] = s_sum[0]; host_dst[6] = s_max[0]; __threadfence_system(); }
+    if (t == 0) {
+        const unsigned long long total = part_cap ? s_sum[0] : st[ST_SLOTS];
+        st[ST_NMEMS] = total; st[ST_MAXPART] = part_cap ? s_max[0] : total;
+        st[ST_NM] = total < mems_cap ? total : mems_cap;
+    }
 }
-void peek(pgi_batch *b, const void *dptr, unsigned n) {
-    peek_kernel<<<1, 32, 0, b->stream>>>((const uint64_t *) dptr, b->h_ctr.as<uint64_t>(), n);
+__global__ void set_nm_kernel(unsigned long long *st, uint64_t nm) { st[ST_NMEMS] = nm; st[ST_MAXPART] = 0; st[ST_NM] = nm; }
+__global__ void collect_kernel(const unsigned long long *st, const uint64_t *raw_off, const uint64_t *tag_off, volatile uint64_t *host) {
+    if (threadIdx.x == 0) {
+        const uint64_t nm = st[ST_NM];
+        host[0] = st[ST_NMEMS]; host[1] = st[ST_MAXPART]; host[2] = st[ST_EXT]; host[3] = st[ST_SEED];
+        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0;
+        __threadfence_system();
+    }
+}
+__global__ void peek_kernel(const uint64_t *src, volatile uint64_t *host_dst, unsigned n) {
+    if (threadIdx.x < n) host_dst[threadIdx.x] = src[threadIdx.x];
+    __threadfence_system();
+}
+uint64_t read_back(pgi_batch *b, const void *dptr) {              // locate only (not on the find_mems path)
+    peek_kernel<<<1, 32, 0, b->stream>>>((const uint64_t *) dptr, b->h_ctr.as<uint64_t>() + 8, 1);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(b->stream));
-}
-uint64_t read_back(pgi_batch *b, const void *dptr) {
-    peek(b, dptr, 1);
-    return *b->h_ctr.as<volatile uint64_t>();
+    return b->h_ctr.as<volatile uint64_t>()[8];
 }
 
 // K1 instantiations: block-fetch mode x CTA shape (pgi_kernels.cuh). PGI_K1=<name> picks one for tuning runs
@@ -723,11 +746,8 @@ const K1Variant &k1_variant() {
 
 // The persistent grid is sized for the occupancy the kernel's static shared memory allows (4 CTAs x 43 KB per SM). With the
 // default carve-out preference the driver chooses the shared-memory configuration itself; asking for the smallest one that
-// holds all those CTAs makes the occupancy the grid was sized for a fact instead of a heuristic. (Measured: no difference
-// to the driver's default on the boxes tried; the 8.8 <-> 10.7 ms spread of this kernel between GPUs, processes and even
-// launches -- DESIGN.md section 6 -- is NOT caused by the carve-out: it appears with every setting.)
+// holds all those CTAs makes the occupancy the grid was sized for a fact instead of a heuristic.
 static void prefer_max_shared(void (*fn)(const MemArgs)) {
-    // the smallest configuration that holds every CTA the other limits allow (PGI_CARVEOUT=<percent> overrides, -1 = driver default)
     const void *f = reinterpret_cast<const void *>(fn);
     cudaFuncAttributes at; CK(cudaFuncGetAttributes(&at, f));
     int dev = 0, smem_sm = 0, blocks = 0; CK(cudaGetDevice(&dev));
@@ -738,21 +758,29 @@ static void prefer_max_shared(void (*fn)(const MemArgs)) {
     if (pct > 100) pct = 100;
     CK(cudaFuncSetAttribute(f, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
 }
+static unsigned persistent_grid(pgi_index *ix, void (*fn)(const MemArgs), unsigned threads, uint64_t n) {
+    // the occupancy query and the carve-out are per function: asked once, not in every step
+    static std::mutex mu; static std::vector<std::pair<const void *, int>> cache;
+    int bps = 0;
+    { std::lock_guard<std::mutex> l(mu); for (auto &c : cache) if (c.first == (const void *) fn) bps = c.second; }
+    if (!bps) {
+        prefer_max_shared(fn);
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, (int) threads, 0));
+        if (bps < 1) bps = 1;
+        std::lock_guard<std::mutex> l(mu); cache.emplace_back((const void *) fn, bps);
+    }
+    return (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * bps, (n + threads - 1) / threads));
+}
 
-// MEM finding: K1 (+ re-run with a larger append buffer if it overflowed), scan, scatter.
-void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launches, int &reruns) {
+// MEM finding: K0 (2-bit codes), K1, the count of MEMs (device), scan of the per-read counts, scatter into read order.
+// Enqueues only. Leaves b->mems_cap = capacity of the ordered MEM buffer the later stages are launched over.
+void enqueue_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launches) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
     b->d_nmems.need((n + 1) * 8); b->d_mem_off.need((n + 1) * 8);
-    uint64_t cap = std::max<uint64_t>(1024, (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
-    int blocks_per_sm = 0;
+    const uint64_t cap = std::max<uint64_t>(1024, b->mem_cap_hint ? b->mem_cap_hint : (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
     const K1Variant &k1 = k1_variant();
-    prefer_max_shared(k1.fn);
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, k1.fn, (int) k1.threads, 0));
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-    const uint64_t want_blocks = (n + k1.threads - 1) / k1.threads;
-    const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, want_blocks));
-    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
-    uint64_t total = 0;
+    const unsigned grid = persistent_grid(ix, k1.fn, k1.threads, n);
+    unsigned long long *st = b->d_ctr.as<unsigned long long>();
     if (ix->seed_k && n) {                                   // K0: 2-bit codes + per-read flags for the seed lookups
         const uint64_t n_words = (b->reads_bytes + 7) / 8;
         b->d_codes.need(n_words * 2 + 16); b->d_read_flags.need((n / 32 + 1) * 4);
@@ -764,59 +792,37 @@ void run_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &launch
             ++launches; CK(cudaGetLastError());
         }
     }
-    // PGI_SLOT_PARTS=0 falls back to the single global slot counter (tuning / comparison runs)
-    // ... and so do small batches: with fewer reads than a few rounds of all warps the partitions fill unevenly (the read
-    // queue is dynamic), and their atomics are too few to matter anyway.
-    // PGI_SLOT_PARTS=<reads>: smallest batch that uses the partitions (default 600000; 0 = never; 1 = always: tests).
+    // MEM slots: one global counter, or -- for batches of PGI_SLOT_PARTS=<reads> (default 600000; 0 = never; 1 = always)
+    // reads and more -- 256 partitions with a counter each (pgi_kernels.cuh MemArgs)
     uint64_t parts_min = 600000;
     if (const char *e = std::getenv("PGI_SLOT_PARTS")) parts_min = std::strtoull(e, nullptr, 10);
     const bool parts_on = parts_min != 0 && n >= parts_min;
-    uint64_t part_cap = 0, slots = 0;
+    const uint64_t part_cap = parts_on ? (cap + PGI_SLOT_PARTS - 1) / PGI_SLOT_PARTS + 64 : 0;
+    const uint64_t slots = parts_on ? part_cap * PGI_SLOT_PARTS : cap;
+    b->part_cap = part_cap; b->mem_slots = slots; b->mems_cap = slots;
     b->d_slot_ctr.need(PGI_SLOT_PARTS * 128);
-    for (;;) {
-        part_cap = parts_on ? (cap + PGI_SLOT_PARTS - 1) / PGI_SLOT_PARTS + 64 : 0;
-        slots = parts_on ? part_cap * PGI_SLOT_PARTS : cap;
-        b->d_mem_buf.need(slots * 32); b->d_mem_key.need(slots * 8);
-        CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
-        CK(cudaMemsetAsync(b->d_slot_ctr.p, 0, PGI_SLOT_PARTS * 128, b->stream));
-        CK(cudaMemsetAsync(b->d_nmems.p, 0, (n + 1) * 8, b->stream));
-        MemArgs a;
-        a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
-        a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
-        a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
-        a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = cap;
-        a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
-        a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
-        CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
-        if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; }
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
-        if (parts_on) { peek_parts_kernel<<<1, PGI_SLOT_PARTS, 0, b->stream>>>(a.slot_ctr, b->h_ctr.as<uint64_t>()); CK(cudaGetLastError()); }
-        peek(b, ctr, 5);
-        volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
-        b->extensions = h[2]; b->seed_lookups = h[4];
-        if (parts_on) {
-            total = h[5];
-            if (h[6] <= part_cap) break;
-            cap = (h[6] + h[6] / 8 + 64) * PGI_SLOT_PARTS; ++reruns;   // the fullest partition overflowed: its count is exact, run again
-        } else {
-            total = h[1];
-            if (total <= cap) break;
-            cap = total + 1024; ++reruns;                // append buffer overflowed: the count is exact, run again
-        }
-    }
-    if (n) b->mems_per_read = std::max(1.0, (double) total / (double) n);
-    b->n_mems = total;
+    b->d_mem_buf.need(slots * 32); b->d_mem_key.need(slots * 8); b->d_mems.need((slots + 1) * 32);
+    CK(cudaMemsetAsync(st, 0, ST_WORDS * 8, b->stream));
+    CK(cudaMemsetAsync(b->d_slot_ctr.p, 0, PGI_SLOT_PARTS * 128, b->stream));
+    CK(cudaMemsetAsync(b->d_nmems.p, 0, (n + 1) * 8, b->stream));
+    MemArgs a;
+    a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
+    a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
+    a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.mem_cap = cap;
+    a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
+    a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
+    CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
+    if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
+    CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
+    mem_finalize_kernel<<<1, PGI_SLOT_PARTS, 0, b->stream>>>(st, a.slot_ctr, part_cap, b->mems_cap);
+    ++launches; CK(cudaGetLastError());
     CK(cudaEventRecord(b->ev[EV_MEM], b->stream));
     exclusive_scan(b, b->d_nmems.as<uint64_t>(), b->d_mem_off.as<uint64_t>(), n + 1, launches);
-    b->d_mems.need(std::max<uint64_t>(1, total) * 32);
-    if (total) {
-        const uint64_t walk = parts_on ? slots : total;
-        mem_scatter_kernel<<<grid_for(walk, 256), 256, 0, b->stream>>>(b->d_mem_buf.as<uint4>(), b->d_mem_key.as<uint64_t>(),
-                                                                         b->d_mem_off.as<uint64_t>(), walk, b->d_mems.as<uint4>(),
-                                                                         b->d_slot_ctr.as<unsigned long long>(), part_cap);
-        ++launches; CK(cudaGetLastError());
-    }
+    mem_scatter_kernel<<<grid_for(slots, 256), 256, 0, b->stream>>>(b->d_mem_buf.as<uint4>(), b->d_mem_key.as<uint64_t>(), b->d_mem_off.as<uint64_t>(), slots,
+                                                                      b->d_mems.as<uint4>(), b->d_slot_ctr.as<unsigned long long>(), part_cap,
+                                                                      (const uint64_t *) (st + ST_NMEMS), b->mems_cap);
+    ++launches; CK(cudaGetLastError());
     CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
 }
 
@@ -825,90 +831,113 @@ __global__ void iota_kernel(uint64_t n_plus_1, uint64_t *out) {
     const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
     if (i < n_plus_1) out[i] = i;
 }
-void run_count_stage(pgi_batch *b, int &launches) {
+void enqueue_count_stage(pgi_batch *b, int &launches) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
-    b->d_mem_off.need((n + 1) * 8); b->d_mems.need(std::max<uint64_t>(1, n) * 32);
+    b->d_mem_off.need((n + 1) * 8); b->d_mems.need((n + 1) * 32);
     void (*fn)(const MemArgs) = fmd_mem_kernel<1, 256, 4, 1>; const unsigned threads = 256;
-    prefer_max_shared(fn);
-    int blocks_per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fn, (int) threads, 0));
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-    const unsigned grid = (unsigned) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) ix->sm_count * blocks_per_sm, (n + threads - 1) / threads));
-    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
-    CK(cudaMemsetAsync(ctr, 0, 64, b->stream));
+    const unsigned grid = persistent_grid(ix, fn, threads, n);
+    unsigned long long *st = b->d_ctr.as<unsigned long long>();
+    CK(cudaMemsetAsync(st, 0, ST_WORDS * 8, b->stream));
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
-    a.cursor = ctr; a.mem_count = ctr + 1; a.ext_count = ctr + 2; a.seed_count = ctr + 4; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
     CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
     iota_kernel<<<grid_for(n + 1, 256), 256, 0, b->stream>>>(n + 1, b->d_mem_off.as<uint64_t>());
-    ++launches; CK(cudaGetLastError());
-    b->extensions = read_back(b, ctr + 2); b->seed_lookups = 0;
-    b->n_mems = n;
+    set_nm_kernel<<<1, 1, 0, b->stream>>>(st, n);
+    launches += 2; CK(cudaGetLastError());
+    b->mems_cap = n; b->part_cap = 0; b->mem_slots = n;
     CK(cudaEventRecord(b->ev[EV_MEM], b->stream)); CK(cudaEventRecord(b->ev[EV_ORDER], b->stream));
 }
 
-// Tag lookup for nm intervals given either as ordered MEM records or as start/end arrays (device pointers).
-void run_tag_stage(pgi_batch *b, uint64_t nm, const uint4 *mems, const uint64_t *start, const uint64_t *end, int &launches) {
-    pgi_index *ix = b->ix; cudaStream_t st = b->stream;
-    b->d_n_runs.need((nm + 1) * 8); b->d_cnt.need((nm + 1) * 8); b->d_raw_off.need((nm + 1) * 8); b->d_first.need((nm + 1) * 8);
-    b->d_skip.need((nm + 1) * 4); b->d_ucnt.need((nm + 1) * 8); b->d_tag_off.need((nm + 1) * 8); b->d_large.need((nm + 1) * 8);
-    unsigned long long *ctr = b->d_ctr.as<unsigned long long>();
-    CK(cudaMemsetAsync(ctr + 3, 0, 8, st));
-    CK(cudaMemsetAsync(b->d_cnt.as<uint64_t>() + nm, 0, 8, st));
-    CK(cudaMemsetAsync(b->d_ucnt.as<uint64_t>() + nm, 0, 8, st));
-    if (nm) {
-        tag_plan_kernel<<<grid_for(nm, 256), 256, 0, st>>>(ix->tg, nm, mems, start, end, b->d_n_runs.as<uint64_t>(), b->d_cnt.as<uint64_t>(),
+// Tag lookup for up to `cap` intervals (their number is st[ST_NM]) given either as ordered MEM records or as start/end
+// arrays (device pointers). Enqueues only.
+void enqueue_tag_stage(pgi_batch *b, uint64_t cap, const uint4 *mems, const uint64_t *start, const uint64_t *end, int &launches) {
+    pgi_index *ix = b->ix; cudaStream_t s = b->stream;
+    unsigned long long *st = b->d_ctr.as<unsigned long long>();
+    const uint64_t *nm_dev = (const uint64_t *) (st + ST_NM);
+    b->d_n_runs.need((cap + 1) * 8); b->d_cnt.need((cap + 1) * 8); b->d_raw_off.need((cap + 1) * 8); b->d_first.need((cap + 1) * 8);
+    b->d_skip.need((cap + 1) * 4); b->d_ucnt.need((cap + 1) * 8); b->d_tag_off.need((cap + 1) * 8);
+    const uint64_t raw_cap = std::max<uint64_t>(b->raw_cap_hint, (uint64_t) ((double) cap * std::max(1.0, b->raw_per_mem) * 1.25) + 4096);
+    const uint64_t large_cap = b->large_cap_hint;
+    b->raw_cap = raw_cap; b->large_cap = large_cap;
+    b->d_raw.need(raw_cap * 8); b->d_tags.need(raw_cap * 8); b->d_large.need((large_cap + 1) * 8);
+    CK(cudaMemsetAsync(b->d_cnt.p, 0, (cap + 1) * 8, s)); CK(cudaMemsetAsync(b->d_ucnt.p, 0, (cap + 1) * 8, s));
+    CK(cudaMemsetAsync(b->d_n_runs.p, 0, (cap + 1) * 8, s));
+    if (cap) {
+        tag_plan_kernel<<<grid_for(cap, 256), 256, 0, s>>>(ix->tg, cap, nm_dev, mems, start, end, b->d_n_runs.as<uint64_t>(), b->d_cnt.as<uint64_t>(),
                                                            b->d_first.as<uint64_t>(), b->d_skip.as<uint32_t>());
         ++launches; CK(cudaGetLastError());
     }
-    exclusive_scan(b, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), nm + 1, launches);
-    const uint64_t total_raw = read_back(b, b->d_raw_off.as<uint64_t>() + nm);
-    CK(cudaEventRecord(b->ev[EV_PLAN], st));
-    b->d_raw.need(std::max<uint64_t>(1, total_raw) * 8);
-    if (nm) {
-        tag_small_kernel<<<grid_for(nm, 128), 128, 0, st>>>(ix->tg, nm, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_first.as<uint64_t>(),
-                                                            b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(), b->d_ucnt.as<uint64_t>(),
-                                                            b->d_large.as<uint64_t>(), ctr + 3);
+    exclusive_scan(b, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), cap + 1, launches);
+    CK(cudaEventRecord(b->ev[EV_PLAN], s));
+    if (cap) {
+        tag_small_kernel<<<grid_for(cap, 128), 128, 0, s>>>(ix->tg, cap, nm_dev, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_first.as<uint64_t>(),
+                                                            b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(), raw_cap, b->d_ucnt.as<uint64_t>(),
+                                                            b->d_large.as<uint64_t>(), large_cap, st + ST_LARGE);
         ++launches; CK(cudaGetLastError());
     }
-    const uint64_t n_large = nm ? read_back(b, ctr + 3) : 0;
-    if (n_large) {
-        b->d_raw2.need(total_raw * 8); b->d_seg_b.need(n_large * 8); b->d_seg_e.need(n_large * 8);
-        const unsigned g = grid_for(n_large * 32, 256);
-        tag_large_decode_kernel<<<g, 256, 0, st>>>(ix->tg, n_large, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
-                                                   b->d_first.as<uint64_t>(), b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(),
-                                                   b->d_seg_b.as<uint64_t>(), b->d_seg_e.as<uint64_t>());
+    const unsigned lgrid = (unsigned) std::min<uint64_t>((uint64_t) ix->sm_count * 8, std::max<uint64_t>(1, (large_cap * 32 + 255) / 256));
+    if (large_cap) {                                    // long lists (more than PGI_TAG_SMALL runs): warp per list + CUB segmented sort
+        b->d_raw2.need(raw_cap * 8); b->d_seg_b.need(large_cap * 8); b->d_seg_e.need(large_cap * 8);
+        CK(cudaMemsetAsync(b->d_seg_b.p, 0, large_cap * 8, s)); CK(cudaMemsetAsync(b->d_seg_e.p, 0, large_cap * 8, s));
+        tag_large_decode_kernel<<<lgrid, 256, 0, s>>>(ix->tg, st + ST_LARGE, large_cap, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                      b->d_first.as<uint64_t>(), b->d_skip.as<uint32_t>(), b->d_raw.as<uint64_t>(),
+                                                      b->d_seg_b.as<uint64_t>(), b->d_seg_e.as<uint64_t>());
         CK(cudaGetLastError());
         size_t tmp = 0;
-        CK(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) total_raw, (int64_t) n_large,
-                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), st));
+        CK(cub::DeviceSegmentedSort::SortKeys(nullptr, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) raw_cap, (int64_t) large_cap,
+                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), s));
         b->d_cub.need(tmp);
-        CK(cub::DeviceSegmentedSort::SortKeys(b->d_cub.p, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) total_raw, (int64_t) n_large,
-                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), st));
-        tag_large_unique_kernel<<<g, 256, 0, st>>>(n_large, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
-                                                   b->d_raw2.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_ucnt.as<uint64_t>());
+        CK(cub::DeviceSegmentedSort::SortKeys(b->d_cub.p, tmp, b->d_raw.as<uint64_t>(), b->d_raw2.as<uint64_t>(), (int64_t) raw_cap, (int64_t) large_cap,
+                                              b->d_seg_b.as<int64_t>(), b->d_seg_e.as<int64_t>(), s));
+        tag_large_unique_kernel<<<lgrid, 256, 0, s>>>(st + ST_LARGE, large_cap, b->d_large.as<uint64_t>(), b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                      b->d_raw2.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_ucnt.as<uint64_t>());
         CK(cudaGetLastError());
         launches += 2;                                   // decode + unique (the segmented sort is CUB's)
     }
-    CK(cudaEventRecord(b->ev[EV_DECODE], st));
-    exclusive_scan(b, b->d_ucnt.as<uint64_t>(), b->d_tag_off.as<uint64_t>(), nm + 1, launches);
-    const uint64_t n_tags = read_back(b, b->d_tag_off.as<uint64_t>() + nm);
-    b->d_tags.need(std::max<uint64_t>(1, n_tags) * 8);
-    if (nm) {
-        tag_copy_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_tag_off.as<uint64_t>(),
+    CK(cudaEventRecord(b->ev[EV_DECODE], s));
+    exclusive_scan(b, b->d_ucnt.as<uint64_t>(), b->d_tag_off.as<uint64_t>(), cap + 1, launches);
+    if (cap) {
+        tag_copy_kernel<<<grid_for(cap, 256), 256, 0, s>>>(cap, nm_dev, b->d_cnt.as<uint64_t>(), b->d_raw_off.as<uint64_t>(), b->d_tag_off.as<uint64_t>(),
                                                            b->d_raw.as<uint64_t>(), b->d_tags.as<uint64_t>());
         ++launches; CK(cudaGetLastError());
     }
-    if (n_large) {
-        tag_large_copy_kernel<<<grid_for(n_large * 32, 256), 256, 0, st>>>(n_large, b->d_large.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
-                                                                           b->d_tag_off.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_tags.as<uint64_t>());
+    if (large_cap) {
+        tag_large_copy_kernel<<<lgrid, 256, 0, s>>>(st + ST_LARGE, large_cap, b->d_large.as<uint64_t>(), b->d_raw_off.as<uint64_t>(),
+                                                    b->d_tag_off.as<uint64_t>(), b->d_raw.as<uint64_t>(), b->d_tags.as<uint64_t>());
         ++launches; CK(cudaGetLastError());
     }
-    b->n_tags = n_tags;
+}
+
+// The ONE synchronisation of a step: fetch the counters, decide whether everything fitted. Returns true when the step has
+// to be run again (capacity hints of the batch were raised).
+bool collect_and_check(pgi_batch *b, bool with_tags, bool mem_stage) {
+    unsigned long long *st = b->d_ctr.as<unsigned long long>();
+    collect_kernel<<<1, 32, 0, b->stream>>>(st, with_tags ? b->d_raw_off.as<uint64_t>() : nullptr, with_tags ? b->d_tag_off.as<uint64_t>() : nullptr, b->h_ctr.as<uint64_t>());
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(b->ev[EV_END], b->stream));
+    CK(cudaStreamSynchronize(b->stream));
+    volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
+    const uint64_t total = h[0], maxpart = h[1], total_raw = h[4], n_large = h[5], raw_ovf = h[6];
+    b->extensions = h[2]; b->seed_lookups = h[3]; b->n_mems = total; b->n_tags = with_tags ? h[7] : 0;
+    bool again = false;
+    if (mem_stage) {
+        if (b->part_cap ? maxpart > b->part_cap : total > b->mem_slots) {
+            // the counts are exact: size for them (partitioned: every partition gets what the fullest one asked for)
+            b->mem_cap_hint = b->part_cap ? (maxpart + maxpart / 8 + 64) * PGI_SLOT_PARTS : total + total / 8 + 1024;
+            again = true;
+        } else if (b->n_reads) { b->mems_per_read = std::max(1.0, (double) total / (double) b->n_reads); b->mem_cap_hint = 0; }
+    }
+    if (with_tags && !again) {
+        if (raw_ovf || total_raw > b->raw_cap) { b->raw_cap_hint = std::max<uint64_t>(2 * b->raw_cap, total_raw + total_raw / 4 + 4096); again = true; }
+        if (n_large > b->large_cap) { b->large_cap_hint = std::max<uint64_t>(1024, n_large + n_large / 2); again = true; }
+        if (!again && total) b->raw_per_mem = std::max(1.0, (double) total_raw / (double) total);
+    }
+    return again;
 }
 
 float ev_ms(pgi_batch *b, int from, int to) { float ms = 0; cudaEventElapsedTime(&ms, b->ev[from], b->ev[to]); return ms; }
@@ -931,22 +960,24 @@ static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t m
     try {
         DeviceGuard g(b->ix->device);
         int launches = 0, reruns = 0;
-        CK(cudaEventRecord(b->ev[EV_START], b->stream));
-        if (count_mode) run_count_stage(b, launches);
-        else run_mem_stage(b, min_len, min_occ, launches, reruns);
-        const uint64_t nm = b->n_mems;
-        if (b->ix->has_tags) run_tag_stage(b, nm, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
-        else {
-            b->d_tag_off.need((nm + 1) * 8); b->d_n_runs.need((nm + 1) * 8); b->d_tags.need(8);
-            CK(cudaMemsetAsync(b->d_tag_off.p, 0, (nm + 1) * 8, b->stream));
-            CK(cudaMemsetAsync(b->d_n_runs.p, 0, (nm + 1) * 8, b->stream));
-            CK(cudaEventRecord(b->ev[EV_PLAN], b->stream)); CK(cudaEventRecord(b->ev[EV_DECODE], b->stream));
-            b->n_tags = 0;
+        const bool with_tags = b->ix->has_tags;
+        for (;; ++reruns) {
+            if (reruns > 8) return fail(PGI_ECUDA, "internal: the work buffers of a step did not converge");
+            launches = 0;
+            CK(cudaEventRecord(b->ev[EV_START], b->stream));
+            if (count_mode) enqueue_count_stage(b, launches);
+            else enqueue_mem_stage(b, min_len, min_occ, launches);
+            if (with_tags) enqueue_tag_stage(b, b->mems_cap, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
+            else {
+                b->d_tag_off.need((b->mems_cap + 1) * 8); b->d_n_runs.need((b->mems_cap + 1) * 8); b->d_tags.need(8);
+                CK(cudaMemsetAsync(b->d_tag_off.p, 0, (b->mems_cap + 1) * 8, b->stream));
+                CK(cudaMemsetAsync(b->d_n_runs.p, 0, (b->mems_cap + 1) * 8, b->stream));
+                CK(cudaEventRecord(b->ev[EV_PLAN], b->stream)); CK(cudaEventRecord(b->ev[EV_DECODE], b->stream));
+            }
+            ++launches;                                      // collect_kernel
+            if (!collect_and_check(b, with_tags, !count_mode)) break;
         }
-        CK(cudaEventRecord(b->ev[EV_END], b->stream));
-        CK(cudaStreamSynchronize(b->stream));
-        // [0] the K1 launch alone (device time between two in-stream events; EV_START..EV_MEM also holds the pre-pass, the
-        // counter read-back and the host's wake-up from it, which is host time on a busy multi-GPU box)
+        // [0] the K1 launch alone (device time between two in-stream events)
         b->stage_ms[0] = ev_ms(b, EV_K1A, EV_K1B); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
         b->stage_ms[3] = ev_ms(b, EV_PLAN, EV_DECODE); b->stage_ms[4] = ev_ms(b, EV_DECODE, EV_END); b->stage_ms[5] = ev_ms(b, EV_START, EV_END);
         b->stage_ms[6] = launches; b->stage_ms[7] = reruns;
@@ -1067,9 +1098,17 @@ extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *st
         b->d_reads.need(std::max<uint64_t>(1, n) * 16);
         uint64_t *ds = b->d_reads.as<uint64_t>(), *de = ds + n;
         if (n) { CK(cudaMemcpyAsync(ds, start, n * 8, cudaMemcpyHostToDevice, b->stream)); CK(cudaMemcpyAsync(de, end, n * 8, cudaMemcpyHostToDevice, b->stream)); }
-        int launches = 0;
-        CK(cudaEventRecord(b->ev[EV_START], b->stream));
-        run_tag_stage(b, n, nullptr, ds, de, launches);
+        for (int tries = 0;; ++tries) {
+            if (tries > 8) { pool_give(ix, b); return fail(PGI_ECUDA, "internal: the work buffers of a tag query did not converge"); }
+            int launches = 0;
+            CK(cudaEventRecord(b->ev[EV_START], b->stream));
+            CK(cudaMemsetAsync(b->d_ctr.p, 0, ST_WORDS * 8, b->stream));
+            set_nm_kernel<<<1, 1, 0, b->stream>>>(b->d_ctr.as<unsigned long long>(), n);
+            CK(cudaGetLastError());
+            b->mems_cap = n; b->part_cap = 0; b->mem_slots = n;
+            enqueue_tag_stage(b, n, nullptr, ds, de, launches);
+            if (!collect_and_check(b, true, false)) break;
+        }
         b->n_reads = 0; b->n_mems = n; b->extensions = 0; b->seed_lookups = 0; b->has_result = true;
         b->d_mem_off.need(8); CK(cudaMemsetAsync(b->d_mem_off.p, 0, 8, b->stream));
         b->d_mems.need(std::max<uint64_t>(1, n) * 32);

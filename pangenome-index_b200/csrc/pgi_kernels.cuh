@@ -376,14 +376,18 @@ __global__ void pack_reads_kernel(const uint64_t *reads64, uint64_t n_words, uin
     }
 }
 
-// K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read.
+// K4. Appended MEMs -> read order: dst = mem_off[read] + index within the read. The number of appended MEMs is read from
+// device memory (state[0]; the host does not know it yet: the whole step is stream-ordered, pgi_capi.cu batch_run).
 __global__ void mem_scatter_kernel(const uint4 *mem_buf, const uint64_t *mem_key, const uint64_t *mem_off,
-                                   uint64_t n_mems, uint4 *mems, const unsigned long long *slot_ctr, uint64_t part_cap) {
+                                   uint64_t n_slots, uint4 *mems, const unsigned long long *slot_ctr, uint64_t part_cap,
+                                   const uint64_t *n_appended, uint64_t mems_cap) {
     const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (i >= n_mems) return;                                            // partitioned: n_mems = PGI_SLOT_PARTS * part_cap slots
-    if (part_cap && i % part_cap >= slot_ctr[16u * (i / part_cap)]) return;   // behind the filled prefix of its partition
+    if (i >= n_slots) return;                                           // partitioned: n_slots = PGI_SLOT_PARTS * part_cap slots
+    if (part_cap) { if (i % part_cap >= slot_ctr[16u * (i / part_cap)]) return; }   // behind the filled prefix of its partition
+    else if (i >= *n_appended) return;
     const uint64_t key = mem_key[i];
     const uint64_t dst = mem_off[key >> 32] + (key & 0xFFFFFFFFull);
+    if (dst >= mems_cap) return;                                        // only after an overflow (the step is run again)
     mems[2 * dst] = mem_buf[2 * i]; mems[2 * dst + 1] = mem_buf[2 * i + 1];
 }
 

@@ -6,13 +6,17 @@
 
 namespace pgi {
 
+// The number of MEMs (nm) of a step is known on the device only (state word written by mem_finalize_kernel): every kernel
+// below is launched over the CAPACITY of the MEM buffers and takes nm from *n_dev, so that one find_mems step is a single
+// stream-ordered sequence without host round trips (pgi_capi.cu batch_run).
+//
 // K2a. One thread per MEM: the two ranks and the select; sizes only.
 // Intervals come either from ordered MEM records (mems != nullptr: [bwt_start, bwt_start + size - 1])
-// or from explicit start/end arrays.
-__global__ void tag_plan_kernel(TagDev t, uint64_t n, const uint4 *mems, const uint64_t *start, const uint64_t *end,
+// or from explicit start/end arrays. cnt[] is zeroed beforehand (entries >= nm stay 0 for the scan).
+__global__ void tag_plan_kernel(TagDev t, uint64_t cap, const uint64_t *n_dev, const uint4 *mems, const uint64_t *start, const uint64_t *end,
                                 uint64_t *n_runs, uint64_t *cnt, uint64_t *first_item, uint32_t *skip) {
     const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i >= cap || i >= *n_dev) return;
     uint64_t s, e;
     if (mems) {
         const uint4 r = __ldg(mems + 2 * i + 1);
@@ -24,16 +28,19 @@ __global__ void tag_plan_kernel(TagDev t, uint64_t n, const uint4 *mems, const u
     n_runs[i] = p.n_runs; cnt[i] = p.count; first_item[i] = p.first_item; skip[i] = (uint32_t) p.skip;
 }
 
+// Tag-stage state words (device): [0] number of long lists queued (keeps counting past large_cap), [1] set when a list
+// did not fit the raw buffer (raw_cap).
 // K2b (short lists). One thread per MEM: decode <= PGI_TAG_SMALL runs, insertion sort, unique; the unique
 // values go to raw[raw_off[m] ..) and their number to ucnt[m]. Longer lists are queued for the warp kernels.
-__global__ void tag_small_kernel(TagDev t, uint64_t n, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *first_item,
-                                 const uint32_t *skip, uint64_t *raw, uint64_t *ucnt, uint64_t *large_list,
-                                 unsigned long long *large_count) {
+__global__ void tag_small_kernel(TagDev t, uint64_t cap, const uint64_t *n_dev, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *first_item,
+                                 const uint32_t *skip, uint64_t *raw, uint64_t raw_cap, uint64_t *ucnt, uint64_t *large_list, uint64_t large_cap,
+                                 unsigned long long *tag_state) {
     const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (m >= n) return;
+    if (m >= cap || m >= *n_dev) return;
     const uint64_t c = cnt[m];
     if (c == 0) { ucnt[m] = 0; return; }
-    if (c > PGI_TAG_SMALL) { large_list[atomicAdd(large_count, 1ull)] = m; return; }
+    if (raw_off[m] + c > raw_cap) { tag_state[1] = 1ull; ucnt[m] = 0; return; }
+    if (c > PGI_TAG_SMALL) { const unsigned long long q = atomicAdd(tag_state, 1ull); if (q < large_cap) large_list[q] = m; ucnt[m] = 0; return; }
     uint64_t v[PGI_TAG_SMALL];
     uint32_t k = 0;                                     // sorted unique prefix v[0..k)
     uint64_t loc = first_item[m]; const uint32_t sk = skip[m];
@@ -52,60 +59,65 @@ __global__ void tag_small_kernel(TagDev t, uint64_t n, const uint64_t *cnt, cons
     ucnt[m] = k;
 }
 
-// K2b (long lists). One warp per queued MEM: decode its runs into raw (lane-strided for the bit-packed
-// layout; the ByteCode stream is inherently serial and is walked by lane 0).
-__global__ void tag_large_decode_kernel(TagDev t, uint64_t n_large, const uint64_t *large_list, const uint64_t *cnt,
+// K2b (long lists). One warp per queued MEM (grid-stride over the queue, whose length is on the device): decode its runs
+// into raw (lane-strided for the bit-packed layout; the ByteCode stream is inherently serial and is walked by lane 0).
+// Segments of queue slots that stay unused are empty (seg arrays are zeroed beforehand).
+__device__ __forceinline__ uint64_t queued(const unsigned long long *tag_state, uint64_t large_cap) { const uint64_t q = tag_state[0]; return q < large_cap ? q : large_cap; }
+__global__ void tag_large_decode_kernel(TagDev t, const unsigned long long *tag_state, uint64_t large_cap, const uint64_t *large_list, const uint64_t *cnt,
                                         const uint64_t *raw_off, const uint64_t *first_item, const uint32_t *skip,
                                         uint64_t *raw, uint64_t *seg_begin, uint64_t *seg_end) {
-    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31u;
-    if (w >= n_large) return;
-    const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
-    if (lane == 0) { seg_begin[w] = o; seg_end[w] = o + c; }
-    if (t.layout == 0) {
-        const uint64_t f = first_item[m] + skip[m];
-        for (uint64_t i = lane; i < c; i += 32) raw[o + i] = tag_item_compact(t, f + i);
-    } else if (lane == 0) {
-        uint64_t loc = first_item[m];
-        for (uint32_t i = 0, sk = skip[m]; i < sk; ++i) (void) tag_bytecode_next(t, loc);
-        for (uint64_t i = 0; i < c; ++i) raw[o + i] = tag_value_bytecode(tag_bytecode_next(t, loc));
+    const uint64_t n_large = queued(tag_state, large_cap), n_warps = ((uint64_t) gridDim.x * blockDim.x) >> 5;
+    for (uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5; w < n_large; w += n_warps) {
+        const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
+        if (lane == 0) { seg_begin[w] = o; seg_end[w] = o + c; }
+        if (t.layout == 0) {
+            const uint64_t f = first_item[m] + skip[m];
+            for (uint64_t i = lane; i < c; i += 32) raw[o + i] = tag_item_compact(t, f + i);
+        } else if (lane == 0) {
+            uint64_t loc = first_item[m];
+            for (uint32_t i = 0, sk = skip[m]; i < sk; ++i) (void) tag_bytecode_next(t, loc);
+            for (uint64_t i = 0; i < c; ++i) raw[o + i] = tag_value_bytecode(tag_bytecode_next(t, loc));
+        }
     }
 }
 
 // K3 (long lists). One warp per queued MEM: unique of the sorted segment in `sorted`, written back to raw.
-__global__ void tag_large_unique_kernel(uint64_t n_large, const uint64_t *large_list, const uint64_t *cnt, const uint64_t *raw_off,
+__global__ void tag_large_unique_kernel(const unsigned long long *tag_state, uint64_t large_cap, const uint64_t *large_list, const uint64_t *cnt, const uint64_t *raw_off,
                                         const uint64_t *sorted, uint64_t *raw, uint64_t *ucnt) {
-    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31u;
-    if (w >= n_large) return;
-    const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
-    uint64_t k = 0;
-    for (uint64_t b = 0; b < c; b += 32) {
-        const uint64_t i = b + lane;
-        bool keep = false; uint64_t x = 0;
-        if (i < c) { x = sorted[o + i]; keep = i == 0 || sorted[o + i - 1] != x; }
-        const unsigned mask = __ballot_sync(0xFFFFFFFFu, keep);
-        if (keep) raw[o + k + __popc(mask & ((1u << lane) - 1u))] = x;
-        k += __popc(mask);
+    const uint64_t n_large = queued(tag_state, large_cap), n_warps = ((uint64_t) gridDim.x * blockDim.x) >> 5;
+    for (uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5; w < n_large; w += n_warps) {
+        const uint64_t m = large_list[w], c = cnt[m], o = raw_off[m];
+        uint64_t k = 0;
+        for (uint64_t b = 0; b < c; b += 32) {
+            const uint64_t i = b + lane;
+            bool keep = false; uint64_t x = 0;
+            if (i < c) { x = sorted[o + i]; keep = i == 0 || sorted[o + i - 1] != x; }
+            const unsigned mask = __ballot_sync(0xFFFFFFFFu, keep);
+            if (keep) raw[o + k + __popc(mask & ((1u << lane) - 1u))] = x;
+            k += __popc(mask);
+        }
+        if (lane == 0) ucnt[m] = k;
     }
-    if (lane == 0) ucnt[m] = k;
 }
 
 // K4. Compaction: unique lists -> tags[tag_off[m] ..). Short lists: one thread per MEM.
-__global__ void tag_copy_kernel(uint64_t n, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *tag_off,
+__global__ void tag_copy_kernel(uint64_t cap, const uint64_t *n_dev, const uint64_t *cnt, const uint64_t *raw_off, const uint64_t *tag_off,
                                 const uint64_t *raw, uint64_t *tags) {
     const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (m >= n || cnt[m] > PGI_TAG_SMALL) return;
+    if (m >= cap || m >= *n_dev || cnt[m] > PGI_TAG_SMALL) return;
     const uint64_t a = tag_off[m], k = tag_off[m + 1] - a; const uint64_t *src = raw + raw_off[m];
     for (uint64_t i = 0; i < k; ++i) tags[a + i] = src[i];
 }
-__global__ void tag_large_copy_kernel(uint64_t n_large, const uint64_t *large_list, const uint64_t *raw_off, const uint64_t *tag_off,
+__global__ void tag_large_copy_kernel(const unsigned long long *tag_state, uint64_t large_cap, const uint64_t *large_list, const uint64_t *raw_off, const uint64_t *tag_off,
                                       const uint64_t *raw, uint64_t *tags) {
-    const uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31u;
-    if (w >= n_large) return;
-    const uint64_t m = large_list[w], a = tag_off[m], k = tag_off[m + 1] - a, o = raw_off[m];
-    for (uint64_t i = lane; i < k; i += 32) tags[a + i] = raw[o + i];
+    const uint64_t n_large = queued(tag_state, large_cap), n_warps = ((uint64_t) gridDim.x * blockDim.x) >> 5;
+    for (uint64_t w = (blockIdx.x * (uint64_t) blockDim.x + threadIdx.x) >> 5; w < n_large; w += n_warps) {
+        const uint64_t m = large_list[w], a = tag_off[m], k = tag_off[m + 1] - a, o = raw_off[m];
+        for (uint64_t i = lane; i < k; i += 32) tags[a + i] = raw[o + i];
+    }
 }
 
 // M1. Random-access roofline: every thread walks `chain` dependent hops through a buffer of `n_slots`
