@@ -32,22 +32,36 @@ def capture_stdout():
 def log(*a):
     print("[bench]", *a, file=sys.stderr, flush=True)
 
+WORKLOADS = {
+    # name: (ref_len, n_hap, read_len, reads_per_step, substitution rate, 1-bp indel rate, BASELINE.json config it is)
+    "config4": (150_000_000, 256, 150, 2_000_000, 0.01, 0.0, "configs[3]: synthetic 256-haplotype 150 Mbp pangenome + reverse complements (random reference with N stretches, SNP 1/1000, indel 1/10000; exact BWT from the graph structure), 150 bp reads with 1 % substitutions"),
+    "config3": (50_000_000, 64, 150, 2_000_000, 0.01, 0.0, "configs[2]: synthetic 64-haplotype 50 Mbp pangenome + reverse complements (random reference with N stretches, SNP 1/1000, indel 1/10000; exact BWT from the graph structure), 150 bp reads with 1 % substitutions"),
+    "long": (150_000_000, 256, 10_000, 30_000, 0.03, 0.02, "configs[4]: long-read stress, 10 kbp reads with 5 % errors (3 % substitutions + 2 % 1-bp indels) on the 256-haplotype 150 Mbp index"),
+}
+
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=9)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    p.add_argument("--workload", default="synth", choices=["synth", "xy"])
-    p.add_argument("--ref-len", type=int, default=int(os.environ.get("PGI_BENCH_REF_LEN", 50_000_000)))
-    p.add_argument("--n-hap", type=int, default=int(os.environ.get("PGI_BENCH_N_HAP", 20)))
-    p.add_argument("--reads-per-step", type=int, default=int(os.environ.get("PGI_BENCH_READS", 2_000_000)))
-    p.add_argument("--read-len", type=int, default=150)
-    p.add_argument("--sub", type=float, default=0.01)
+    p.add_argument("--workload", default=os.environ.get("PGI_BENCH_WORKLOAD", "config4"), choices=["config4", "config3", "long", "xy", "x"])
+    p.add_argument("--ref-len", type=int, default=int(os.environ.get("PGI_BENCH_REF_LEN", 0)), help="override the workload's reference length (diagnostic runs)")
+    p.add_argument("--n-hap", type=int, default=int(os.environ.get("PGI_BENCH_N_HAP", 0)))
+    p.add_argument("--reads-per-step", type=int, default=int(os.environ.get("PGI_BENCH_READS", 0)))
     p.add_argument("--min-len", type=int, default=20)
     p.add_argument("--min-occ", type=int, default=1)
     p.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
-    return p.parse_args()
+    p.add_argument("--no-extras", action="store_true", help="skip the next-row / text-format / microbenchmark legs (scaling runs)")
+    p.add_argument("--device-only", action="store_true", help="stop after the device-resident steps (profiler runs: ncu replays every kernel)")
+    a = p.parse_args()
+    if a.workload in WORKLOADS:
+        w = WORKLOADS[a.workload]
+        a.nominal = not (a.ref_len or a.n_hap)
+        a.ref_len = a.ref_len or w[0]; a.n_hap = a.n_hap or w[1]; a.read_len = w[2]; a.reads_per_step = a.reads_per_step or w[3]; a.sub = w[4]; a.indel = w[5]
+    else:
+        a.nominal = True; a.read_len = 150; a.reads_per_step = a.reads_per_step or (1_000_000 if a.workload == "xy" else 10_000); a.sub = 0.01 if a.workload == "xy" else 0.0; a.indel = 0.0
+    return a
 
 class ClockSampler(threading.Thread):
     """SM clocks / throttle reasons during the timed region (B200_PROFILING.md), read in-process through NVML
@@ -123,79 +137,165 @@ def host_threads():
     try: return max(1, len(os.sched_getaffinity(0)))
     except Exception: return max(1, os.cpu_count() or 1)
 
-def make_workload(args, dev_index, rank):
-    """-> dict(ri, tags, layout, reads (cuda uint8 [pool, n, L]), name, facts). Data prep only (not timed)."""
+class Workload:
+    """Index + read batches for one rank. Data prep only (never timed)."""
+    pass
+
+def files_for_oracle(w, prep):
+    """.ri / tags bytes of the workload, for the CPU legs (the reference's own loaders read these)."""
+    if getattr(w, "ri", None) is None:
+        t0 = time.time()
+        h = w.host_runs()
+        w.ri, info = prep.rindex_from_rlbwt(prep.rlbwt_from_runs(h["rl_sym"], h["rl_len"]), encoded=True, with_samples=False)
+        w.tags, _ = prep.tags_from_runs(h["tag_val"], h["tag_len"], 0); w.layout = 0
+        w.facts.update(ri_bytes=len(w.ri), tags_bytes=len(w.tags), files_for_cpu_legs_s=round(time.time() - t0, 1))
+    return w.ri, w.tags, w.layout
+
+def make_workload(args, dev_index, rank, world=1, dist=None, need_index=True):
+    """-> Workload(ix or None, reads (cuda uint8 [pool, n, L]), name, facts, host_runs()). Multi-GPU: rank 0 builds the
+    run-length BWT + tag runs ONCE per node and broadcasts them over NCCL (NVLink); every rank builds its own replica of the
+    index from the runs on its own GPU (pgi_index_create_from_runs)."""
     import torch
     from __graft_entry__ import load_package
-    pkg = load_package(); prep = pkg.prep
+    pkg = load_package(); prep = pkg.prep; capi = pkg.capi
     dev = torch.device("cuda", dev_index)
-    t0 = time.time()
-    pool = max(1, min(4, args.steps + args.warmup))
-    if args.workload == "xy":
-        gold = os.path.join(ROOT, "tests", "golden")
-        ri = open(os.path.join(gold, "xy.ri"), "rb").read(); tags = open(os.path.join(gold, "xy_bidirectional_compressed.tags"), "rb").read()
-        text = open(os.path.join(gold, "contigs_xy"), "rb").read()
+    w = Workload(); t0 = time.time()
+    pool = max(1, min(4, args.steps + args.warmup)); n = args.reads_per_step; L = args.read_len
+    if args.workload in ("xy", "x"):
+        import refcases, datasets
         from pangenome_index_b200 import synth
+        if args.workload == "xy":
+            w.ri = datasets.gold("xy.ri"); w.tags = datasets.gold("xy_bidirectional_compressed.tags"); w.layout = 1; text = datasets.gold("contigs_xy")
+            w.name = "configs[1]: shipped bidirectional_test xy.ri (legacy, n=8022, sigma=5) + xy_bidirectional_compressed.tags (ByteCode), reads with 1 % substitutions"
+        else:
+            x = refcases.x_index(); w.ri, w.tags, w.layout, text = x["ri"], x["tags"], 0, x["text"]
+            w.name = "configs[0]: index rebuilt from the shipped x.rl_bwt (encoded, n=3012, sigma=5, forward-only) + synthetic aligned tags, error-free reads"
         tt = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev)
         starts = np.concatenate([[0], np.nonzero(np.frombuffer(text, dtype=np.uint8) == 10)[0] + 1])
-        reads = torch.stack([synth.sample_reads(tt, starts, args.reads_per_step, args.read_len, args.sub, 2 + 97 * rank + 7 * i, dev) for i in range(pool)])
-        name = "configs[1]: shipped bidirectional_test xy.ri (legacy, n=8022, sigma=5) + xy_bidirectional_compressed.tags (ByteCode)"
-        return dict(ri=ri, tags=tags, layout=1, reads=reads, name=name, facts={"n": 8022})
-    from pangenome_index_b200 import synth
-    d = synth.build(args.ref_len, args.n_hap, seed=3, device=dev_index, log=log if rank == 0 else None)
-    reads = torch.stack([synth.sample_reads(d["text"], d["seq_starts"], args.reads_per_step, args.read_len, args.sub, 4 + 97 * rank + 7 * i, dev) for i in range(pool)])
-    del d["text"]; torch.cuda.empty_cache()
-    rl = prep.rlbwt_from_runs(d["rl_sym"], d["rl_len"])
-    ri, info = prep.rindex_from_rlbwt(rl, encoded=True, with_samples=False)
-    del rl
-    tags, n_tag_runs = prep.tags_from_runs(d["tag_val"], d["tag_len"], 0)
-    facts = {"n": int(d["n"]), "r": int(info["total_runs"]), "sequences": int(d["n_seq"]), "tag_runs": int(n_tag_runs),
-             "ri_bytes": len(ri), "tags_bytes": len(tags), "prep_s": round(time.time() - t0, 1)}
-    name = ("configs[2]-style synthetic pangenome: %d haplotypes x %.1f Mbp + reverse complements (nominal config: 64 x 50 Mbp; "
-            "built size stated in facts), SNP 1/1000, indel 1/10000, N stretches (sigma=6)" % (args.n_hap, args.ref_len / 1e6))
-    if rank == 0: log("workload ready:", facts)
-    return dict(ri=ri, tags=tags, layout=0, reads=reads, name=name, facts=facts)
+        w.reads = torch.stack([synth.sample_reads(tt, starts, n, L, args.sub, 2 + 97 * rank + 7 * i, dev) for i in range(pool)])
+        w.facts = {"n": len(text)}
+        w.ix = capi.Index(w.ri, w.tags, w.layout, device=dev_index) if need_index else None
+        w.index_create_s = 0.0
+        return w
+    from pangenome_index_b200 import pangraph as pg
+    lg = log if rank == 0 else None
+    prepared = pg.prepare(args.ref_len, args.n_hap, seed=3, device=dev_index, log=lg)      # every rank: the graph (reads are sampled from it)
+    g = prepared[0]
+    t1 = time.time()
+    if rank == 0:
+        d = pg.build(args.ref_len, args.n_hap, prepared=prepared, log=lg); runs = d["dev_runs"]; del d
+        meta = torch.tensor([len(runs["sym"]), len(runs["tag_val"])], dtype=torch.int64, device=dev)
+    else:
+        runs = None; meta = torch.zeros(2, dtype=torch.int64, device=dev)
+    bcast_s = 0.0
+    if world > 1:
+        dist.broadcast(meta, 0); torch.cuda.synchronize(); tb = time.time()
+        if rank != 0:
+            runs = dict(sym=torch.empty(int(meta[0]), dtype=torch.uint8, device=dev), len=torch.empty(int(meta[0]), dtype=torch.int64, device=dev),
+                        tag_val=torch.empty(int(meta[1]), dtype=torch.int64, device=dev), tag_len=torch.empty(int(meta[1]), dtype=torch.int64, device=dev))
+        for k in ("sym", "len", "tag_val", "tag_len"): dist.broadcast(runs[k], 0)
+        torch.cuda.synchronize(); bcast_s = time.time() - tb
+    build_s = time.time() - t1
+    w.host_runs = lambda: pg.host_runs(runs)
+    n_bwt = int(runs["len"].sum())
+    t2 = time.time()
+    w.ix = capi.Index.from_runs(runs["sym"], runs["len"], runs["tag_val"], runs["tag_len"], device=dev_index) if need_index else None
+    torch.cuda.synchronize(); w.index_create_s = time.time() - t2
+    w.reads = torch.stack([pg.sample_reads(prepared[1], n, L, args.sub, 4 + 97 * rank + 7 * i, indel=args.indel) for i in range(pool)])
+    w.runs = runs
+    w.facts = {"n": n_bwt, "r": int(len(runs["sym"])), "sequences": 2 * g.H, "haplotypes": g.H, "reference_bp": g.L, "sites": g.S, "tag_runs": int(len(runs["tag_val"])),
+               "graph_and_bwt_s": round(build_s - bcast_s, 1), "nccl_broadcast_of_runs_s": round(bcast_s, 2), "runs_broadcast_bytes": int(sum(v.numel() * v.element_size() for v in runs.values())) if world > 1 else 0,
+               "index_from_runs_on_gpu_s": round(w.index_create_s, 2), "prep_s": round(time.time() - t0, 1)}
+    w.name = WORKLOADS[args.workload][6] if args.nominal else ("%s at a NON-NOMINAL size: %d haplotypes x %.1f Mbp" % (args.workload, args.n_hap, args.ref_len / 1e6))
+    w.ri = None
+    if rank == 0: log("workload ready:", w.facts)
+    return w
 
-def cpu_oracle_rate(o, reads_np, L, min_len, min_occ, target_s, threads=0, count_work=True):
+def cpu_rate(o, R, reads_np, L, min_len, min_occ, target_s, threads=0):
+    """Time the CPU baseline on a bounded sample sized for about target_s seconds: the reference's own code (R, oracle/_ref)
+    when it is built, else the restatement (o). -> dict(reads, seconds, rate, kind)"""
     threads = threads or host_threads()
-    """Time the oracle (all host threads) on a bounded sample sized for about target_s seconds. -> dict"""
     n_avail = len(reads_np) // L
-    probe = min(n_avail, 20000)
-    off = np.arange(probe + 1, dtype=np.uint64) * np.uint64(L)
-    dt = max(1e-6, o.find_mems(reads_np[: probe * L], off, min_len, min_occ, threads=threads, text=False)["seconds"])
+    def run(n):
+        off = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
+        if R is not None: return R.ref_time(reads_np[: n * L], off, min_len, min_occ, threads=threads)[0]
+        return o.find_mems(reads_np[: n * L], off, min_len, min_occ, threads=threads, text=False)["seconds"]
+    probe = min(n_avail, max(64, 3_000_000 // L))
+    dt = max(1e-6, run(probe))
     n = int(min(n_avail, max(probe, probe * target_s / dt)))
-    off = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
-    R = o.find_mems(reads_np[: n * L], off, min_len, min_occ, threads=threads, count_work=count_work, text=False); dt = R["seconds"]
-    return dict(reads=n, seconds=dt, rate=n / dt, result=R)
+    dt = run(n)
+    return dict(reads=n, seconds=dt, rate=n / dt, kind="reference" if R is not None else "port")
+
+def cpu_indexes(w, prep):
+    """(oracle restatement, reference library or None) over the workload's files."""
+    import orc
+    ri, tags, layout = files_for_oracle(w, prep)
+    o = orc.Index(ri, tags, layout)
+    R = None
+    try:
+        if orc.ref_available(): R = orc.Index(ri, tags, layout, impl="ref")
+    except Exception as e:
+        log("reference library not usable, falling back to the restatement:", e)
+    return o, R
 
 def run_reference(args, rank, world):
-    """--impl reference: the CPU restatement of the reference's find_mems (oracle/), all host threads, rank 0 only."""
+    """--impl reference: the reference's own find_mems code on the host cores (oracle/_ref/libpgiref.so = src/r-index.cpp +
+    src/tag_arrays.cpp + find_all_mems compiled against stand-in SDSL headers; OpenMP over reads is ours -- the reference's
+    loop is serial), or the restatement in oracle/ when that library is not built. Rank 0 only."""
     if rank != 0:
         return
-    import torch, orc
-    w = make_workload(args, 0, 0)
-    o = orc.Index(w["ri"], w["tags"], w["layout"])
+    import torch
+    from __graft_entry__ import load_package
+    prep = load_package().prep
+    w = make_workload(args, 0, 0, need_index=False)
+    o, R = cpu_indexes(w, prep)
     L = args.read_len
-    reads_np = w["reads"][0].reshape(-1).cpu().numpy()
+    reads_np = w.reads[0].reshape(-1).cpu().numpy()
     cores = host_threads()
     per_step_s = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
-    probe = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, per_step_s, count_work=False)
+    probe = cpu_rate(o, R, reads_np, L, args.min_len, args.min_occ, per_step_s)
     n = probe["reads"]; off = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
-    for _ in range(max(0, args.warmup - 1)):
-        o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores, text=False)
-    t = 0.0
-    for _ in range(args.steps):
-        t += o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores, text=False)["seconds"]
+    def step():
+        if R is not None: return R.ref_time(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores)[0]
+        return o.find_mems(reads_np[: n * L], off, args.min_len, args.min_occ, threads=cores, text=False)["seconds"]
+    for _ in range(max(0, args.warmup - 1)): step()
+    t = sum(step() for _ in range(args.steps))
     rate = n * args.steps / t
+    kind = probe["kind"]
     sample = "%d reads per step (bounded sample of the %d-read batch), %d OpenMP threads" % (n, args.reads_per_step, cores)
+    note = ("the reference's own code: src/r-index.cpp + src/tag_arrays.cpp compiled unmodified against stand-in SDSL / GBWT headers, find_all_mems + tag query per MEM "
+            "cut out by line range (oracle/Makefile); its find_mems loop is single-threaded, the OpenMP loop over reads is ours; stdout muted") if kind == "reference" else \
+           "oracle/_ref is not built on this machine: the CPU restatement in oracle/, parallelised over reads with OpenMP"
     line = {"impl": "reference", "metric": "find_mems reads/s (150bp, MEM + tag query)", "value": rate, "unit": "reads/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": w["name"], "facts": w["facts"], "reads_per_step": n, "read_len": L, "min_len": args.min_len, "min_occ": args.min_occ,
-                       "note": "the reference's own find_mems is single-threaded and cannot be built here (SDSL/GBWT absent): this is the CPU restatement in oracle/, parallelised over reads with OpenMP"},
-            "cpu_baseline": {"value": rate, "unit": "reads/s", "cores": cores, "kind": "port", "sample": sample},
+            "config": {"workload": w.name, "facts": w.facts, "reads_per_step": n, "read_len": L, "min_len": args.min_len, "min_occ": args.min_occ, "note": note},
+            "cpu_baseline": {"value": rate, "unit": "reads/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": rate, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit_json(line)
+
+def pin_rank_to_own_cores(local, world):
+    """One process per GPU on DISJOINT cores: the cores NVML names for this GPU (its NUMA node) are divided among the ranks
+    that share them, so that a rank's stream synchronisation never waits behind another rank's threads (SCALE_r01: all ranks
+    ran on cores 0-31 and one of them lost 25 % to a single 25 ms host hiccup). Returns the original affinity mask."""
+    orig = os.sched_getaffinity(0)
+    if world <= 1: return orig
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", ""); idx = local
+        if vis and all(x.strip().isdigit() for x in vis.split(",")): idx = int(vis.split(",")[local])
+        words = pynvml.nvmlDeviceGetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(idx), (os.cpu_count() + 63) // 64)
+        near = sorted(c for c in orig if (words[c // 64] >> (c % 64)) & 1) or sorted(orig)
+    except Exception as e:
+        log("NVML affinity unavailable:", e); near = sorted(orig)
+    # ranks sharing the same `near` set split it evenly (ranks are mapped to GPUs in order: neighbours share a node)
+    sharers = max(1, min(world, round(world * len(near) / max(1, len(orig)))))
+    per = max(1, len(near) // sharers); k = local % sharers
+    mine = near[k * per:(k + 1) * per] or near
+    try: os.sched_setaffinity(0, mine)
+    except Exception as e: log("cpu affinity not set:", e)
+    return orig
 
 def main():
     capture_stdout()
@@ -205,45 +305,32 @@ def main():
         return run_reference(args, rank, world)
     import torch, torch.distributed as dist
     from __graft_entry__ import load_package
-    capi = load_package().capi
+    pkg = load_package(); capi = pkg.capi; prep = pkg.prep
     if capi.lib().pgi_device_count() < 1:
         raise SystemExit("bench.py: no CUDA device; the find_mems path has no CPU fallback")
     torch.cuda.set_device(local)
-    # One process per GPU: run on the CPU cores next to this GPU (NVML's affinity mask), so that pinned staging buffers are
-    # allocated on the GPU's own NUMA node and stream synchronisations wake a near core (r01r, 8 GPUs: ranks 0-3 moved
-    # their results at 31 ms per step, ranks 4-7 at 22 ms). The CPU legs widen it again (host_threads).
-    orig_affinity = None
-    if world > 1:
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            orig_affinity = os.sched_getaffinity(0)
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES", ""); idx = local
-            if vis and all(x.strip().isdigit() for x in vis.split(",")): idx = int(vis.split(",")[local])
-            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(idx))
-            if not (os.sched_getaffinity(0) & orig_affinity): os.sched_setaffinity(0, orig_affinity)
-        except Exception as e:
-            log("cpu affinity not set:", e)
+    orig_affinity = pin_rank_to_own_cores(local, world)
+    my_cores = sorted(os.sched_getaffinity(0))
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     def barrier():
         if world > 1: dist.barrier()
         torch.cuda.synchronize()
-    w = make_workload(args, local, rank)
-    t0 = time.time()
-    ix = capi.Index(w["ri"], w["tags"], w["layout"], device=local)
-    index_create_s = time.time() - t0                       # parse + flatten on the host + upload: excluded from every timed region (SURVEY §8 d)
-    if rank == 0: log("index on device: %.1f MB in %.1fs" % (ix.info["device_bytes"] / 1e6, index_create_s), ix.info)
-    L = args.read_len; n = args.reads_per_step; pool = w["reads"].shape[0]
+    l2_fetch = capi.l2_fetch_granularity(local, int(os.environ.get("PGI_L2FETCH", 0)))
+    w = make_workload(args, local, rank, world, dist)
+    ix = w.ix
+    if rank == 0: log("index on device: %.1f MB in %.2fs" % (ix.info["device_bytes"] / 1e6, w.index_create_s), ix.info)
+    L = args.read_len; n = args.reads_per_step; pool = w.reads.shape[0]
     d_off = torch.arange(n + 1, dtype=torch.int64, device="cuda") * L
     stream = torch.cuda.current_stream()
     batch = capi.Batch(ix, stream=stream.cuda_stream)
     # pinned host copies of the read batches for the end-to-end leg
     h_reads = [torch.empty(n * L + 16, dtype=torch.uint8).pin_memory() for _ in range(pool)]
-    for i in range(pool): h_reads[i][: n * L].copy_(w["reads"][i].reshape(-1))
+    for i in range(pool): h_reads[i][: n * L].copy_(w.reads[i].reshape(-1))
     h_off = (torch.arange(n + 1, dtype=torch.int64) * L).pin_memory()
-    d_reads = [torch.cat([w["reads"][i].reshape(-1), torch.zeros(16, dtype=torch.uint8, device="cuda")]) for i in range(pool)]
+    d_reads = [torch.cat([w.reads[i].reshape(-1), torch.zeros(16, dtype=torch.uint8, device="cuda")]) for i in range(pool)]
+    del w.reads
     torch.cuda.synchronize()
 
     def step_device(i):
@@ -259,23 +346,26 @@ def main():
     # ---- device-resident timing (value)
     for i in range(args.warmup): step_device(i)
     sampler = ClockSampler(local, rank)
-    if not os.environ.get("PGI_BENCH_NOSAMPLER"): sampler.start()          # diagnostic switch (tools/placement_probe.py)
+    if not os.environ.get("PGI_BENCH_NOSAMPLER"): sampler.start()
     barrier()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0; seed_total = 0
+    k1_ms = 0.0; stage = np.zeros(8); ext_total = 0; launches = 0; mems_total = 0; tags_total = 0; seed_total = 0; blk_total = 0; reruns = 0
     e0.record(stream); host_gap = []; t_prev = time.perf_counter()
     for i in range(args.steps):
         step_device(args.warmup + i)
         t_now = time.perf_counter(); host_gap.append(1e3 * (t_now - t_prev)); t_prev = t_now      # host wall time of the step (diagnostic)
-        ms = batch.stage_ms(); stage += np.array(ms); k1_ms += ms[0]; launches += int(ms[6]) + 0
-        r = batch.device_result(); ext_total += r.extensions; mems_total += r.n_mems; tags_total += r.n_tags; seed_total += r.seed_lookups
+        ms = batch.stage_ms(); stage += np.array(ms); k1_ms += ms[0]; launches += int(ms[6]); reruns += int(ms[7])
+        r = batch.device_result(); ext_total += r.extensions; mems_total += r.n_mems; tags_total += r.n_tags; seed_total += r.seed_lookups; blk_total += r.blocks_fetched
     e1.record(stream)
     barrier()
     dev_ms = e0.elapsed_time(e1)
+    if args.device_only:
+        log("device-only run: %.3f ms per step, fmd_mem_kernel %.3f ms, L2 fetch granularity %d B, K1 variant %s" % (dev_ms / args.steps, k1_ms / args.steps, l2_fetch, os.environ.get("PGI_K1", "default")))
+        sampler.stop_flag = True
+        return
     # ---- end-to-end timing: K calls of pgi_find_mems (pinned host buffers in, all result arrays out to pinned host memory),
     # issued by E2E_CALLERS host threads the way the batched find_mems driver does, so the copies of one call overlap the
     # kernels of another. Wall clock around all K calls (every call blocks until its result is in host memory).
-    import threading
     def e2e_pass(k_calls, first):
         nxt = [first]; lock = threading.Lock(); acc = [0]
         def caller():
@@ -298,111 +388,133 @@ def main():
     # ---- max over ranks
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([launches, ext_total, mems_total, tags_total], dtype=torch.float64, device="cuda")
-    per_rank = [[dev_ms / args.steps, e2e_ms / args.steps, max(host_gap)]]
+    per_rank = [[dev_ms / args.steps, e2e_ms / args.steps, max(host_gap), k1_ms / args.steps]]
     if world > 1:
         mine = torch.tensor(per_rank[0], dtype=torch.float64, device="cuda"); allr = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine); per_rank = [[round(float(x), 3) for x in r] for r in allr]
         dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     dev_ms, e2e_ms = float(t[0]), float(t[1])
-    if rank == 0: log("per rank [device ms/step, e2e ms/step, slowest host step ms]:", per_rank, "rank 0 host ms per step:", [round(x, 2) for x in host_gap])
+    if rank == 0: log("per rank [device ms/step, e2e ms/step, slowest host step ms, K1 ms]:", per_rank, "rank 0 host ms per step:", [round(x, 2) for x in host_gap], "cores of rank 0:", my_cores)
     if rank != 0:
         if world > 1: dist.destroy_process_group()
         return
     total_reads = n * args.steps * world
     value = total_reads / (dev_ms * 1e-3); e2e = total_reads / (e2e_ms * 1e-3)
-    # ---- CPU oracle: parity on a sample + work counters + cpu_baseline (rank 0, not timed against the GPU)
-    if orig_affinity:
-        try: os.sched_setaffinity(0, orig_affinity)          # the CPU legs use every host core again
-        except Exception: pass
-    import orc
-    o = orc.Index(w["ri"], w["tags"], w["layout"])
+    try: os.sched_setaffinity(0, orig_affinity)          # the CPU legs use every host core again
+    except Exception: pass
+    # ---- CPU side (rank 0, never inside a timed region): the files the reference's loaders read, the restatement, the reference library
+    o, R = cpu_indexes(w, prep)
     reads_np = h_reads[0][: n * L].numpy()
-    ns = min(n, 20000); offs = np.arange(ns + 1, dtype=np.uint64) * np.uint64(L)
-    R = o.find_mems(reads_np[: ns * L], offs, args.min_len, args.min_occ, count_work=True, text=False)
-    G = ix.find_mems(reads_np[: ns * L], offs, args.min_len, args.min_occ, text=False)
-    parity = bool(G["n_mems"] == R["n_mems"] and np.array_equal(G["mems"], R["mems"]) and np.array_equal(G["tags"], R["tags"])
-                  and np.array_equal(G["n_runs"], R["n_runs"]) and G["extensions"] == R["counters"]["E"])
-    # ---- next row of the scope table, reported beside the headline, not part of it: the query_tags path
-    # (whole-read count_encoded + tag query of the final range) on the same reads, device-resident, with its own parity check
-    next_rows = {}
-    try:
-        qs = []
-        for i in range(2 + 3):
-            batch.set_device_reads(d_reads[i % pool].data_ptr(), d_off.data_ptr(), n, n * L)
-            batch.run_query_tags()
-            if i >= 2: qs.append((batch.stage_ms()[5], batch.device_result().extensions))
-        QG = ix.query_tags(reads_np[: ns * L], offs, text=False); QR = o.query_tags(reads_np[: ns * L], offs, text=False, threads=host_threads())
-        q_par = bool(np.array_equal(QG["mems"], QR["mems"]) and np.array_equal(QG["tags"], QR["tags"]) and np.array_equal(QG["n_runs"], QR["n_runs"]))
-        q_ms = float(np.median([x[0] for x in qs]))
-        next_rows["query_tags"] = {"reads_per_s": n / (q_ms * 1e-3), "ms_per_step": q_ms, "lf_steps_per_read": qs[-1][1] / n,
-                                   "matched_fraction": float((QR["mems"][:, 3] > 0).mean()), "parity_sample": "%d reads bit-exact vs oracle: %s" % (ns, q_par),
-                                   "cpu_port_reads_per_s": ns / QR["seconds"], "note": "150 bp reads with 1 % errors searched whole (right to left until the range is empty)"}
-    except Exception as e:
-        next_rows["query_tags"] = {"error": str(e)}
-    # ---- text formatting (src/find_mems.cpp:115-139 stdout grammar): host-bound, reported separately (SURVEY §8 d)
-    fmt = {}
-    try:
-        import ctypes
-        r = ix.find_mems_raw(h_reads[0].data_ptr(), h_off.data_ptr(), n, args.min_len, args.min_occ)
-        ln = ctypes.c_uint64(); t1 = time.perf_counter()
-        ptxt = capi.lib().pgi_format_text(ctypes.byref(r), 1, 1, ctypes.byref(ln)); t_fmt = time.perf_counter() - t1
-        capi.lib().pgi_free(ptxt); ix.result_free(r)
-        fmt = {"reads_per_s": n / t_fmt, "text_bytes_per_step": int(ln.value), "threads": 1, "note": "pgi_format_text, one host thread; not inside value / e2e"}
-    except Exception as e:
-        fmt = {"error": str(e)}
-    c = R["counters"]; d_per_e = c["D"] / max(1, c["E"])
-    cpu = cpu_oracle_rate(o, reads_np, L, args.min_len, args.min_occ, args.cpu_seconds, count_work=False)
+    # parity of a FULL timed batch: the same batch object and the same 2 M-read device batch as the timed steps (partitioned
+    # MEM slots and all); its first `ns` reads are compared with the oracle array by array, the whole result is summarised.
+    ns = min(n, max(2000, min(200_000, 30_000_000 // L))); offs = np.arange(ns + 1, dtype=np.uint64) * np.uint64(L)
+    batch.set_device_reads(d_reads[0].data_ptr(), d_off.data_ptr(), n, n * L); batch.run(args.min_len, args.min_occ)
+    G = batch.fetch(text=False)
+    Ro = o.find_mems(reads_np[: ns * L], offs, args.min_len, args.min_occ, count_work=True, text=False)
+    m1 = int(G["mem_off"][ns]); t1 = int(G["tag_off"][m1])
+    parity = bool(m1 == Ro["n_mems"] and np.array_equal(G["mem_off"][: ns + 1], Ro["mem_off"]) and np.array_equal(G["mems"][:m1], Ro["mems"])
+                  and np.array_equal(G["tag_off"][: m1 + 1], Ro["tag_off"]) and np.array_equal(G["tags"][:t1], Ro["tags"]) and np.array_equal(G["n_runs"][:m1], Ro["n_runs"]))
+    parity_ref = None
+    if R is not None:                                       # and a slice against the reference's own code
+        nr = min(ns, 20000); Rr = R.find_mems(reads_np[: nr * L], offs[: nr + 1], args.min_len, args.min_occ, text=False, threads=host_threads())
+        mr = int(G["mem_off"][nr]); tr = int(G["tag_off"][mr])
+        parity_ref = bool(np.array_equal(G["mems"][:mr], Rr["mems"]) and np.array_equal(G["tags"][:tr], Rr["tags"]) and np.array_equal(G["n_runs"][:mr], Rr["n_runs"]))
+    small = ix.find_mems(reads_np[: 2000 * L] if n >= 2000 else reads_np, offs[: min(n, 2000) + 1], args.min_len, args.min_occ, text=False)   # small batches take the single-counter path
+    parity_small = bool(np.array_equal(small["mems"], G["mems"][: small["n_mems"]]))
+    wide = {"max_bwt_start": int(G["mems"][:, 2].max()) if G["n_mems"] else 0, "mems_beyond_2^32": int((G["mems"][:, 2] >= (1 << 32)).sum())}
+    import hashlib
+    batch_digest = hashlib.sha256(G["mems"].tobytes() + G["tags"].tobytes() + G["n_runs"].tobytes()).hexdigest()[:16]
+    # ---- next rows of the scope table (SURVEY.md section 8 f), reported beside the headline, not part of it
+    next_rows = {}; fmt = {}; rnd = {}
+    if not args.no_extras:
+        try:
+            qs = []
+            for i in range(2 + 3):
+                batch.set_device_reads(d_reads[i % pool].data_ptr(), d_off.data_ptr(), n, n * L)
+                batch.run_query_tags()
+                if i >= 2: qs.append((batch.stage_ms()[5], batch.device_result().extensions))
+            nq = min(ns, 20000)
+            QG = ix.query_tags(reads_np[: nq * L], offs[: nq + 1], text=False); QR = o.query_tags(reads_np[: nq * L], offs[: nq + 1], text=False, threads=host_threads())
+            q_par = bool(np.array_equal(QG["mems"], QR["mems"]) and np.array_equal(QG["tags"], QR["tags"]) and np.array_equal(QG["n_runs"], QR["n_runs"]))
+            q_ms = float(np.median([x[0] for x in qs]))
+            next_rows["query_tags"] = {"reads_per_s": n / (q_ms * 1e-3), "ms_per_step": q_ms, "lf_steps_per_read": qs[-1][1] / n,
+                                       "matched_fraction": float((QR["mems"][:, 3] > 0).mean()), "parity_sample": "%d reads bit-exact vs oracle: %s" % (nq, q_par),
+                                       "cpu_port_reads_per_s": nq / QR["seconds"], "note": "reads searched whole (right to left until the range is empty)"}
+        except Exception as e:
+            next_rows["query_tags"] = {"error": str(e)}
+        # text formatting (src/find_mems.cpp:115-139 stdout grammar): host-bound, reported separately (SURVEY section 8 d)
+        try:
+            import ctypes
+            r = ix.find_mems_raw(h_reads[0].data_ptr(), h_off.data_ptr(), n, args.min_len, args.min_occ)
+            ln = ctypes.c_uint64(); t1_ = time.perf_counter()
+            ptxt = capi.lib().pgi_format_text(ctypes.byref(r), 1, 1, ctypes.byref(ln)); t_fmt = time.perf_counter() - t1_
+            capi.lib().pgi_free(ptxt); ix.result_free(r)
+            fmt = {"reads_per_s": n / t_fmt, "text_bytes_per_step": int(ln.value), "threads": host_threads(), "note": "pgi_format_text (read ranges formatted in parallel); not inside value / e2e"}
+        except Exception as e:
+            fmt = {"error": str(e)}
+        # M1: random-access figures over a buffer of the size of the run-block array (capped), for the record
+        try:
+            foot = int(min(max(ix.info["n_dev_blocks"] * 64, 1 << 30), 24 << 30))
+            for b in (32, 64):
+                rnd["random%d_ceiling_gbs" % b] = round(capi.random_access_gbs(local, foot, b, 1 << 28, 0), 1)
+            rnd["random64_chained8_gbs"] = round(capi.random_access_gbs(local, foot, 64, 1 << 26, 8), 1)
+            rnd["footprint_bytes"] = foot
+        except Exception as e:
+            rnd["error"] = str(e)
+    c = Ro["counters"]; d_per_e = c["D"] / max(1, c["E"])
+    cpu = cpu_rate(o, R, reads_np, L, args.min_len, args.min_occ, args.cpu_seconds)
     cores = host_threads()
-    # ---- roofline of the dominant kernel (fmd_mem_kernel): algorithmic bytes = 128 B x D
+    # ---- roofline of the dominant kernel (fmd_mem_kernel)
     peaks = {}
     try: peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception: pass
-    peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s"
-    ext_rank0 = ext_total
-    k1_bytes_per_launch = 128.0 * d_per_e * ext_rank0 / args.steps
+    peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
     k1_s = (k1_ms / args.steps) * 1e-3
-    achieved = k1_bytes_per_launch / k1_s / 1e9
-    # DRAM traffic of the same kernel on the same default workload, from the committed ncu --set full capture (per launch)
+    # (a) what the kernel MOVES, counted by the kernel itself: 64 B per run block fetched + 16 B per seed lookup + the read
+    # bytes and their 2-bit codes + 48 B per MEM appended (32 B record, 8 B key, 8 B per-read count share)
+    blk = blk_total / args.steps; seeds = seed_total / args.steps; mems_step = mems_total / args.steps
+    moved = 64.0 * blk + 16.0 * seeds + n * L * 1.25 + 48.0 * mems_step
+    achieved = moved / k1_s / 1e9
+    # (b) the REFERENCE algorithm's bytes for the same answers (SURVEY.md section 8 d): 128 B per distinct 10-run block per extension
+    equiv = 128.0 * d_per_e * (ext_total / args.steps)
     traffic = None; traffic_src = None
-    if args.workload == "synth" and args.ref_len == 50_000_000 and args.n_hap == 20 and n == 2_000_000 and L == 150:
-        try:
-            import glob, re
-            f = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_fmd_mem_kernel_raw.txt")))[-1]
-            vals = {}
-            for ln in open(f):
-                m = re.match(r"(dram__bytes_(?:read|write)\.sum)\s+(\S+)\s+(\S+)", ln)
-                if m: vals[m.group(1)] = float(m.group(3)) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[m.group(2)]
-            traffic = vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"]; traffic_src = os.path.relpath(f, ROOT)
-        except Exception:
-            pass
-    rnd = {}
-    try:
-        for b in (32, 64):
-            rnd["random%d_gbs" % b] = round(capi.random_access_gbs(local, 8 << 30, b, 1 << 27, 8), 1)
-    except Exception as e:
-        rnd["error"] = str(e)
+    try:                                                    # ncu dram bytes per launch, only from a capture of THIS kernel build on THIS workload
+        import hashlib as _h
+        hh = _h.sha256()
+        for f in sorted(os.listdir(os.path.join(ROOT, "pangenome-index_b200", "csrc"))):
+            if f.endswith((".cuh", ".cu", ".h", ".hpp")): hh.update(open(os.path.join(ROOT, "pangenome-index_b200", "csrc", f), "rb").read())
+        tj = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
+        for e in tj:
+            if e["csrc_sha256"] == hh.hexdigest() and e["workload"] == args.workload and e["nominal"] == args.nominal and e["reads_per_step"] == n:
+                traffic = e["dram_bytes_per_launch"]; traffic_src = e["source"]
+    except Exception:
+        pass
     line = {"metric": "find_mems reads/s (150bp, MEM + tag query)", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int64", "data": "synthetic",
-            "config": {"workload": w["name"], "facts": w["facts"], "reads_per_step_per_gpu": n, "read_len": L, "substitution_rate": args.sub,
-                       "min_len": args.min_len, "min_occ": args.min_occ, "index": "replicated per GPU", "device_index_bytes": ix.info["device_bytes"], "seed_k": ix.info["seed_k"],
-                       "l2_policy": "read batch (%.0f MB) and index are cycled over %d distinct batches; inputs larger than L2" % (n * L / 1e6, pool),
-                       "parity_sample": "%d reads bit-exact vs oracle: %s" % (ns, parity),
+            "config": {"workload": w.name, "workload_key": args.workload, "facts": w.facts, "reads_per_step_per_gpu": n, "read_len": L, "substitution_rate": args.sub, "indel_rate": args.indel,
+                       "min_len": args.min_len, "min_occ": args.min_occ, "index": "built once per node on rank 0's GPU, run arrays broadcast over NCCL, replica constructed on every GPU from the runs",
+                       "l2_fetch_granularity_bytes": l2_fetch, "device_index_bytes": ix.info["device_bytes"], "bucket_shift": ix.info["bucket_shift"], "seed_k": ix.info["seed_k"],
+                       "l2_policy": "read batch (%.0f MB) and a %.1f GB index, cycled over %d distinct batches; inputs larger than L2" % (n * L / 1e6, ix.info["device_bytes"] / 1e9, pool),
+                       "parity_full_batch": "first %d reads of a timed-path %d-read batch bit-exact vs oracle (MEMs, offsets, tags, n_runs): %s" % (ns, n, parity),
+                       "parity_vs_reference_code": parity_ref, "parity_small_batch_path": parity_small, "batch_digest": batch_digest, "positions_beyond_32_bits": wide,
                        "mems_per_read": float(cnt[2]) / total_reads, "tags_per_read": float(cnt[3]) / total_reads,
-                       "extensions_per_read": float(cnt[1]) / total_reads},
+                       "extensions_per_read": float(cnt[1]) / total_reads, "step_reruns": reruns},
             "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": n * L + (n + 1) * 8, "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e2e_ms / args.steps, "concurrent_callers": E2E_CALLERS},
             "gpu_launches": int(cnt[0]),
-            "per_rank_ms_per_step": {"device": [r[0] for r in per_rank], "e2e": [r[1] for r in per_rank]},
+            "per_rank_ms_per_step": {"device": [r[0] for r in per_rank], "e2e": [r[1] for r in per_rank], "slowest_host_step": [r[2] for r in per_rank], "fmd_mem_kernel": [r[3] for r in per_rank]},
             "stage_ms_per_step": {k: round(float(v) / args.steps, 3) for k, v in zip(["fmd_mem_kernel", "mem_order", "tag_plan", "tag_decode_sort", "tag_unique_compact", "run_total"], stage[:6])},
             "roofline": {"bound": "hbm", "kernel": "fmd_mem_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": k1_bytes_per_launch,
-                         "seed_lookups_per_launch": seed_total // args.steps, "executed_extensions_per_launch": (ext_rank0 - seed_total * ix.info["seed_k"]) // args.steps,
+                         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": moved,
+                         "bytes_model": "bytes the kernel moves, counted by the kernel: 64 B x %d run blocks fetched + 16 B x %d seed lookups + 1.25 B x %d read bytes (+ 2-bit codes) + 48 B x %d MEMs" % (blk, seeds, n * L, mems_step),
+                         "blocks_fetched_per_launch": blk, "seed_lookups_per_launch": seeds, "executed_extensions_per_launch": (ext_total - seed_total * ix.info["seed_k"]) / args.steps,
+                         "reference_algorithm_equivalent": {"bytes_per_launch": equiv, "gbs": equiv / k1_s / 1e9, "over_peak": equiv / k1_s / 1e9 / peak,
+                                                            "model": "SURVEY.md 8(d): 128 B x D (oracle: D/E = %.3f) x E = %d extensions of the reference algorithm per launch; NOT a bandwidth: the seed table answers %d of them from 16-byte entries and the layout moves 64 B where the reference moves 128 B" % (d_per_e, ext_total // args.steps, int(seeds * ix.info["seed_k"]))},
                          "traffic_gbs": (traffic / k1_s / 1e9) if traffic else None, "frac_traffic": (traffic / k1_s / 1e9 / peak) if traffic else None,
-                         "bytes_model": "128 B x D, D = distinct reference 10-run blocks touched per extension (oracle: D/E = %.3f) x E = %d extensions per launch (the reference algorithm's count = the oracle's E; with seed_k > 0 the first seed_k extensions of a walk from the full interval are ONE 16-byte table lookup, so the kernel moves fewer bytes than the algorithm names and frac may exceed 1)" % (d_per_e, ext_rank0 // args.steps),
                          "kernel_ms_per_launch": k1_ms / args.steps, **rnd},
-            "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": "port",
-                             "sample": "%d reads of the same batch in %.1f s, %d OpenMP threads (oracle/ restatement; the reference itself is single-threaded)" % (cpu["reads"], cpu["seconds"], cores)},
-            "index_create_s": round(index_create_s, 2), "text_format": fmt,
+            "cpu_baseline": {"value": cpu["rate"], "unit": "reads/s", "cores": cores, "kind": cpu["kind"],
+                             "sample": "%d reads of the same batch in %.1f s, %d OpenMP threads (%s; the reference's own loop is single-threaded)" % (cpu["reads"], cpu["seconds"], cores, "the reference's own code, oracle/_ref" if cpu["kind"] == "reference" else "oracle/ restatement")},
+            "index_create_s": round(w.index_create_s, 2), "text_format": fmt,
             "next_rows": next_rows,
             "clocks": sampler.summary()}
     emit_json(line)

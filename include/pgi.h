@@ -59,6 +59,7 @@ typedef struct {
     uint64_t *n_runs;    /* n_mems      : the reference's number_of_runs out-parameter                  */
     uint64_t extensions; /* FMD extensions of the reference algorithm (work counter; equals the oracle's E) */
     uint64_t seed_lookups; /* seed-table lookups; each stood for seed_k of those extensions (pgi_index_info_t) */
+    uint64_t blocks_fetched; /* 64-byte run blocks the MEM kernel fetched from the index (work counter: the bytes it really moves) */
     void *owner;         /* internal */
 } pgi_result;
 
@@ -234,7 +235,14 @@ void pgi_free(void *);
 /* M1 microbenchmark: independent random `bytes_per_access`-byte (32, 64 or 128) gathers
  * over a buffer of buf_bytes on `device`; returns GB/s of useful bytes in *gbs. The random-access roofline. */
 int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t bytes_per_access, uint64_t n_access,
-                          int chain /* dependent chain length per thread, >= 1 */, double *gbs);
+                          int chain /* >= 2: dependent chain of that length per thread; 1: four independent loads in flight per
+                                       thread; 0: the CEILING -- teams of bytes_per_access / 16 lanes per slot, eight independent
+                                       slots in flight per lane, full occupancy (the MEM kernel's fetch pattern, no arithmetic) */,
+                          double *gbs);
+
+/* cudaLimitMaxL2FetchGranularity of `device` (bytes fetched from DRAM around a missing 32-byte sector: 32, 64 or 128).
+ * set_bytes != 0 sets it first; *current receives the value in effect. A device-wide setting of the calling process. */
+int pgi_l2_fetch_granularity(int device, int set_bytes, int *current);
 
 #ifdef __cplusplus
 }

@@ -11,12 +11,12 @@ SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
            "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
-           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs"]
+           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs", "pgi_l2_fetch_granularity"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
                 ("mem_off", ctypes.c_void_p), ("mems", ctypes.c_void_p), ("tag_off", ctypes.c_void_p),
-                ("tags", ctypes.c_void_p), ("n_runs", ctypes.c_void_p), ("extensions", ctypes.c_uint64), ("seed_lookups", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
+                ("tags", ctypes.c_void_p), ("n_runs", ctypes.c_void_p), ("extensions", ctypes.c_uint64), ("seed_lookups", ctypes.c_uint64), ("blocks_fetched", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
 
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
@@ -94,7 +94,7 @@ def _arr(ptr, n, dtype=np.uint64):
     return np.frombuffer(buf, dtype=dtype).copy()
 
 def _result_to_dict(res, L, with_tags, text=True):
-    out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags, extensions=res.extensions, seed_lookups=res.seed_lookups,
+    out = dict(n_reads=res.n_reads, n_mems=res.n_mems, n_tags=res.n_tags, extensions=res.extensions, seed_lookups=res.seed_lookups, blocks_fetched=res.blocks_fetched,
                mem_off=_arr(res.mem_off, res.n_reads + 1 if res.mem_off else 0),
                mems=_arr(res.mems, 4 * res.n_mems if res.mems else 0).reshape(-1, 4),
                tag_off=_arr(res.tag_off, res.n_mems + 1), tags=_arr(res.tags, res.n_tags), n_runs=_arr(res.n_runs, res.n_mems))
@@ -250,3 +250,6 @@ class Batch:
 def random_access_gbs(device=0, buf_bytes=8 << 30, bytes_per_access=32, n_access=1 << 28, chain=8):
     g = ctypes.c_double(); _ck(lib().pgi_random_access_gbs(device, buf_bytes, bytes_per_access, n_access, chain, ctypes.byref(g)))
     return g.value
+
+def l2_fetch_granularity(device=0, set_bytes=0):
+    v = ctypes.c_int(); _ck(lib().pgi_l2_fetch_granularity(device, set_bytes, ctypes.byref(v))); return v.value

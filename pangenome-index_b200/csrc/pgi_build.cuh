@@ -52,13 +52,36 @@ __device__ __forceinline__ uint32_t bucket_last_run(const uint32_t *frun, const 
     const uint32_t f = frun[b + 1];
     return starts[f] == ((b + 1) << s) ? f - 1 : f;
 }
-__global__ void count_entries_kernel(const uint32_t *frun, const uint64_t *starts, uint64_t nb, unsigned s, uint64_t n_runs, uint64_t n, uint32_t *n_chunks, unsigned long long *n_crowded) {
+// End offset (relative to the bucket, clipped to it) of run i.
+__device__ __forceinline__ uint32_t clipped_end(const uint64_t *starts, const uint64_t *len, uint32_t i, uint64_t lo, uint64_t hi) {
+    const uint64_t e = starts[i] + len[i]; return (uint32_t) ((e < hi ? e : hi) - lo);
+}
+// Crowded bucket: the largest sub_shift for which every sub-bucket of 2^sub_shift positions holds at most PGI_CHUNK_RUNS
+// clipped runs (pgi_flatten.hpp choose_sub_shift).
+__device__ unsigned choose_sub_shift_dev(const uint64_t *starts, const uint64_t *len, uint32_t first, uint32_t cnt, uint64_t lo, unsigned S) {
+    const uint64_t hi = lo + (1ull << S);
+    for (unsigned ss = S - 1;; --ss) {
+        bool ok = true; uint32_t i = 0; const uint32_t n_sub = 1u << (S - ss);
+        for (uint32_t c = 0; c < n_sub && ok; ++c) {
+            const uint32_t hc = (c + 1) << ss; unsigned k = 0;
+            while (i < cnt) { ++k; const uint32_t e = clipped_end(starts, len, first + i, lo, hi); if (e > hc) break; ++i; if (e == hc) break; }
+            ok = k <= PGI_CHUNK_RUNS;
+        }
+        if (ok || ss == 0) return ss;
+    }
+}
+// n_chunks == nullptr: only count the crowded buckets (bucket-shift selection). Otherwise n_chunks[b] = chunk blocks of
+// bucket b (0 for a normal one) and sub_shift[b] its sub-bucket shift.
+__global__ void count_entries_kernel(const uint32_t *frun, const uint64_t *starts, const uint64_t *len, uint64_t nb, unsigned s, uint64_t n_runs, uint64_t n,
+                                     uint32_t *n_chunks, uint8_t *sub_shift, unsigned long long *n_crowded) {
     const uint64_t b = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
     if (b >= nb) return;
-    const uint32_t cnt = bucket_last_run(frun, starts, b, nb, s, n_runs, n) - frun[b] + 1;
-    uint32_t nc = 0;
-    if (cnt > PGI_RUNS_PER_BLOCK) { nc = 1 + (cnt - PGI_RUNS_PER_BLOCK + PGI_RUNS_PER_BLOCK - 2) / (PGI_RUNS_PER_BLOCK - 1); atomicAdd(n_crowded, 1ull); }
-    if (n_chunks) n_chunks[b] = nc;
+    const uint32_t first = frun[b], cnt = bucket_last_run(frun, starts, b, nb, s, n_runs, n) - first + 1;
+    if (cnt <= PGI_RUNS_PER_BLOCK) { if (n_chunks) { n_chunks[b] = 0; sub_shift[b] = 0; } return; }
+    atomicAdd(n_crowded, 1ull);
+    if (!n_chunks) return;
+    const unsigned ss = choose_sub_shift_dev(starts, len, first, cnt, b << s, s);
+    n_chunks[b] = 1u << (s - ss); sub_shift[b] = (uint8_t) ss;
 }
 
 // One 64-byte block from up to 12 entries (pgi_flatten.hpp write_block). cum[c] goes into the header as 32-bit partial
@@ -76,7 +99,7 @@ __device__ __forceinline__ void put_block(uint32_t *w, const uint32_t cum[6], co
 }
 
 __global__ void bucket_kernel(const uint32_t *frun, const uint64_t *starts, const uint64_t *len, const uint8_t *code, uint64_t nb, unsigned s, uint64_t n_runs, uint64_t n,
-                              const uint32_t *n_chunks, const uint64_t *chunk_base, uint32_t *blocks) {
+                              const uint32_t *n_chunks, const uint8_t *sub_shift, const uint64_t *chunk_base, uint32_t *blocks) {
     const uint64_t b = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
     if (b >= nb) return;
     const uint64_t lo = b << s, hi = lo + (1ull << s);
@@ -84,28 +107,31 @@ __global__ void bucket_kernel(const uint32_t *frun, const uint64_t *starts, cons
     const uint32_t cnt = last - first + 1;
     uint32_t tot[6] = {0, 0, 0, 0, 0, 0};
     uint32_t *dst = blocks + b * PGI_BLOCK_U32;
-    auto end_of = [&](uint32_t i) -> uint32_t { const uint64_t e = starts[i] + len[i]; return (uint32_t) ((e < hi ? e : hi) - lo); };
     if (cnt <= PGI_RUNS_PER_BLOCK) {
         uint32_t c[PGI_RUNS_PER_BLOCK], e[PGI_RUNS_PER_BLOCK]; uint32_t prev = 0;
-        for (uint32_t i = 0; i < cnt; ++i) { c[i] = code[first + i]; e[i] = end_of(first + i); tot[c[i]] += e[i] - prev; prev = e[i]; }
+        for (uint32_t i = 0; i < cnt; ++i) { c[i] = code[first + i]; e[i] = clipped_end(starts, len, first + i, lo, hi); tot[c[i]] += e[i] - prev; prev = e[i]; }
         put_block(dst, tot, c, e, cnt, 0u);
         return;
     }
-    // crowded bucket: directory block + chunk blocks (chunk 0: 12 runs; later chunks: pad entry + 11 runs)
+    // crowded bucket: directory block + one chunk block per sub-bucket (pad entry + at most 11 runs; pgi_flatten.hpp build_buckets)
+    const unsigned ss = sub_shift[b]; const uint32_t n_sub = 1u << (s - ss);
     const uint64_t base = nb + chunk_base[b];
-    uint8_t bounds[PGI_DIR_BOUNDS]; for (int i = 0; i < PGI_DIR_BOUNDS; ++i) bounds[i] = 0;
-    uint32_t nchunks = 0, i = 0, prev_end = 0;
-    while (i < cnt) {
+    uint32_t i = 0, at = 0;
+    for (uint32_t c = 0; c < n_sub; ++c) {
+        const uint32_t lo_c = c << ss, hi_c = (c + 1) << ss;
         uint32_t cc[PGI_RUNS_PER_BLOCK], ce[PGI_RUNS_PER_BLOCK]; unsigned k = 0;
         uint32_t before[6]; for (int q = 0; q < 6; ++q) before[q] = tot[q];
-        if (nchunks) { bounds[nchunks - 1] = (uint8_t) prev_end; cc[0] = PGI_CODE_UNUSED; ce[0] = prev_end; k = 1; }
-        for (; k < PGI_RUNS_PER_BLOCK && i < cnt; ++k, ++i) { cc[k] = code[first + i]; ce[k] = end_of(first + i); tot[cc[k]] += ce[k] - prev_end; prev_end = ce[k]; }
-        put_block(blocks + (base + nchunks) * PGI_BLOCK_U32, before, cc, ce, k, 0u);
-        ++nchunks;
+        if (c) { cc[0] = PGI_CODE_UNUSED; ce[0] = lo_c; k = 1; }
+        while (i < cnt && at < hi_c && k < PGI_RUNS_PER_BLOCK) {
+            const uint32_t ei = clipped_end(starts, len, first + i, lo, hi), e = ei < hi_c ? ei : hi_c;
+            cc[k] = code[first + i]; ce[k] = e; ++k; tot[cc[k - 1]] += e - at; at = e;
+            if (ei <= hi_c) ++i;
+        }
+        put_block(blocks + (base + c) * PGI_BLOCK_U32, before, cc, ce, k, 0u);
     }
     put_block(dst, tot, nullptr, nullptr, 0, (uint32_t) base);
-    dst[8] &= 0xFFFFu; dst[9] = PGI_CODE_DIRBLOCK;
-    for (int j = 0; j < PGI_DIR_BOUNDS / 4; ++j) dst[10 + j] = (uint32_t) bounds[4 * j] | (uint32_t) bounds[4 * j + 1] << 8 | (uint32_t) bounds[4 * j + 2] << 16 | (uint32_t) bounds[4 * j + 3] << 24;
+    dst[8] &= 0xFFFFu; dst[9] = PGI_CODE_DIRBLOCK; dst[10] = ss;
+    for (int j = 11; j < PGI_BLOCK_U32; ++j) dst[j] = 0;
 }
 
 // In-bucket total of one header field, read straight out of the primary blocks (scan input).

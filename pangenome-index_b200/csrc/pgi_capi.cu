@@ -8,6 +8,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <sched.h>
+#include <thread>
 #include <string>
 #include <vector>
 #include "../../include/pgi.h"
@@ -355,7 +357,7 @@ extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *le
         unsigned S = PGI_MAX_BSHIFT; bool forced = false;
         if (const char *e = std::getenv("PGI_BSHIFT")) {
             S = (unsigned) std::atoi(e); forced = true;
-            if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 8]");
+            if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 12]");
         }
         unsigned long long *d_ctr = tmp.get<unsigned long long>(1);
         uint32_t *frun = nullptr; uint64_t nb = 0; unsigned long long n_crowded = 0;
@@ -368,21 +370,21 @@ extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *le
             thrust::upper_bound(pol, starts, starts + r, q, q + nb, frun);
             thrust::transform(pol, frun, frun + nb, frun, B::MinusOne());
             CK(cudaMemset(d_ctr, 0, 8));
-            B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, nb, S, r, n, nullptr, d_ctr);
+            B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, rlen, nb, S, r, n, nullptr, nullptr, d_ctr);
             CK(cudaGetLastError());
             CK(cudaMemcpy(&n_crowded, d_ctr, 8, cudaMemcpyDeviceToHost));
-            if (forced || S == PGI_MIN_BSHIFT || n_crowded <= ((n >> S) + 1) / 64) break;
+            if (forced || S == PGI_MIN_BSHIFT || n_crowded <= ((n >> S) + 1) / crowded_div()) break;
         }
-        uint32_t *n_chunks = tmp.get<uint32_t>(nb + 1); uint64_t *chunk_base = tmp.get<uint64_t>(nb + 1);
+        uint32_t *n_chunks = tmp.get<uint32_t>(nb + 1); uint64_t *chunk_base = tmp.get<uint64_t>(nb + 1); uint8_t *sub_shift = tmp.get<uint8_t>(nb + 1);
         CK(cudaMemset(n_chunks, 0, (nb + 1) * 4)); CK(cudaMemset(d_ctr, 0, 8));
-        B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, nb, S, r, n, n_chunks, d_ctr);
+        B::count_entries_kernel<<<grid_of(nb, 256), 256>>>(frun, starts, rlen, nb, S, r, n, n_chunks, sub_shift, d_ctr);
         CK(cudaGetLastError());
         thrust::exclusive_scan(pol, thrust::make_transform_iterator(n_chunks, B::Widen()), thrust::make_transform_iterator(n_chunks, B::Widen()) + nb + 1, chunk_base);
         uint64_t total_chunks = 0; CK(cudaMemcpy(&total_chunks, chunk_base + nb, 8, cudaMemcpyDeviceToHost));
         const uint64_t n_blocks = nb + total_chunks;
         if (n_blocks >= 0xFFFFFFFFull) throw FormatError("too many run blocks (>= 2^32 - 1) for the 32-bit block indices of the MEM kernel");
         uint32_t *blocks = dev_alloc<uint32_t>(n_blocks * PGI_BLOCK_U32, ix->owned, bytes);
-        B::bucket_kernel<<<grid_of(nb, 128), 128>>>(frun, starts, rlen, code, nb, S, r, n, n_chunks, chunk_base, blocks);
+        B::bucket_kernel<<<grid_of(nb, 128), 128>>>(frun, starts, rlen, code, nb, S, r, n, n_chunks, sub_shift, chunk_base, blocks);
         CK(cudaGetLastError());
         {   // cumulative headers: field by field, the in-bucket totals sit in the primary blocks themselves
             uint64_t *before = tmp.get<uint64_t>(nb);
@@ -395,7 +397,7 @@ extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *le
             CK(cudaDeviceSynchronize());
             tmp.drop(before);
         }
-        tmp.drop(frun); tmp.drop(n_chunks); tmp.drop(chunk_base); tmp.drop(starts); tmp.drop(code); tmp.drop(rlen);
+        tmp.drop(frun); tmp.drop(n_chunks); tmp.drop(chunk_base); tmp.drop(sub_shift); tmp.drop(starts); tmp.drop(code); tmp.drop(rlen);
         // ---- scalars and tables, as FastLocate::calculate_C (r-index.hpp:440-482) + serialize_encoded / load_encoded leave them
         RiImage im; RiConsts &k = im.k; std::memset(&k, 0, sizeof(k));
         bool present[6]; unsigned sigma = 0;
@@ -594,7 +596,7 @@ struct pgi_batch {
     double mems_per_read = 4.0, raw_per_mem = 2.0;         // running estimates that size the next step's buffers
     uint64_t mem_cap_hint = 0, raw_cap_hint = 0, large_cap_hint = 0;   // raised when a step did not fit (collect_and_check)
     uint64_t mems_cap = 0, mem_slots = 0, part_cap = 0, raw_cap = 0, large_cap = 0;   // capacities the current step was launched with
-    uint64_t n_mems = 0, n_tags = 0, extensions = 0, seed_lookups = 0;
+    uint64_t n_mems = 0, n_tags = 0, extensions = 0, seed_lookups = 0, blocks_fetched = 0;
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
     void release_all() {
@@ -691,10 +693,10 @@ void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_
 //   [8] MEMs found (exact even after an overflow)   [9] slots the fullest partition asked for   [10] MEMs the later stages
 //   see (= [8] clamped to the capacity of the ordered MEM buffer)   [12] long tag lists queued   [13] raw buffer too small
 // host mirror (h_ctr, pinned; written by collect_kernel): [0] = [8], [1] = [9], [2] extensions, [3] seed lookups,
-//   [4] items to decode (raw_off[nm]), [5] long lists, [6] raw overflow flag, [7] unique tags (tag_off[nm])
+//   [4] items to decode (raw_off[nm]), [5] long lists, [6] raw overflow flag, [7] unique tags (tag_off[nm]), [9] run blocks fetched
 // A counter reaches the host through a KERNEL writing pinned memory (unified addressing), not a cudaMemcpyAsync: a copy,
 // however small, queues on the device-to-host copy engine behind the result download of whichever call finished before.
-enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
+enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_BLK = 5, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
 
 __global__ void mem_finalize_kernel(unsigned long long *st, const unsigned long long *slot_ctr, uint64_t part_cap, uint64_t mems_cap) {
     __shared__ unsigned long long s_sum[PGI_SLOT_PARTS], s_max[PGI_SLOT_PARTS];
@@ -716,7 +718,7 @@ __global__ void collect_kernel(const unsigned long long *st, const uint64_t *raw
     if (threadIdx.x == 0) {
         const uint64_t nm = st[ST_NM];
         host[0] = st[ST_NMEMS]; host[1] = st[ST_MAXPART]; host[2] = st[ST_EXT]; host[3] = st[ST_SEED];
-        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0;
+        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0; host[9] = st[ST_BLK];
         __threadfence_system();
     }
 }
@@ -809,7 +811,7 @@ void enqueue_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &la
     a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
     a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
-    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.mem_cap = cap;
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.mem_cap = cap;
     a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
     a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
@@ -841,7 +843,7 @@ void enqueue_count_stage(pgi_batch *b, int &launches) {
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
-    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
@@ -923,7 +925,7 @@ bool collect_and_check(pgi_batch *b, bool with_tags, bool mem_stage) {
     CK(cudaStreamSynchronize(b->stream));
     volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
     const uint64_t total = h[0], maxpart = h[1], total_raw = h[4], n_large = h[5], raw_ovf = h[6];
-    b->extensions = h[2]; b->seed_lookups = h[3]; b->n_mems = total; b->n_tags = with_tags ? h[7] : 0;
+    b->extensions = h[2]; b->seed_lookups = h[3]; b->blocks_fetched = h[9]; b->n_mems = total; b->n_tags = with_tags ? h[7] : 0;
     bool again = false;
     if (mem_stage) {
         if (b->part_cap ? maxpart > b->part_cap : total > b->mem_slots) {
@@ -999,7 +1001,7 @@ extern "C" int pgi_batch_device_result(pgi_batch *b, pgi_result *out) {
     if (!b || !out) return fail(PGI_EINVAL, "null argument");
     if (!b->has_result) return fail(PGI_EINVAL, "no completed run on this batch");
     std::memset(out, 0, sizeof(*out));
-    out->n_reads = b->n_reads; out->n_mems = b->n_mems; out->n_tags = b->n_tags; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups;
+    out->n_reads = b->n_reads; out->n_mems = b->n_mems; out->n_tags = b->n_tags; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups; out->blocks_fetched = b->blocks_fetched;
     out->mem_off = b->d_mem_off.as<uint64_t>(); out->mems = b->d_mems.as<pgi_mem>(); out->tag_off = b->d_tag_off.as<uint64_t>();
     out->tags = b->d_tags.as<uint64_t>(); out->n_runs = b->d_n_runs.as<uint64_t>();
     return PGI_OK;
@@ -1020,7 +1022,7 @@ extern "C" int pgi_batch_fetch(pgi_batch *b, pgi_result *out) {
         if (nm) CK(cudaMemcpyAsync(b->h_n_runs.p, b->d_n_runs.p, nm * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         std::memset(out, 0, sizeof(*out));
-        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups;
+        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = b->extensions; out->seed_lookups = b->seed_lookups; out->blocks_fetched = b->blocks_fetched;
         out->mem_off = b->h_mem_off.as<uint64_t>(); out->mems = b->h_mems.as<pgi_mem>(); out->tag_off = b->h_tag_off.as<uint64_t>();
         out->tags = b->h_tags.as<uint64_t>(); out->n_runs = b->h_n_runs.as<uint64_t>();
         return PGI_OK;
@@ -1233,29 +1235,49 @@ static inline void put_i64(std::string &s, int64_t v) {
     if (v < 0) { s.push_back('-'); put_u64(s, (uint64_t) 0 - (uint64_t) v); } else put_u64(s, (uint64_t) v);
 }
 
-// stdout grammar of src/find_mems.cpp:115-139 and src/tag_arrays.cpp:885-889.
-extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int with_tags, uint64_t *len) {
-    if (!r || !len) { fail(PGI_EINVAL, "null argument"); return nullptr; }
-    std::string s;
-    s.reserve((size_t) (r->n_reads * 16 + r->n_mems * 96 + r->n_tags * 12));
-    for (uint64_t i = 0; i < r->n_reads; ++i) {
+// stdout grammar of src/find_mems.cpp:115-139 and src/tag_arrays.cpp:885-889. Host work: the reads of a
+// result are cut into contiguous ranges, one per host thread this process may run on (PGI_FORMAT_THREADS overrides), each
+// range is formatted into its own string and the pieces are concatenated (one thread managed 3 M reads/s, 60 x below the
+// rate the GPU produces results at).
+static void format_range(const pgi_result *r, uint64_t first_seq, int with_tags, uint64_t a, uint64_t b, std::string &s) {
+    s.reserve((size_t) ((b - a) * 16 + (r->mem_off[b] - r->mem_off[a]) * 96 + (with_tags ? (r->tag_off[r->mem_off[b]] - r->tag_off[r->mem_off[a]]) * 14 : 0)));
+    for (uint64_t i = a; i < b; ++i) {
         s += "Seq: "; put_u64(s, first_seq + i); s.push_back('\n');
         for (uint64_t m = r->mem_off[i]; m < r->mem_off[i + 1]; ++m) {
             const pgi_mem &x = r->mems[m];
             s += "MEM START: "; put_u64(s, x.start); s += ", MEM END: "; put_u64(s, x.end);
             s += " BWT START: "; put_u64(s, x.bwt_start); s += " SIZE: "; put_i64(s, x.size); s.push_back('\n');
             if (with_tags) {
-                const uint64_t a = r->tag_off[m], e = r->tag_off[m + 1];
-                s += "Number of unique positions: "; put_u64(s, e - a); s.push_back('\n');
-                for (uint64_t t = a; t < e; ++t) { put_u64(s, r->tags[t]); s += ", "; }
+                const uint64_t ta = r->tag_off[m], te = r->tag_off[m + 1];
+                s += "Number of unique positions: "; put_u64(s, te - ta); s.push_back('\n');
+                for (uint64_t t = ta; t < te; ++t) { put_u64(s, r->tags[t]); s += ", "; }
                 s.push_back('\n');
             }
         }
         s.push_back('\n');
     }
-    char *buf = (char *) std::malloc(s.size() + 1);
+}
+extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int with_tags, uint64_t *len) {
+    if (!r || !len) { fail(PGI_EINVAL, "null argument"); return nullptr; }
+    unsigned nt = 1;
+    { cpu_set_t set; CPU_ZERO(&set); if (sched_getaffinity(0, sizeof(set), &set) == 0) nt = (unsigned) std::max(1, CPU_COUNT(&set)); }
+    if (const char *e = std::getenv("PGI_FORMAT_THREADS")) nt = (unsigned) std::max(1, std::atoi(e));
+    nt = (unsigned) std::min<uint64_t>(nt, std::max<uint64_t>(1, r->n_reads / 4096));
+    std::vector<std::string> part(nt);
+    try {
+        if (nt == 1) format_range(r, first_seq, with_tags, 0, r->n_reads, part[0]);
+        else {
+            std::vector<std::thread> th;
+            for (unsigned k = 0; k < nt; ++k)
+                th.emplace_back([&, k] { format_range(r, first_seq, with_tags, r->n_reads * k / nt, r->n_reads * (k + 1) / nt, part[k]); });
+            for (auto &t : th) t.join();
+        }
+    } catch (const std::exception &) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
+    size_t total = 0; for (auto &p : part) total += p.size();
+    char *buf = (char *) std::malloc(total + 1);
     if (!buf) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
-    std::memcpy(buf, s.data(), s.size()); buf[s.size()] = 0; *len = s.size();
+    size_t at = 0; for (auto &p : part) { std::memcpy(buf + at, p.data(), p.size()); at += p.size(); }
+    buf[total] = 0; *len = total;
     return buf;
 }
 // stdout of src/query_tags.cpp:87-109 for a pgi_query_tags result: for every read with a match the two lines that
@@ -1289,15 +1311,50 @@ extern "C" void *pgi_host_alloc(size_t bytes) {
 }
 extern "C" void pgi_host_free(void *p) { if (p) cudaFreeHost(p); }
 
+// cudaLimitMaxL2FetchGranularity of `device`: bytes the L2 fetches from DRAM around a missing sector (32, 64 or 128). A run
+// block is one aligned 64-byte unit; with a granularity of 128 every block fetch drags in the neighbouring block as well.
+extern "C" int pgi_l2_fetch_granularity(int device, int set_bytes, int *current) {
+    if (int rc = check_device(device)) return rc;
+    try {
+        DeviceGuard g(device);
+        if (set_bytes) CK(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t) set_bytes));
+        size_t v = 0; CK(cudaDeviceGetLimit(&v, cudaLimitMaxL2FetchGranularity));
+        if (current) *current = (int) v;
+        return PGI_OK;
+    } PGI_CATCH
+}
+
 extern "C" int pgi_random_access_gbs(int device, uint64_t buf_bytes, uint32_t bytes_per_access, uint64_t n_access, int chain, double *gbs) {
-    if (!gbs || chain < 1 || (bytes_per_access != 32 && bytes_per_access != 64 && bytes_per_access != 128)) return fail(PGI_EINVAL, "bad argument");
+    if (!gbs || chain < 0 || (bytes_per_access != 32 && bytes_per_access != 64 && bytes_per_access != 128)) return fail(PGI_EINVAL, "bad argument");
     if (int rc = check_device(device)) return rc;
     try {
         DeviceGuard g(device);
         DevBuf buf, sink; buf.need(buf_bytes); sink.need(8);
         CK(cudaMemset(buf.p, 1, buf_bytes)); CK(cudaMemset(sink.p, 0, 8));
         const uint64_t n_slots = buf_bytes / bytes_per_access;
-        if (n_slots < 1 || (chain == 1 && n_slots >> 32)) return fail(PGI_EINVAL, "buffer too small or too large for the microbenchmark");
+        if (n_slots < 1 || (chain <= 1 && n_slots >> 32)) return fail(PGI_EINVAL, "buffer too small or too large for the microbenchmark");
+        if (chain == 0) {                                 // cooperative form: teams of lanes, 8 independent slots in flight per lane
+            const uint32_t team = bytes_per_access / 16, rounds = 16;
+            const uint64_t n_teams = std::max<uint64_t>(1, n_access / (rounds * 8ull));
+            const unsigned grid = grid_for(n_teams * team, 256);
+            const uint64_t accesses = (uint64_t) grid * 256 / team * rounds * 8ull;
+            cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+            float best = 1e30f;
+            for (int rep = 0; rep < 4; ++rep) {
+                CK(cudaEventRecord(e0));
+                unsigned long long *sk = sink.as<unsigned long long>();
+                if (bytes_per_access == 32) gather_team_kernel<32><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, rounds, sk);
+                else if (bytes_per_access == 64) gather_team_kernel<64><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, rounds, sk);
+                else gather_team_kernel<128><<<grid, 256>>>(buf.as<uint4>(), (uint32_t) n_slots, rounds, sk);
+                CK(cudaGetLastError());
+                CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+                float ms = 0; CK(cudaEventElapsedTime(&ms, e0, e1));
+                if (rep > 0 && ms < best) best = ms;
+            }
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+            *gbs = (double) accesses * bytes_per_access / (best * 1e-3) / 1e9; buf.release(); sink.release();
+            return PGI_OK;
+        }
         uint64_t n_threads = std::max<uint64_t>(1, n_access / (uint64_t) chain);
         const uint32_t per_thread = 64;                   // independent form: 64 loads per thread
         if (chain == 1) n_threads = std::max<uint64_t>(256, (n_access / per_thread + 255) / 256 * 256);

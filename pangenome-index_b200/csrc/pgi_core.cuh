@@ -174,16 +174,8 @@ __device__ __noinline__
 inline
 #endif
 PosRank rank_in_chunk(const RiDev &ix, const uint32_t w[16], uint32_t rel, uint32_t tbl) {
-    uint32_t j = 0;
-#pragma unroll 1
-    for (int i = 10; i < 16; ++i) {
-        const uint32_t x = w[i];
-        const uint32_t c = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
-        j += c;                                                          // boundary b (> 0) counts when b <= rel; 0 = unused never counts
-        if (c < 4u) break;                                               // ascending
-    }
     uint32_t v[16];
-    ld_block(ix.blocks + ((uint64_t) w[0] + j) * PGI_BLOCK_WORDS, v);
+    ld_block(ix.blocks + ((uint64_t) w[0] + (rel >> w[10])) * PGI_BLOCK_WORDS, v);      // sub-bucket number = rel >> sub_shift
     return pos_rank(v, rel, tbl, scan_tab(tbl));
 }
 // Rank of one position from memory (batched rank API, lane-private fetch mode, hostsim).

@@ -161,6 +161,11 @@ private:
     }
 };
 
+// At most one bucket in crowded_div() may be crowded (PGI_CROWDED_DIV=<n> overrides the default for tuning runs).
+inline uint64_t crowded_div() {
+    if (const char *e = std::getenv("PGI_CROWDED_DIV")) { const long v = std::strtol(e, nullptr, 10); if (v > 0) return (uint64_t) v; }
+    return PGI_CROWDED_DIV;
+}
 // Buckets holding more than PGI_RUNS_PER_BLOCK clipped runs for a bucket size of 2^S positions.
 inline uint64_t count_overflow_buckets(const std::vector<uint32_t> &runs, unsigned S) {
     uint64_t pos = 0, cur = 0, cnt = 0, over = 0;      // cur: bucket being filled, cnt: its entries so far
@@ -193,6 +198,20 @@ inline void write_block(uint64_t *dst, const uint64_t cum[6], const uint32_t *co
     for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) dst[j] = (uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32;
 }
 
+// Crowded bucket (more than 12 clipped runs, given as code[] / end[] with end offsets relative to the bucket): the largest
+// sub_shift for which every sub-bucket of 2^sub_shift positions holds at most PGI_CHUNK_RUNS clipped runs.
+inline unsigned choose_sub_shift(const std::vector<uint32_t> &end, unsigned S) {
+    for (unsigned ss = S - 1;; --ss) {
+        bool ok = true; size_t i = 0; const uint32_t n_sub = 1u << (S - ss);
+        for (uint32_t c = 0; c < n_sub && ok; ++c) {
+            const uint32_t hi = (c + 1) << ss; unsigned k = 0;
+            while (i < end.size()) { ++k; if (end[i] > hi) break; ++i; if (end[i - 1] == hi) break; }
+            ok = k <= PGI_CHUNK_RUNS;
+        }
+        if (ok || ss == 0) return ss;
+    }
+}
+
 // The bucket array (pgi_layout.h): block b = positions [b << S, (b + 1) << S); chunk blocks of crowded buckets behind.
 // totals[c] receives the number of occurrences of code c.
 inline void build_buckets(RiImage &im, const std::vector<uint32_t> &runs, uint64_t n, uint64_t totals[6]) {
@@ -200,9 +219,9 @@ inline void build_buckets(RiImage &im, const std::vector<uint32_t> &runs, uint64
     unsigned S = PGI_MAX_BSHIFT;
     if (const char *e = std::getenv("PGI_BSHIFT")) {
         S = (unsigned) std::atoi(e);
-        if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 8]");
+        if (S < PGI_MIN_BSHIFT || S > PGI_MAX_BSHIFT) throw FormatError("PGI_BSHIFT outside [4, 12]");
     } else {
-        for (; S > PGI_MIN_BSHIFT; --S) if (count_overflow_buckets(runs, S) <= ((n >> S) + 1) / 64) break;
+        for (; S > PGI_MIN_BSHIFT; --S) if (count_overflow_buckets(runs, S) <= ((n >> S) + 1) / crowded_div()) break;
     }
     const uint64_t nb = (n >> S) + 1, bsize = 1ull << S;
     im.k.bshift = S; im.k.n_buckets = nb;
@@ -224,30 +243,32 @@ inline void build_buckets(RiImage &im, const std::vector<uint32_t> &runs, uint64
         uint64_t *dst = im.blocks.data() + (size_t) b * PGI_BLOCK_WORDS;
         const unsigned ne = (unsigned) code.size();
         if (ne <= PGI_RUNS_PER_BLOCK) { write_block(dst, bcum, code.data(), end.data(), ne, 0u); continue; }
-        // crowded bucket: directory block + chunk blocks (chunk 0: 12 runs; later chunks: pad entry + 11 runs)
+        // crowded bucket: directory block + one chunk block per sub-bucket of 2^ss positions (pad entry + at most 11 runs)
+        const unsigned ss = choose_sub_shift(end, S); const uint32_t n_sub = 1u << (S - ss);
         const uint64_t base = im.blocks.size() / PGI_BLOCK_WORDS;
-        uint8_t bounds[PGI_DIR_BOUNDS] = {0}; unsigned nchunks = 0;
+        im.blocks.resize(im.blocks.size() + (size_t) n_sub * PGI_BLOCK_WORDS);
         uint64_t ccum[6]; std::memcpy(ccum, bcum, sizeof(bcum));
-        for (unsigned i = 0; i < ne;) {
+        size_t i = 0; uint32_t at = 0;                                       // at: bucket offset reached so far
+        for (uint32_t c = 0; c < n_sub; ++c) {
+            const uint32_t lo_c = c << ss, hi_c = (c + 1) << ss;
             uint32_t cc[PGI_RUNS_PER_BLOCK], ce[PGI_RUNS_PER_BLOCK]; unsigned k = 0;
-            if (nchunks) {
-                if (nchunks > PGI_DIR_BOUNDS) throw FormatError("internal: too many chunks in a bucket");
-                bounds[nchunks - 1] = (uint8_t) end[i - 1];                 // < 2^S <= 256, and > 0
-                cc[0] = PGI_CODE_UNUSED; ce[0] = end[i - 1]; k = 1;
-            }
+            if (c) { cc[0] = PGI_CODE_UNUSED; ce[0] = lo_c; k = 1; }
             uint64_t add[6] = {0, 0, 0, 0, 0, 0};
-            for (; k < PGI_RUNS_PER_BLOCK && i < ne; ++k, ++i) { cc[k] = code[i]; ce[k] = end[i]; add[code[i]] += end[i] - (i ? end[i - 1] : 0u); }
-            im.blocks.resize(im.blocks.size() + PGI_BLOCK_WORDS);
-            write_block(im.blocks.data() + im.blocks.size() - PGI_BLOCK_WORDS, ccum, cc, ce, k, 0u);
-            for (unsigned c = 0; c < 6; ++c) ccum[c] += add[c];
-            ++nchunks;
+            while (i < ne && at < hi_c) {
+                const uint32_t e = end[i] < hi_c ? end[i] : hi_c;
+                if (k >= PGI_RUNS_PER_BLOCK) throw FormatError("internal: sub-bucket overflow");
+                cc[k] = code[i]; ce[k] = e; ++k; add[code[i]] += e - at; at = e;
+                if (end[i] <= hi_c) ++i;
+            }
+            write_block(im.blocks.data() + (size_t) (base + c) * PGI_BLOCK_WORDS, ccum, cc, ce, k, 0u);
+            for (unsigned q = 0; q < 6; ++q) ccum[q] += add[q];
         }
         dst = im.blocks.data() + (size_t) b * PGI_BLOCK_WORDS;             // (the vector may have moved)
         write_block(dst, bcum, nullptr, nullptr, 0, (uint32_t) base);    // header: counts before the bucket (the answer at offset 0)
         uint32_t w[PGI_BLOCK_U32];
         for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) { w[2 * j] = (uint32_t) dst[j]; w[2 * j + 1] = (uint32_t) (dst[j] >> 32); }
-        w[8] &= 0xFFFFu; w[9] = PGI_CODE_DIRBLOCK;                       // marker; the scan of offset 0 adds nothing whatever the entries
-        std::memcpy(&w[10], bounds, PGI_DIR_BOUNDS);
+        w[8] &= 0xFFFFu; w[9] = PGI_CODE_DIRBLOCK; w[10] = ss;            // marker; the scan of offset 0 adds nothing whatever the entries
+        for (unsigned j = 11; j < PGI_BLOCK_U32; ++j) w[j] = 0;
         for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) dst[j] = (uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32;
         ++n_dir;
     }

@@ -27,6 +27,7 @@ struct MemArgs {
     unsigned long long *mem_count; // MEMs appended so far (keeps counting past mem_cap)
     unsigned long long *ext_count; // FMD extensions of the reference algorithm (a seed lookup counts as its seed_k extensions)
     unsigned long long *seed_count;// seed lookups that replaced seed_k extensions each
+    unsigned long long *blk_count; // 64-byte run blocks fetched (bucket blocks + chunk blocks): what the kernel moves from the index
     uint64_t mem_cap;
     uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
     uint64_t *mem_key;             // read id << 32 | index of the MEM within its read
@@ -85,18 +86,9 @@ __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned whic
 // became empty, and its record {0, len, range.first, size} (empty range: bwt_start 1, size 0 = the reference's {1,0})
 // goes to mem_buf[read] directly: one record per read, already in read order.
 // Crowded bucket (pgi_layout.h): sl = the lane's staged directory block, z = its swizzle. Index of the chunk block that
-// holds bucket offset rel (> 0): first chunk + number of chunk boundaries <= rel.
-__device__ __noinline__ uint32_t staged_chunk_of(const uint4 *sl, unsigned z, uint32_t rel) {
-    uint32_t j = sl[0u ^ z].x;                                           // first chunk
-    const uint32_t *c = reinterpret_cast<const uint32_t *>(sl + (2u ^ z)), *d = reinterpret_cast<const uint32_t *>(sl + (3u ^ z));
-#pragma unroll 1
-    for (int i = 2; i < 8; ++i) {                                        // boundary words: w10, w11 (part 2), w12..w15 (part 3)
-        const uint32_t x = i < 4 ? c[i] : d[i - 4];                      // a boundary b (> 0) counts when b <= rel; 0 = unused never counts
-        const uint32_t n = (((x & 0xFFu) - 1u) < rel) + ((((x >> 8) & 0xFFu) - 1u) < rel) + ((((x >> 16) & 0xFFu) - 1u) < rel) + (((x >> 24) - 1u) < rel);
-        j += n;
-        if (n < 4u) break;                                               // ascending: nothing further can count
-    }
-    return j;
+// holds bucket offset rel (> 0): first chunk + sub-bucket number (pgi_layout.h).
+__device__ __forceinline__ uint32_t staged_chunk_of(const uint4 *sl, unsigned z, uint32_t rel) {
+    return sl[0u ^ z].x + (rel >> sl[2u ^ z].z);                          // w0 + (rel >> w10): first chunk + sub-bucket number
 }
 
 template <int MODE, int THREADS, int BPS, int OP = 0>
@@ -104,6 +96,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     __shared__ uint32_t s_desc[512];
     __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
     __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
+    __shared__ uint32_t s_blk[THREADS / 32];                              // per warp: run blocks fetched (work counter, kept out of the registers)
+    if (threadIdx.x < THREADS / 32) s_blk[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < 512; i += blockDim.x) {
         s_desc[i] = a.desc[i];
         if (MODE) s_tab[i] = reinterpret_cast<const uint4 *>(a.desc + 512)[i];
@@ -273,6 +267,10 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
             coop_issue(b1, b2);
+            {
+                const unsigned nb = __popc(__ballot_sync(FULL, b1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, b2 != PGI_NOBLK));
+                if (lane == 0) s_blk[threadIdx.x >> 5] += nb;
+            }
             bool seed_ok = false;
             if (OP == 0 && seed_k && __any_sync(FULL, cand)) {
                 if (cand) {
@@ -305,6 +303,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
                 if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
                     __syncwarp();                             // every lane has read its directory words
+                    const unsigned nc = __popc(__ballot_sync(FULL, c1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, c2 != PGI_NOBLK));
+                    if (lane == 0) s_blk[threadIdx.x >> 5] += nc;
                     coop_fetch(c1, c2);
                     if (c2 != PGI_NOBLK) which2 = 1u;
                 }
@@ -350,6 +350,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     unsigned long long tot = n_ext;
     for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
     if (lane == 0 && tot) atomicAdd(a.ext_count, tot);
+    if (MODE && lane == 0 && a.blk_count && s_blk[threadIdx.x >> 5]) atomicAdd(a.blk_count, (unsigned long long) s_blk[threadIdx.x >> 5]);
     if (OP == 0 && seed_k) {
         unsigned tots = n_seed;
         for (int o = 16; o; o >>= 1) tots += __shfl_xor_sync(FULL, tots, o);

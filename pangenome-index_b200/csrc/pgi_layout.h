@@ -23,24 +23,30 @@
 // two runs per 16x2 SIMD min, and the weighted sums are byte dot products (dp2a) against 8-byte weight tables looked
 // up with the code nibbles as PRMT selectors (pos_rank in pgi_core.cuh).
 //
-// bshift is chosen per index (largest value <= 8 for which at most 1/64 of the buckets hold more than 12 clipped runs;
-// PGI_BSHIFT=<n> overrides it for tuning / tests). A bucket with MORE than 12 runs becomes a DIRECTORY block:
+// bshift is chosen per index: the largest value <= 12 for which at most 1/PGI_CROWDED_DIV of the buckets hold more than 12
+// clipped runs (PGI_BSHIFT=<n> overrides it for tuning / tests). Larger buckets mean fewer block fetches: the two
+// positions k and k + s of an extension share their bucket more often (on a pangenome of H haplotypes s stays near 2 H for
+// most of a read), and the B200's DRAM delivers 128 bytes per access whatever is asked for (ncu: 114 B of DRAM reads per
+// 64-byte block fetched, profiles/r02h), so every fetch saved is 128 bytes of the bound resource. A bucket with MORE than
+// 12 runs becomes a DIRECTORY block:
 //   w9 low nibble = 0xF (no run has that code), w0 = index of its first chunk block (chunks are stored behind the
-//   n_buckets primary blocks), bytes of w10..w15 = bucket offsets at which chunks 1, 2, ... start (0: unused); its
-//   header (w1..w8 low half) holds the counts before the bucket, which is the whole answer for bucket offset 0.
-// A chunk block has the normal format with the counts before ITS first run in the header; chunk 0 holds 12 runs,
-// later chunks start with a pad entry (code 7, E = the chunk's start offset) so that the same scan applies, then 11
-// runs. A position in such a bucket costs ONE more dependent 64-byte access (count the boundaries <= rel, load that
-// chunk): dense stretches are rare by the choice of bshift (but not negligible: the first n_seq BWT rows are runs of
-// length 1 next to C['A'], where every search for an 'A' starts).
+//   n_buckets primary blocks), w10 = sub_shift: the bucket is cut into 2^(bshift - sub_shift) SUB-BUCKETS of 2^sub_shift
+//   positions, one chunk block each, sub_shift being the largest value for which every sub-bucket holds at most 11 clipped
+//   runs; its header (w1..w8 low half) holds the counts before the bucket, which is the whole answer for bucket offset 0.
+// The chunk of bucket offset rel is chunk number rel >> sub_shift: no search. A chunk block has the normal format with
+// the counts before ITS first position in the header; chunks 1.. start with a pad entry (code 7, E = the chunk's start
+// offset) so that the same scan applies (end offsets stay relative to the BUCKET). A position in such a bucket costs ONE
+// more dependent 64-byte access: dense stretches are rare by the choice of bshift (but not negligible: the first n_seq
+// BWT rows are runs of length 1 next to C['A'], where every search for an 'A' starts).
 #define PGI_BLOCK_U32 16
 #define PGI_BLOCK_WORDS 8            /* the same block counted in u64 words (host vectors are u64) */
 #define PGI_RUNS_PER_BLOCK 12
 #define PGI_CODE_UNUSED 7u
 #define PGI_CODE_DIRBLOCK 0xFu
-#define PGI_MAX_BSHIFT 8             /* chunk boundaries are bytes */
+#define PGI_MAX_BSHIFT 12            /* end offsets are 16 bits; 4096 positions per 64-byte block is already more than 12 runs ever cover */
 #define PGI_MIN_BSHIFT 4
-#define PGI_DIR_BOUNDS 24            /* bytes of w10..w15 */
+#define PGI_CHUNK_RUNS 11            /* runs per chunk block (+ the pad entry) */
+#define PGI_CROWDED_DIV 512          /* at most one bucket in this many may be crowded (bshift rule) */
 
 // Sources of one rank-vector slot R(pos)[i]: true rank of nuc code 0..5,
 // the legacy "column-0 cumulative at the reference block start" quirk, or constant zero.

@@ -163,6 +163,31 @@ __global__ void gather_indep_kernel(const uint4 *buf, uint32_t n_slots, uint32_t
     if (acc == 0x12345u) atomicAdd(sink, 1ull);
 }
 
+// M1, cooperative form (chain == 0): the access pattern of fmd_mem_kernel's block fetch without any of its arithmetic. A TEAM
+// of BYTES / 16 adjacent lanes loads one random slot (16 bytes per lane: one request of the warp covers 32 / team slots),
+// eight independent slots in flight per lane, at full occupancy: about 260 KB of requests in flight per SM, an order of
+// magnitude more than latency x bandwidth needs. Nothing depends on loaded data. This is the CEILING for random BYTES-byte
+// bursts over a footprint of n_slots x BYTES (the figure a gather-bound kernel is measured against).
+template <int BYTES>
+__global__ void __launch_bounds__(256) gather_team_kernel(const uint4 *buf, uint32_t n_slots, uint32_t rounds, unsigned long long *sink) {
+    constexpr unsigned TEAM = BYTES / 16;
+    const uint64_t tid = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    const uint64_t team = tid / TEAM; const unsigned part = (unsigned) (tid % TEAM);
+    uint64_t x = team * (uint64_t) rounds * 8u * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull; uint32_t acc = 0;
+    for (uint32_t r = 0; r < rounds; ++r) {
+        uint4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            x += 0x9E3779B97F4A7C15ull; uint64_t z = x; z ^= z >> 30; z *= 0xBF58476D1CE4E5B9ull; z ^= z >> 27; z *= 0x94D049BB133111EBull; z ^= z >> 31;
+            const uint32_t slot = (uint32_t) (((z >> 32) * (uint64_t) n_slots) >> 32);
+            v[u] = __ldg(buf + (uint64_t) slot * TEAM + part);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc += v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
+    }
+    if (acc == 0x12345u) atomicAdd(sink, 1ull);
+}
+
 // ------------------------------------------------------------------------------------ locate (toehold + phi)
 // FastLocate::locate_encoded (src/r-index.cpp:1300-1343), one thread per BWT range [first, second]: SA value of the first
 // row from the sample of its run, then one phi step (locateNext, :1369-1372) per further row -- an inherently serial

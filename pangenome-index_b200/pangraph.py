@@ -434,18 +434,26 @@ def strand_records(st, log=None):
     return {k: torch.cat(v) for k, v in rec.items()}
 
 # --------------------------------------------------------------------------------------------------------------- the whole collection
-def build(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, **kw):
-    """-> dict(rl_sym uint8, rl_len uint64, tag_val uint64, tag_len uint64 (numpy), n, n_seq, graph, strands)
-    Sequences are hap0, rc(hap0), hap1, rc(hap1), ... each followed by its own end marker (written '\\n'), as in synth.py."""
+def prepare(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, **kw):
+    """The graph and its two strands (haplotype orders at every site) on `device`: enough to sample reads."""
     import time
     t0 = time.time()
     dev = torch.device(device) if not isinstance(device, int) else torch.device("cuda", device)
     g = graph if graph is not None else make_graph(ref_len, n_hap, seed, **kw)
-    if n_hap > 512: raise ValueError("at most 512 haplotypes")
+    if g.H > 512: raise ValueError("at most 512 haplotypes")
     gm = mirror(g)
     if log: log("pangraph: %d haplotypes x %d bp reference, %d sites (%.1fs)" % (g.H, g.L, g.S, time.time() - t0))
     strands = [Strand(g, 0, dev, g.L), Strand(gm, 1, dev, g.L, gm.orig_anchor)]
     if log: log("pangraph: haplotype orders at every site (%.1fs)" % (time.time() - t0))
+    return g, strands
+
+def build(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, prepared=None, **kw):
+    """-> dict(rl_sym uint8, rl_len uint64, tag_val uint64, tag_len uint64 (numpy), n, n_seq, graph, strands, dev_runs)
+    Sequences are hap0, rc(hap0), hap1, rc(hap1), ... each followed by its own end marker (written '\\n'), as in synth.py."""
+    import time
+    t0 = time.time()
+    g, strands = prepared if prepared is not None else prepare(ref_len, n_hap, seed, device, log, graph, **kw)
+    dev = strands[0].dev
     recs = [strand_records(s, log) for s in strands]
     R = {k: torch.cat([r[k] for r in recs]) for k in recs[0]}
     del recs
@@ -477,9 +485,15 @@ def _assemble(R, strands, g, dev, log, t0):
     n = int(cnt.sum())
     if log: log("pangraph: n = %d, r = %d BWT runs, %d tag runs (%.1fs)" % (n, len(sym), len(tv), time.time() - t0))
     byte_of = torch.as_tensor(BYTE_OF, device=dev)
-    return dict(rl_sym=byte_of[sym].cpu().numpy(), rl_len=slen.cpu().numpy().astype(np.uint64), tag_val=tv.cpu().numpy().astype(np.uint64),
-                tag_len=tl.cpu().numpy().astype(np.uint64), n=n, n_seq=2 * g.H, graph=g, strands=strands,
-                dev_runs=dict(sym=byte_of[sym].contiguous(), len=slen, tag_val=tv, tag_len=tl))
+    dev_runs = dict(sym=byte_of[sym].contiguous(), len=slen.contiguous(), tag_val=tv.contiguous(), tag_len=tl.contiguous())
+    out = dict(n=n, n_seq=2 * g.H, graph=g, strands=strands, dev_runs=dev_runs, r=len(sym), n_tag_runs=len(tv))
+    out.update(host_runs(dev_runs))
+    return out
+
+def host_runs(dev_runs):
+    """numpy copies of the run arrays (what prep.rlbwt_from_runs / tags_from_runs take)."""
+    return dict(rl_sym=dev_runs["sym"].cpu().numpy(), rl_len=dev_runs["len"].cpu().numpy().astype(np.uint64),
+                tag_val=dev_runs["tag_val"].cpu().numpy().astype(np.uint64), tag_len=dev_runs["tag_len"].cpu().numpy().astype(np.uint64))
 
 # --------------------------------------------------------------------------------------------------------------- reads
 def sample_reads(strands, n_reads, read_len, sub, seed, indel=0.0):

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_structs_match_header_layout():
     capi = load_package().capi
-    assert ctypes.sizeof(capi.Result) == 11 * 8                 # pgi_result: 3 counts, 5 pointers, extensions, seed_lookups, owner
+    assert ctypes.sizeof(capi.Result) == 12 * 8                 # pgi_result: 3 counts, 5 pointers, extensions, seed_lookups, blocks_fetched, owner
     assert ctypes.sizeof(capi.IndexInfo) == 19 * 8 + 8 * 8 + 256
     assert ctypes.sizeof(capi.LocateResult) == 7 * 8
 
@@ -60,7 +60,7 @@ def test_format_text_is_host_side():
     capi = load_package().capi; L = capi.lib()
     mem_off = np.array([0, 1, 1], dtype=np.uint64); mems = np.array([[3, 10, 1381, 4]], dtype=np.uint64)
     tag_off = np.array([0, 3], dtype=np.uint64); tags = np.array([62467, 128008, 203779], dtype=np.uint64); nr = np.array([3], dtype=np.uint64)
-    r = capi.Result(2, 1, 3, mem_off.ctypes.data, mems.ctypes.data, tag_off.ctypes.data, tags.ctypes.data, nr.ctypes.data, 0, 0, None)
+    r = capi.Result(2, 1, 3, mem_off.ctypes.data, mems.ctypes.data, tag_off.ctypes.data, tags.ctypes.data, nr.ctypes.data, 0, 0, 0, None)
     ln = ctypes.c_uint64(); p = L.pgi_format_text(ctypes.byref(r), 2, 1, ctypes.byref(ln))
     txt = ctypes.string_at(p, ln.value); L.pgi_free(p)
     assert txt == (b"Seq: 2\nMEM START: 3, MEM END: 10 BWT START: 1381 SIZE: 4\nNumber of unique positions: 3\n"

@@ -276,7 +276,7 @@ def test_query_tags_large_and_refusal(capi):
     r5, o5 = datasets.sample_reads(s5["text"], 500, 150, 0.01, seed=2)                  # find_mems itself works on it
     compare(g5.find_mems(r5, o5, 20, 1), orc.Index(s5["ri"]).find_mems(r5, o5, 20, 1), False)
 
-@pytest.mark.parametrize("shift", ["8", "4"])
+@pytest.mark.parametrize("shift", ["12", "10", "8", "4"])
 def test_crowded_buckets(capi, shift, monkeypatch):
     """Bucket size forced (PGI_BSHIFT) so that most buckets are crowded (8: directory block + cooperatively fetched chunk
     blocks on every trip) or tiny (4): the answers do not depend on the device layout."""
@@ -422,7 +422,7 @@ def _runs_of_rlbwt(rl):
     for i in range(int(fb)): ln |= rec[:, 1 + i].astype(np.uint64) << np.uint64(8 * i)
     return rec[:, 0].copy(), ln
 
-@pytest.mark.parametrize("shift", [None, "4", "6"])
+@pytest.mark.parametrize("shift", [None, "4", "6", "9", "12"])
 def test_create_from_runs_equals_create_from_files(capi, shift, monkeypatch):
     if shift: monkeypatch.setenv("PGI_BSHIFT", shift)
     prep = load_package().prep
@@ -436,7 +436,7 @@ def test_create_from_runs_equals_create_from_files(capi, shift, monkeypatch):
               "tag_runs", "tag_items", "tag_item_width", "tag_universe", "n_crowded_buckets", "seed_k"):
         assert a.info[k] == b.info[k], k
     assert a.C == b.C and a.sym_map == b.sym_map
-    if shift == "4": assert b.info["n_crowded_buckets"] > 0
+    if shift in ("9", "12"): assert b.info["n_crowded_buckets"] > 0
     pos = np.arange(0, a.n + 1, dtype=np.uint64)
     assert np.array_equal(a.rank_batch(pos), b.rank_batch(pos))
     reads, off = datasets.sample_reads(s["text"], 4000, 150, 0.01, seed=3)

@@ -143,3 +143,28 @@ def test_locate_matches_oracle(name):
     s5 = datasets.synth_index(ref_len=2000, n_hap=2, seed=3, encoded=True, n_N=0)
     ri5, _ = prep.rindex_from_rlbwt(s5["rl_bwt"], encoded=True, with_samples=True)
     assert sim.Index(ri5).locate(0, 3) is None                                           # encoded, sigma 5
+
+
+@pytest.mark.parametrize("shift", ["4", "8", "10", "12"])
+def test_forced_bucket_shift(shift, monkeypatch):
+    """Bucket sizes from 16 to 4096 positions (PGI_BSHIFT): with the large ones nearly every bucket of these small indexes is
+    crowded (directory block + sub-bucket chunks, pgi_layout.h); extension and MEM finding must not notice."""
+    monkeypatch.setenv("PGI_BSHIFT", shift)
+    for name in ("xy_legacy_bytecode", "synth_enc_compact"):
+        c = case(name); o = orc.Index(c["ri"]); g = sim.Index(c["ri"])
+        assert g.info["bshift"] == int(shift)
+        if int(shift) >= 8: assert g.info["n_crowded"] > 0
+        rng = np.random.default_rng(5); N = 20000; n = o.n
+        iv = np.zeros((N, 3), dtype=np.uint64)
+        k = rng.integers(0, n, N); sz = np.minimum(rng.integers(0, 600, N), n - k)
+        iv[:, 0] = k; iv[:, 1] = rng.integers(0, n, N); iv[:, 2] = sz; iv[:200] = [0, 0, n]
+        sym = rng.choice(np.frombuffer(b"ACGTN\n\0", dtype=np.uint8), N); d = rng.integers(0, 2, N).astype(np.uint8)
+        assert np.array_equal(g.extend_batch(iv, sym, d), o.extend_batch(iv, sym, d))
+        pos_iv = np.zeros((n + 1, 3), dtype=np.uint64); pos_iv[:, 0] = np.arange(n + 1); pos_iv[:, 2] = 0        # every position as k (size 0 -> k + s = k)
+        s2 = np.full(n + 1, ord("A"), dtype=np.uint8); d2 = np.zeros(n + 1, dtype=np.uint8)
+        assert np.array_equal(g.extend_batch(pos_iv, s2, d2), o.extend_batch(pos_iv, s2, d2))
+        reads, off = datasets.sample_reads(c["text"], 60, 150, 0.02, seed=4)
+        R = o.find_mems(reads, off, 12, 1, with_tags=False, threads=1)
+        for i in range(60):
+            mems, ne = g.find_mems(reads[int(off[i]):int(off[i + 1])].tobytes(), 12, 1)
+            assert np.array_equal(mems, R["mems"][int(R["mem_off"][i]):int(R["mem_off"][i + 1])]), i
