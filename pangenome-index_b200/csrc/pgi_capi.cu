@@ -165,7 +165,8 @@ __global__ void seed_table_kernel(RiDev ix, const uint32_t *desc, uint32_t K, ui
 // (interval sizes are not monotone there) or without an r-index part.
 static uint32_t choose_seed_k(const ImageMeta &m) {
     if (!m.has_ri || m.k.has_quirk || m.k.n < 16) return 0;
-    uint32_t K = m.k.n >= (1ull << 28) ? 12u : m.k.n >= (1ull << 22) ? 10u : m.k.n >= (1ull << 16) ? 8u : 6u;
+    // (config 4, n = 2^36.2: K = 12 / 13 / 14 / 15 -> 10.64 / 10.17 / 10.92 / 12.33 ms per step; config 3, n = 2^32.6: 12 beats 14)
+    uint32_t K = m.k.n >= (1ull << 35) ? 13u : m.k.n >= (1ull << 28) ? 12u : m.k.n >= (1ull << 22) ? 10u : m.k.n >= (1ull << 16) ? 8u : 6u;
     if (const char *e = std::getenv("PGI_SEEDK")) { const long v = std::strtol(e, nullptr, 10); if (v >= 0 && v <= (long) PGI_SEED_MAX_K) K = (uint32_t) v; }
     return K;
 }

@@ -332,7 +332,7 @@ PGI_HD void lane_after_ext(MemLane &L, const BiInt &t, uint32_t min_len, uint64_
 // Window of the read: bytes [lo, lo + K) with lo = (position of the first symbol extended) - K + 1; byte i of the window
 // is read position lo + i; extensions run from byte K - 1 down to byte 0. Code of a byte = (byte >> 1) & 3
 // (A 0, C 1, T 2, G 3); idx = sum code_i << 2 i.
-#define PGI_SEED_MAX_K 12u
+#define PGI_SEED_MAX_K 15u
 struct SeedWord { uint32_t x, y, z, w; };            // k, k', s: low 32 bits in x, y, z; bits 32..39 in the bytes of w
 PGI_HD SeedWord seed_pack(const BiInt &b) {
     SeedWord e; e.x = (uint32_t) b.k; e.y = (uint32_t) b.kp; e.z = (uint32_t) (uint64_t) b.s;

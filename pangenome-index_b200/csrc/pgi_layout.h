@@ -46,7 +46,7 @@
 #define PGI_MAX_BSHIFT 12            /* end offsets are 16 bits; 4096 positions per 64-byte block is already more than 12 runs ever cover */
 #define PGI_MIN_BSHIFT 4
 #define PGI_CHUNK_RUNS 11            /* runs per chunk block (+ the pad entry) */
-#define PGI_CROWDED_DIV 512          /* at most one bucket in this many may be crowded (bshift rule) */
+#define PGI_CROWDED_DIV 128          /* at most one bucket in this many may be crowded (bshift rule; config 4: shift 9 / 10 / 11 = 9.79 / 9.71 / 9.68 ms, 12: 12.7 ms, profiles/r02i) */
 
 // Sources of one rank-vector slot R(pos)[i]: true rank of nuc code 0..5,
 // the legacy "column-0 cumulative at the reference block start" quirk, or constant zero.

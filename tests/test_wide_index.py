@@ -74,7 +74,7 @@ def test_gpu_37_bit_index_from_runs(capi):
     n = int(ln.sum()); assert n > 1 << 36
     ri, info = prep.rindex_from_rlbwt(prep.rlbwt_from_runs(sym, ln), encoded=True, with_samples=False)
     o = orc.Index(ri); g = capi.Index.from_runs(sym, ln)
-    assert g.info["n"] == n and g.info["seed_k"] == 12 and g.info["sigma"] == 6 and g.C == o.C
+    assert g.info["n"] == n and g.info["seed_k"] == 13 and g.info["sigma"] == 6 and g.C == o.C
     iv, s, d = random_queries(n, 6, 50000)
     want = o.extend_batch(iv, s, d)
     assert np.array_equal(g.extend_batch(iv, s, d), want)
