@@ -366,7 +366,13 @@ def main():
     # ---- end-to-end timing: K calls of pgi_find_mems (pinned host buffers in, all result arrays out to pinned host memory),
     # issued by E2E_CALLERS host threads the way the batched find_mems driver does, so the copies of one call overlap the
     # kernels of another. Wall clock around all K calls (every call blocks until its result is in host memory).
-    def e2e_pass(k_calls, first):
+    def step_e2e_compact(i):
+        """The lean form of the same call: fixed-length reads (no offset array), result packed on the GPU (pgi_find_mems_compact)."""
+        r = ix.find_mems_compact_raw(h_reads[i % pool].data_ptr(), None, L, n, args.min_len, args.min_occ)
+        sizes = (r.n_reads, r.n_mems, r.n_tags, r.tag_bytes)
+        ix.result_compact_free(r)
+        return sizes
+    def e2e_pass(k_calls, first, compact):
         nxt = [first]; lock = threading.Lock(); acc = [0]
         def caller():
             while True:
@@ -374,32 +380,39 @@ def main():
                     i = nxt[0]
                     if i >= first + k_calls: return
                     nxt[0] += 1
-                nr_, nm_, nt_ = step_e2e(i)
-                with lock: acc[0] += (nr_ + 1) * 8 + nm_ * 32 + (nm_ + 1) * 8 + nt_ * 8 + nm_ * 8
+                if compact:
+                    nr_, nm_, nt_, tb_ = step_e2e_compact(i); got = nr_ * 4 + nm_ * 24 + nt_ * tb_
+                else:
+                    nr_, nm_, nt_ = step_e2e(i); got = (nr_ + 1) * 8 + nm_ * 32 + (nm_ + 1) * 8 + nt_ * 8 + nm_ * 8
+                with lock: acc[0] += got
         ths = [threading.Thread(target=caller) for _ in range(min(E2E_CALLERS, k_calls))]
         t0 = time.perf_counter(); [t.start() for t in ths]; [t.join() for t in ths]
         return 1e3 * (time.perf_counter() - t0), acc[0]
-    e2e_pass(max(args.warmup, E2E_CALLERS), 0)
+    e2e_pass(max(args.warmup, E2E_CALLERS), 0, False)
     barrier()
-    e2e_ms, d2h = e2e_pass(args.steps, args.warmup)
+    e2e_full_ms, d2h_full = e2e_pass(args.steps, args.warmup, False)
+    barrier()
+    e2e_pass(max(args.warmup, E2E_CALLERS), 0, True)
+    barrier()
+    e2e_ms, d2h = e2e_pass(args.steps, args.warmup, True)
     barrier()
     sampler.stop_flag = True
     if sampler.is_alive(): sampler.join(timeout=2)
     # ---- max over ranks
-    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    t = torch.tensor([dev_ms, e2e_ms, e2e_full_ms], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([launches, ext_total, mems_total, tags_total], dtype=torch.float64, device="cuda")
-    per_rank = [[dev_ms / args.steps, e2e_ms / args.steps, max(host_gap), k1_ms / args.steps]]
+    per_rank = [[dev_ms / args.steps, e2e_ms / args.steps, max(host_gap), k1_ms / args.steps, e2e_full_ms / args.steps]]
     if world > 1:
         mine = torch.tensor(per_rank[0], dtype=torch.float64, device="cuda"); allr = [torch.zeros_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine); per_rank = [[round(float(x), 3) for x in r] for r in allr]
         dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    dev_ms, e2e_ms, e2e_full_ms = float(t[0]), float(t[1]), float(t[2])
     if rank == 0: log("per rank [device ms/step, e2e ms/step, slowest host step ms, K1 ms]:", per_rank, "rank 0 host ms per step:", [round(x, 2) for x in host_gap], "cores of rank 0:", my_cores)
     if rank != 0:
         if world > 1: dist.destroy_process_group()
         return
     total_reads = n * args.steps * world
-    value = total_reads / (dev_ms * 1e-3); e2e = total_reads / (e2e_ms * 1e-3)
+    value = total_reads / (dev_ms * 1e-3); e2e = total_reads / (e2e_ms * 1e-3); e2e_full = total_reads / (e2e_full_ms * 1e-3)
     try: os.sched_setaffinity(0, orig_affinity)          # the CPU legs use every host core again
     except Exception: pass
     # ---- CPU side (rank 0, never inside a timed region): the files the reference's loaders read, the restatement, the reference library
@@ -500,9 +513,13 @@ def main():
                        "parity_vs_reference_code": parity_ref, "parity_small_batch_path": parity_small, "batch_digest": batch_digest, "positions_beyond_32_bits": wide,
                        "mems_per_read": float(cnt[2]) / total_reads, "tags_per_read": float(cnt[3]) / total_reads,
                        "extensions_per_read": float(cnt[1]) / total_reads, "step_reruns": reruns},
-            "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": n * L + (n + 1) * 8, "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e2e_ms / args.steps, "concurrent_callers": E2E_CALLERS},
+            "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": n * L, "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e2e_ms / args.steps, "concurrent_callers": E2E_CALLERS,
+                    "api": "pgi_find_mems_compact: pinned host reads in (fixed length, no offset array), every result array out to pinned host memory in the compact wire form (packed on the GPU; pgi_result_expand restores the reference-layout arrays on the host when a caller wants them)",
+                    "bytes_per_read": (n * L + d2h / args.steps) / n,
+                    "reference_layout": {"value": e2e_full, "unit": "reads/s", "api": "pgi_find_mems: reads + u64 offsets in, pgi_result (struct MEM records, u64 offsets / tags / n_runs) out", "h2d_bytes_per_step": n * L + (n + 1) * 8,
+                                         "d2h_bytes_per_step": d2h_full // args.steps, "ms_per_step": e2e_full_ms / args.steps, "bytes_per_read": (n * L + (n + 1) * 8 + d2h_full / args.steps) / n}},
             "gpu_launches": int(cnt[0]),
-            "per_rank_ms_per_step": {"device": [r[0] for r in per_rank], "e2e": [r[1] for r in per_rank], "slowest_host_step": [r[2] for r in per_rank], "fmd_mem_kernel": [r[3] for r in per_rank]},
+            "per_rank_ms_per_step": {"device": [r[0] for r in per_rank], "e2e": [r[1] for r in per_rank], "e2e_reference_layout": [r[4] for r in per_rank], "slowest_host_step": [r[2] for r in per_rank], "fmd_mem_kernel": [r[3] for r in per_rank]},
             "stage_ms_per_step": {k: round(float(v) / args.steps, 3) for k, v in zip(["fmd_mem_kernel", "mem_order", "tag_plan", "tag_decode_sort", "tag_unique_compact", "run_total"], stage[:6])},
             "roofline": {"bound": "hbm", "kernel": "fmd_mem_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": moved,

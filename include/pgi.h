@@ -127,7 +127,7 @@ typedef struct {
     uint64_t n, sigma, n_dev_blocks, bucket_shift, is_encoded;
     uint64_t has_ri, has_tags, tag_layout, has_locate;
     uint64_t src_ri_bytes, src_tag_bytes;   /* sizes of the files the image was made from                              */
-    uint64_t src_ri_sum, src_tag_sum;       /* pgi_image_source_sum of those files (staleness check)                    */
+    uint64_t src_ri_sum, src_tag_sum;       /* pgi_image_source_sum of those files (staleness check: whole-file checksum) */
     uint64_t chunk_bytes, chunks_copied;    /* filled by pgi_index_open_image only                                      */
 } pgi_image_info_t;
 /* Host-only: flatten the files (same arguments as pgi_index_create) and write the image to `path` (atomically:
@@ -135,7 +135,7 @@ typedef struct {
 int pgi_image_write(const void *ri_bytes, size_t ri_len, const void *tag_bytes, size_t tag_len, int tag_layout, const char *path);
 /* Host-only: validate the header of an image (verify != 0: also the checksum of every section) and describe it. */
 int pgi_image_info(const char *path, int verify, pgi_image_info_t *out);
-/* Cheap content stamp of a source file (FNV-1a over its first and last 64 KiB); compared with src_*_sum. */
+/* Content stamp of a source file (FNV-1a over the whole file, near memory speed); compared with src_*_sum. */
 uint64_t pgi_image_source_sum(const void *bytes, size_t len);
 /* Map an image and upload it to GPU `device`. chunk_bytes = 0: 64 MiB (the reference's chunk_size_mb argument, in
  * bytes). verify != 0 (or PGI_IMAGE_VERIFY=1): check every section checksum first. The resulting index is
@@ -179,6 +179,31 @@ void pgi_locate_result_free(pgi_locate_result *);
 int pgi_find_mems(pgi_index *, const char *reads, const uint64_t *read_off, uint64_t n_reads,
                   uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result *out);
 void pgi_result_free(pgi_result *);
+
+/* ---- Compact wire form of a find_mems result: the same information as pgi_result in fewer bytes across PCIe (a batch of
+ * 2 M reads of 150 bp: 117 MB instead of 227 MB), packed on the GPU and expanded on the host only when asked to.
+ *   mem_cnt[i]            MEMs of read i (u32)                       -> pgi_result.mem_off by prefix sum
+ *   rec[2 m], rec[2 m+1]  bwt_start | start << 40,  size | (end - start) << 40    (positions < 2^40, reads < 2^24 bases)
+ *   runs_tags[2 m], [+1]  number_of_runs, number of unique tags of MEM m (u32 each)  -> n_runs, tag_off
+ *   tags                  tag_bytes (5 or 8) little-endian bytes per tag, all MEMs back to back
+ * pgi_find_mems_compact fails with PGI_EINVAL when a value does not fit (a read of 2^24 bases or more, a count of 2^32 or
+ * more); use pgi_find_mems then. Pointers are pinned host memory owned by the library until pgi_result_compact_free. */
+typedef struct {
+    uint64_t n_reads, n_mems, n_tags, tag_bytes;
+    uint32_t *mem_cnt; uint64_t *rec; uint32_t *runs_tags; uint8_t *tags;
+    uint64_t extensions, seed_lookups, blocks_fetched;
+    void *owner;
+} pgi_result_compact;
+/* pgi_find_mems with the compact result. read_off == NULL: every read has read_len bytes (no offset array crosses PCIe). */
+int pgi_find_mems_compact(pgi_index *, const char *reads, const uint64_t *read_off, uint64_t read_len, uint64_t n_reads,
+                          uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result_compact *out);
+void pgi_result_compact_free(pgi_result_compact *);
+/* Host-side expansion into the reference-layout arrays (malloc'd; free with pgi_result_expanded_free). */
+int pgi_result_expand(const pgi_result_compact *, pgi_result *out);
+void pgi_result_expanded_free(pgi_result *);
+/* Batch-context forms: stage fixed-length reads without an offset array; pack + copy the last run's result. */
+int pgi_batch_upload_fixed(pgi_batch *, const char *reads, uint64_t n_reads, uint64_t read_len);
+int pgi_batch_fetch_compact(pgi_batch *, pgi_result_compact *out);
 
 /* The query_tags path: for every read the whole-read backward search FastLocate::count_encoded
  * (include/pangenome_index/r-index.hpp:550-556; the legacy FastLocate::count :541-547 when the file has no encoded

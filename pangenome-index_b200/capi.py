@@ -11,12 +11,18 @@ SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
            "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
-           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs", "pgi_l2_fetch_granularity"]
+           "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs", "pgi_l2_fetch_granularity", "pgi_find_mems_compact", "pgi_result_compact_free",
+           "pgi_result_expand", "pgi_result_expanded_free", "pgi_batch_upload_fixed", "pgi_batch_fetch_compact"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
                 ("mem_off", ctypes.c_void_p), ("mems", ctypes.c_void_p), ("tag_off", ctypes.c_void_p),
                 ("tags", ctypes.c_void_p), ("n_runs", ctypes.c_void_p), ("extensions", ctypes.c_uint64), ("seed_lookups", ctypes.c_uint64), ("blocks_fetched", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
+
+class ResultCompact(ctypes.Structure):
+    _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64), ("tag_bytes", ctypes.c_uint64),
+                ("mem_cnt", ctypes.c_void_p), ("rec", ctypes.c_void_p), ("runs_tags", ctypes.c_void_p), ("tags", ctypes.c_void_p),
+                ("extensions", ctypes.c_uint64), ("seed_lookups", ctypes.c_uint64), ("blocks_fetched", ctypes.c_uint64), ("owner", ctypes.c_void_p)]
 
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
@@ -50,6 +56,12 @@ def lib():
         vp, u64, i32 = ctypes.c_void_p, ctypes.c_uint64, ctypes.c_int
         L.pgi_index_create.argtypes = [vp, ctypes.c_size_t, vp, ctypes.c_size_t, i32, i32, ctypes.POINTER(vp)]
         L.pgi_index_clone_to.argtypes = [vp, i32, ctypes.POINTER(vp)]
+        L.pgi_find_mems_compact.argtypes = [vp, vp, vp, u64, u64, u64, u64, vp, ctypes.POINTER(ResultCompact)]
+        L.pgi_result_compact_free.argtypes = [ctypes.POINTER(ResultCompact)]
+        L.pgi_result_expand.argtypes = [ctypes.POINTER(ResultCompact), ctypes.POINTER(Result)]
+        L.pgi_result_expanded_free.argtypes = [ctypes.POINTER(Result)]
+        L.pgi_batch_upload_fixed.argtypes = [vp, vp, u64, u64]
+        L.pgi_batch_fetch_compact.argtypes = [vp, ctypes.POINTER(ResultCompact)]
         L.pgi_index_create_from_runs.argtypes = [vp, vp, u64, vp, vp, u64, i32, i32, ctypes.POINTER(vp)]
         L.pgi_index_free.argtypes = [vp]
         L.pgi_index_info.argtypes = [vp, ctypes.POINTER(IndexInfo)]
@@ -218,6 +230,25 @@ class Index:
     @staticmethod
     def result_free(res):
         lib().pgi_result_free(ctypes.byref(res))
+    def find_mems_compact_raw(self, reads_ptr, off_ptr, read_len, n_reads, min_len, min_occ):
+        """pgi_find_mems_compact on raw host pointers (off_ptr None: fixed-length reads); free with result_compact_free."""
+        res = ResultCompact()
+        _ck(lib().pgi_find_mems_compact(self.h, reads_ptr, off_ptr, read_len, n_reads, min_len, min_occ, None, ctypes.byref(res)))
+        return res
+    @staticmethod
+    def result_compact_free(res):
+        lib().pgi_result_compact_free(ctypes.byref(res))
+    def find_mems_compact(self, reads, read_len, min_len, min_occ, read_off=None):
+        """Compact call + host expansion -> the same dict as find_mems (text=False)."""
+        reads = np.ascontiguousarray(reads, dtype=np.uint8); L = lib()
+        if read_off is not None: read_off = np.ascontiguousarray(read_off, dtype=np.uint64)
+        n = (len(read_off) - 1) if read_off is not None else (len(reads) // read_len if read_len else 0)
+        c = self.find_mems_compact_raw(reads.ctypes.data, read_off.ctypes.data if read_off is not None else None, read_len, n, min_len, min_occ)
+        wire = c.n_reads * 4 + c.n_mems * 24 + c.n_tags * c.tag_bytes
+        r = Result(); _ck(L.pgi_result_expand(ctypes.byref(c), ctypes.byref(r)))
+        out = _result_to_dict(r, L, self.has_tags, text=False); out["wire_bytes"] = wire
+        L.pgi_result_expanded_free(ctypes.byref(r)); self.result_compact_free(c)
+        return out
 
 class Batch:
     """Reusable batch context (stream + work buffers) for pipelined or device-resident runs."""

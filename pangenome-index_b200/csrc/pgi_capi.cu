@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <stdexcept>
 #include <sched.h>
 #include <thread>
 #include <string>
@@ -594,6 +595,7 @@ struct pgi_batch {
     // tag stage
     DevBuf d_n_runs, d_cnt, d_raw_off, d_first, d_skip, d_raw, d_raw2, d_ucnt, d_tag_off, d_tags, d_large, d_seg_b, d_seg_e;
     PinBuf h_ctr, h_mem_off, h_mems, h_tag_off, h_tags, h_n_runs;
+    DevBuf d_c_cnt, d_c_rec, d_c_rt, d_c_tags; PinBuf h_c_cnt, h_c_rec, h_c_rt, h_c_tags;   // compact wire form (pgi_batch_fetch_compact)
     double mems_per_read = 4.0, raw_per_mem = 2.0;         // running estimates that size the next step's buffers
     uint64_t mem_cap_hint = 0, raw_cap_hint = 0, large_cap_hint = 0;   // raised when a step did not fit (collect_and_check)
     uint64_t mems_cap = 0, mem_slots = 0, part_cap = 0, raw_cap = 0, large_cap = 0;   // capacities the current step was launched with
@@ -602,9 +604,9 @@ struct pgi_batch {
     bool has_result = false;
     void release_all() {
         DevBuf *db[] = {&d_slot_ctr, &d_codes, &d_read_flags, &d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
-                        &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e};
+                        &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e, &d_c_cnt, &d_c_rec, &d_c_rt, &d_c_tags};
         for (DevBuf *b : db) b->release();
-        PinBuf *pb[] = {&h_ctr, &h_mem_off, &h_mems, &h_tag_off, &h_tags, &h_n_runs};
+        PinBuf *pb[] = {&h_ctr, &h_mem_off, &h_mems, &h_tag_off, &h_tags, &h_n_runs, &h_c_cnt, &h_c_rec, &h_c_rt, &h_c_tags};
         for (PinBuf *b : pb) b->release();
     }
 };
@@ -649,6 +651,7 @@ extern "C" int pgi_batch_upload(pgi_batch *b, const char *reads, const uint64_t 
     try {
         DeviceGuard g(b->ix->device);
         if (read_off[0] != 0) return fail(PGI_EINVAL, "read_off[0] must be 0");
+        for (uint64_t i = 0; i < n_reads; ++i) if (read_off[i + 1] < read_off[i]) return fail(PGI_EINVAL, "read offsets must be ascending");
         const uint64_t total = read_off[n_reads];
         b->d_reads.need(total + 16); b->d_read_off.need((n_reads + 1) * 8);
         if (total) CK(cudaMemcpyAsync(b->d_reads.p, reads, total, cudaMemcpyHostToDevice, b->stream));
@@ -697,7 +700,7 @@ void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_
 //   [4] items to decode (raw_off[nm]), [5] long lists, [6] raw overflow flag, [7] unique tags (tag_off[nm]), [9] run blocks fetched
 // A counter reaches the host through a KERNEL writing pinned memory (unified addressing), not a cudaMemcpyAsync: a copy,
 // however small, queues on the device-to-host copy engine behind the result download of whichever call finished before.
-enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_BLK = 5, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
+enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_BLK = 5, ST_BADOFF = 6, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
 
 __global__ void mem_finalize_kernel(unsigned long long *st, const unsigned long long *slot_ctr, uint64_t part_cap, uint64_t mems_cap) {
     __shared__ unsigned long long s_sum[PGI_SLOT_PARTS], s_max[PGI_SLOT_PARTS];
@@ -719,7 +722,7 @@ __global__ void collect_kernel(const unsigned long long *st, const uint64_t *raw
     if (threadIdx.x == 0) {
         const uint64_t nm = st[ST_NM];
         host[0] = st[ST_NMEMS]; host[1] = st[ST_MAXPART]; host[2] = st[ST_EXT]; host[3] = st[ST_SEED];
-        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0; host[9] = st[ST_BLK];
+        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0; host[9] = st[ST_BLK]; host[10] = st[ST_BADOFF];
         __threadfence_system();
     }
 }
@@ -812,7 +815,7 @@ void enqueue_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &la
     a.ix = ix->ri; a.desc = ix->d_desc; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = std::min<uint64_t>(min_len, 0x7FFFFFFFull); a.min_occ = min_occ;
     a.seed = ix->d_seed; a.seed_k = ix->seed_k; a.pad = 0; a.codes32 = b->d_codes.as<uint32_t>(); a.read_flags = b->d_read_flags.as<uint32_t>();
-    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.mem_cap = cap;
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.bad_off = st + ST_BADOFF; a.reads_bytes = b->reads_bytes; a.mem_cap = cap;
     a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
     a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
@@ -844,7 +847,7 @@ void enqueue_count_stage(pgi_batch *b, int &launches) {
     MemArgs a;
     a.ix = ix->ri; a.desc = ix->d_desc_c; a.reads64 = b->reads64; a.read_off = b->read_off;
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
-    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
+    a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.bad_off = st + ST_BADOFF; a.reads_bytes = b->reads_bytes; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
@@ -926,6 +929,7 @@ bool collect_and_check(pgi_batch *b, bool with_tags, bool mem_stage) {
     CK(cudaStreamSynchronize(b->stream));
     volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
     const uint64_t total = h[0], maxpart = h[1], total_raw = h[4], n_large = h[5], raw_ovf = h[6];
+    if (h[10]) throw std::invalid_argument("read offsets are not ascending or point beyond the reads buffer");
     b->extensions = h[2]; b->seed_lookups = h[3]; b->blocks_fetched = h[9]; b->n_mems = total; b->n_tags = with_tags ? h[7] : 0;
     bool again = false;
     if (mem_stage) {
@@ -1030,6 +1034,110 @@ extern "C" int pgi_batch_fetch(pgi_batch *b, pgi_result *out) {
     } PGI_CATCH
 }
 
+// ------------------------------------------------------------------------------------------ compact wire form
+namespace {
+__global__ void iota_mul_kernel(uint64_t n_plus_1, uint64_t mul, uint64_t *out) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i < n_plus_1) out[i] = i * mul;
+}
+// flags[0] set when a value does not fit the compact form
+__global__ void compact_reads_kernel(uint64_t n_reads, const uint64_t *mem_off, uint32_t *cnt, unsigned long long *flags) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    const uint64_t c = mem_off[i + 1] - mem_off[i];
+    if (c >> 32) flags[0] = 1ull;
+    cnt[i] = (uint32_t) c;
+}
+__global__ void compact_mems_kernel(uint64_t n_mems, const uint4 *mems, const uint64_t *tag_off, const uint64_t *n_runs, const uint64_t *tags, unsigned tag_bytes,
+                                    uint64_t *rec, uint32_t *runs_tags, uint8_t *ctags, unsigned long long *flags) {
+    const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (m >= n_mems) return;
+    const uint4 a = mems[2 * m], b = mems[2 * m + 1];
+    const uint64_t start = a.x | (uint64_t) a.y << 32, end = a.z | (uint64_t) a.w << 32, k = b.x | (uint64_t) b.y << 32, sz = b.z | (uint64_t) b.w << 32;
+    const uint64_t t0 = tag_off[m], nt = tag_off[m + 1] - t0, nr = n_runs[m];
+    if ((start >> 24) || ((end - start) >> 24) || (k >> 40) || (sz >> 40) || (nt >> 32) || (nr >> 32)) flags[0] = 1ull;
+    rec[2 * m] = (k & 0xFFFFFFFFFFull) | start << 40; rec[2 * m + 1] = (sz & 0xFFFFFFFFFFull) | (end - start) << 40;
+    runs_tags[2 * m] = (uint32_t) nr; runs_tags[2 * m + 1] = (uint32_t) nt;
+    for (uint64_t t = 0; t < nt; ++t) {
+        const uint64_t v = tags[t0 + t]; uint8_t *d = ctags + (t0 + t) * tag_bytes;
+        if (tag_bytes < 8 && (v >> (8 * tag_bytes))) flags[0] = 1ull;
+        for (unsigned q = 0; q < tag_bytes; ++q) d[q] = (uint8_t) (v >> (8 * q));
+    }
+}
+} // namespace
+
+extern "C" int pgi_batch_upload_fixed(pgi_batch *b, const char *reads, uint64_t n_reads, uint64_t read_len) {
+    if (!b || (!reads && n_reads)) return fail(PGI_EINVAL, "null argument");
+    try {
+        DeviceGuard g(b->ix->device);
+        const uint64_t total = n_reads * read_len;
+        b->d_reads.need(total + 16); b->d_read_off.need((n_reads + 1) * 8);
+        if (total) CK(cudaMemcpyAsync(b->d_reads.p, reads, total, cudaMemcpyHostToDevice, b->stream));
+        CK(cudaMemsetAsync((char *) b->d_reads.p + total, 0, 16, b->stream));
+        iota_mul_kernel<<<grid_for(n_reads + 1, 256), 256, 0, b->stream>>>(n_reads + 1, read_len, b->d_read_off.as<uint64_t>());
+        CK(cudaGetLastError());
+        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false; b->reads_bytes = total;
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+extern "C" int pgi_batch_fetch_compact(pgi_batch *b, pgi_result_compact *out) {
+    if (!b || !out) return fail(PGI_EINVAL, "null argument");
+    if (!b->has_result) return fail(PGI_EINVAL, "no completed run on this batch");
+    try {
+        DeviceGuard g(b->ix->device);
+        const uint64_t n = b->n_reads, nm = b->n_mems, nt = b->n_tags; cudaStream_t st = b->stream;
+        const unsigned tag_bytes = (b->ix->has_tags && b->ix->tg.layout == 0 && b->ix->tg.width <= 40) ? 5u : 8u;
+        b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((nm + 1) * 16); b->d_c_rt.need((nm + 1) * 8); b->d_c_tags.need((nt + 1) * tag_bytes);
+        b->h_c_cnt.need((n + 1) * 4); b->h_c_rec.need((nm + 1) * 16); b->h_c_rt.need((nm + 1) * 8); b->h_c_tags.need((nt + 1) * tag_bytes);
+        unsigned long long *flags = b->d_ctr.as<unsigned long long>() + 14;
+        CK(cudaMemsetAsync(flags, 0, 8, st));
+        if (n) compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), flags);
+        if (nm) compact_mems_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes,
+                                                                     b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), flags);
+        CK(cudaGetLastError());
+        peek_kernel<<<1, 32, 0, st>>>((const uint64_t *) flags, b->h_ctr.as<uint64_t>() + 12, 1);
+        if (n) CK(cudaMemcpyAsync(b->h_c_cnt.p, b->d_c_cnt.p, n * 4, cudaMemcpyDeviceToHost, st));
+        if (nm) { CK(cudaMemcpyAsync(b->h_c_rec.p, b->d_c_rec.p, nm * 16, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(b->h_c_rt.p, b->d_c_rt.p, nm * 8, cudaMemcpyDeviceToHost, st)); }
+        if (nt) CK(cudaMemcpyAsync(b->h_c_tags.p, b->d_c_tags.p, nt * tag_bytes, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (b->h_ctr.as<volatile uint64_t>()[12]) return fail(PGI_EINVAL, "a value of this result does not fit the compact form (read of 2^24 bases or more, position or count too large): use pgi_find_mems");
+        std::memset(out, 0, sizeof(*out));
+        out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->tag_bytes = tag_bytes;
+        out->mem_cnt = b->h_c_cnt.as<uint32_t>(); out->rec = b->h_c_rec.as<uint64_t>(); out->runs_tags = b->h_c_rt.as<uint32_t>(); out->tags = b->h_c_tags.as<uint8_t>();
+        out->extensions = b->extensions; out->seed_lookups = b->seed_lookups; out->blocks_fetched = b->blocks_fetched;
+        return PGI_OK;
+    } PGI_CATCH
+}
+
+extern "C" int pgi_result_expand(const pgi_result_compact *c, pgi_result *out) {
+    if (!c || !out) return fail(PGI_EINVAL, "null argument");
+    std::memset(out, 0, sizeof(*out));
+    const uint64_t n = c->n_reads, nm = c->n_mems, nt = c->n_tags;
+    out->mem_off = (uint64_t *) std::malloc((n + 1) * 8); out->mems = (pgi_mem *) std::malloc((nm + 1) * sizeof(pgi_mem));
+    out->tag_off = (uint64_t *) std::malloc((nm + 1) * 8); out->tags = (uint64_t *) std::malloc((nt + 1) * 8); out->n_runs = (uint64_t *) std::malloc((nm + 1) * 8);
+    if (!out->mem_off || !out->mems || !out->tag_off || !out->tags || !out->n_runs) { pgi_result_expanded_free(out); return fail(PGI_ENOMEM, "out of host memory"); }
+    uint64_t acc = 0;
+    for (uint64_t i = 0; i < n; ++i) { out->mem_off[i] = acc; acc += c->mem_cnt[i]; }
+    out->mem_off[n] = acc;
+    uint64_t t = 0;
+    for (uint64_t m = 0; m < nm; ++m) {
+        const uint64_t w0 = c->rec[2 * m], w1 = c->rec[2 * m + 1];
+        pgi_mem &x = out->mems[m];
+        x.start = w0 >> 40; x.end = x.start + (w1 >> 40); x.bwt_start = w0 & 0xFFFFFFFFFFull; x.size = (int64_t) (w1 & 0xFFFFFFFFFFull);
+        out->n_runs[m] = c->runs_tags[2 * m]; out->tag_off[m] = t; t += c->runs_tags[2 * m + 1];
+    }
+    out->tag_off[nm] = t;
+    for (uint64_t i = 0; i < nt; ++i) { uint64_t v = 0; std::memcpy(&v, c->tags + i * c->tag_bytes, c->tag_bytes); out->tags[i] = v; }
+    out->n_reads = n; out->n_mems = nm; out->n_tags = nt; out->extensions = c->extensions; out->seed_lookups = c->seed_lookups; out->blocks_fetched = c->blocks_fetched;
+    return PGI_OK;
+}
+extern "C" void pgi_result_expanded_free(pgi_result *r) {
+    if (!r) return;
+    std::free(r->mem_off); std::free(r->mems); std::free(r->tag_off); std::free(r->tags); std::free(r->n_runs);
+    std::memset(r, 0, sizeof(*r));
+}
+
 // ------------------------------------------------------------------------------------------ one-call API
 static pgi_batch *pool_take(pgi_index *ix) {
     { std::lock_guard<std::mutex> l(ix->pool_mu); if (!ix->pool.empty()) { pgi_batch *b = ix->pool.back(); ix->pool.pop_back(); return b; } }
@@ -1082,6 +1190,33 @@ extern "C" int pgi_find_mems(pgi_index *ix, const char *reads, const uint64_t *r
 extern "C" int pgi_query_tags(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t n_reads,
                               void *cuda_stream, pgi_result *out) {
     return one_call(ix, true, reads, read_off, n_reads, 0, 0, cuda_stream, out);
+}
+
+extern "C" int pgi_find_mems_compact(pgi_index *ix, const char *reads, const uint64_t *read_off, uint64_t read_len, uint64_t n_reads,
+                                     uint64_t min_len, uint64_t min_occ, void *cuda_stream, pgi_result_compact *out) {
+    if (!ix || !out || (!reads && n_reads)) return fail(PGI_EINVAL, "null argument");
+    pgi_batch *b = pool_take(ix);
+    if (!b) return PGI_ECUDA;
+    cudaStream_t own = b->stream;
+    if (cuda_stream) b->stream = (cudaStream_t) cuda_stream;
+    int rc;
+    {   // the same three-stage pipeline as pgi_find_mems: upload | compute token | download, one of each at a time
+        std::lock_guard<std::mutex> up(ix->upload_mu);
+        rc = read_off ? pgi_batch_upload(b, reads, read_off, n_reads) : pgi_batch_upload_fixed(b, reads, n_reads, read_len);
+        if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
+    }
+    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = batch_run(b, false, min_len, min_occ); }
+    if (rc == PGI_OK) { std::lock_guard<std::mutex> down(ix->download_mu); rc = pgi_batch_fetch_compact(b, out); }
+    b->stream = own;
+    if (rc != PGI_OK) { pool_give(ix, b); return rc; }
+    out->owner = b;
+    return PGI_OK;
+}
+extern "C" void pgi_result_compact_free(pgi_result_compact *r) {
+    if (!r || !r->owner) return;
+    pgi_batch *b = (pgi_batch *) r->owner;
+    pool_give(b->ix, b);
+    std::memset(r, 0, sizeof(*r));
 }
 
 extern "C" void pgi_result_free(pgi_result *r) {

@@ -61,11 +61,9 @@ inline uint64_t fnv1a(const void *p, size_t n, uint64_t h = 0xcbf29ce484222325ul
     for (; i < n; ++i) h = (h ^ b[i]) * 0x100000001b3ull;
     return h;
 }
-inline uint64_t edge_sum(const void *p, size_t n) {
-    const size_t e = 65536;
-    if (n <= 2 * e) return fnv1a(p, n);
-    return fnv1a((const uint8_t *) p + n - e, e, fnv1a(p, e));
-}
+// Content stamp of a source file (staleness check of the cached image): FNV-1a over the WHOLE file -- it runs near memory
+// speed, and a stamp of the edges only would accept a file that was rebuilt with the same size and changed in the middle.
+inline uint64_t edge_sum(const void *p, size_t n) { return fnv1a(p, n); }
 
 // A view of a flattened index: scalars + one (pointer, bytes) pair per section. Built either over the vectors of a
 // fresh RiImage / TagImage or over a mapped image file; the uploader (pgi_capi.cu) only sees this.

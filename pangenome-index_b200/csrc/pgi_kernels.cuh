@@ -27,6 +27,8 @@ struct MemArgs {
     unsigned long long *mem_count; // MEMs appended so far (keeps counting past mem_cap)
     unsigned long long *ext_count; // FMD extensions of the reference algorithm (a seed lookup counts as its seed_k extensions)
     unsigned long long *seed_count;// seed lookups that replaced seed_k extensions each
+    unsigned long long *bad_off;   // set when a read's offsets are not ascending / leave the reads buffer (the step then fails with PGI_EINVAL)
+    uint64_t reads_bytes;          // bytes of the reads buffer
     unsigned long long *blk_count; // 64-byte run blocks fetched (bucket blocks + chunk blocks): what the kernel moves from the index
     uint64_t mem_cap;
     uint4 *mem_buf;                // 2 x uint4 per appended MEM {start, end, bwt_start, size}
@@ -134,7 +136,11 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 if (id < wq_end) {
                     rd = id; have = true; nm = 0;
                     if (OP == 0 && seed_k) stepwise = ((__ldg(a.read_flags + (id >> 5)) >> (id & 31u)) & 1u) ? 2u : 0u;
-                    const uint64_t o0 = __ldcs(a.read_off + id), o1 = __ldcs(a.read_off + id + 1);
+                    uint64_t o0 = __ldcs(a.read_off + id), o1 = __ldcs(a.read_off + id + 1);
+                    if (o1 < o0 || o1 > a.reads_bytes) {                    // offsets that are not ascending or leave the buffer: an empty
+                        if (a.bad_off) *a.bad_off = 1ull;                   // read instead of a wild address; the host reports PGI_EINVAL
+                        o0 = o1 = 0;
+                    }
                     base = o0;
                     if (OP == 0) lane_begin(L, o1 - o0, min_len, a.ix.n);
                     else {

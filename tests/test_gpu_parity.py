@@ -464,3 +464,32 @@ def test_create_from_runs_long_tag_runs_and_errors(capi):
     pos = np.arange(0, n + 1, dtype=np.uint64); assert np.array_equal(a.rank_batch(pos), b.rank_batch(pos))
     with pytest.raises(capi.PgiError): capi.Index.from_runs(np.frombuffer(b"\nAXC", dtype=np.uint8), np.ones(4, dtype=np.uint64))
     with pytest.raises(capi.PgiError): capi.Index.from_runs(np.frombuffer(b"\nACG", dtype=np.uint8), np.array([1, 0, 2, 3], dtype=np.uint64))
+
+
+def test_compact_result_equals_full_result(capi):
+    """pgi_find_mems_compact (packed on the GPU, fewer bytes across PCIe) expands to exactly pgi_find_mems' arrays; fixed-length
+    reads without an offset array and ragged reads with one."""
+    for name in ("synth_enc_compact", "xy_legacy_bytecode", "two_contig_legacy"):
+        c = get_case(name); g = capi.Index(c["ri"], c["tags"], c["layout"])
+        reads, off = datasets.sample_reads(c["text"], 3000, 150, 0.01, seed=2)
+        for ml in (20, 4):
+            F = g.find_mems(reads, off, ml, 1, text=False); C = g.find_mems_compact(reads, 150, ml, 1)
+            for k in ("n_mems", "n_tags", "extensions"): assert F[k] == C[k], k
+            for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(F[k], C[k]), k
+            assert C["wire_bytes"] < F["n_reads"] * 8 + F["n_mems"] * 48 + F["n_tags"] * 8
+        rs = datasets.ragged_reads(c["text"], seed=3); buf, o2 = orc.pack_reads(rs)
+        F = g.find_mems(buf, o2, 5, 1, text=False); C = g.find_mems_compact(buf, 0, 5, 1, read_off=o2)
+        for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(F[k], C[k]), k
+
+def test_bad_read_offsets_are_refused(capi):
+    """offsets that are not ascending must not reach the kernel as wild addresses."""
+    c = get_case("synth_enc_compact"); g = capi.Index(c["ri"], c["tags"], 0)
+    reads, off = datasets.sample_reads(c["text"], 100, 150, 0.01, seed=2)
+    bad = off.copy(); bad[50] = bad[40]
+    with pytest.raises(capi.PgiError): g.find_mems(reads, bad, 20, 1, text=False)
+    import torch                                                   # device-resident offsets: caught by the kernel, reported after the step
+    d_reads = torch.cat([torch.from_numpy(reads), torch.zeros(16, dtype=torch.uint8)]).cuda(); d_bad = torch.from_numpy(bad.astype(np.int64)).cuda()
+    b = capi.Batch(g); b.set_device_reads(d_reads.data_ptr(), d_bad.data_ptr(), 100, len(reads))
+    with pytest.raises(capi.PgiError): b.run(20, 1)
+    d_off = torch.from_numpy(off.astype(np.int64)).cuda(); b.set_device_reads(d_reads.data_ptr(), d_off.data_ptr(), 100, len(reads)); b.run(20, 1)   # the context survives
+    compare(b.fetch(text=True), orc.Index(c["ri"], c["tags"], 0).find_mems(reads, off, 20, 1), True)
