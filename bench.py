@@ -36,7 +36,7 @@ WORKLOADS = {
     # name: (ref_len, n_hap, read_len, reads_per_step, substitution rate, 1-bp indel rate, BASELINE.json config it is)
     "config4": (150_000_000, 256, 150, 2_000_000, 0.01, 0.0, "configs[3]: synthetic 256-haplotype 150 Mbp pangenome + reverse complements (random reference with N stretches, SNP 1/1000, indel 1/10000; exact BWT from the graph structure), 150 bp reads with 1 % substitutions"),
     "config3": (50_000_000, 64, 150, 2_000_000, 0.01, 0.0, "configs[2]: synthetic 64-haplotype 50 Mbp pangenome + reverse complements (random reference with N stretches, SNP 1/1000, indel 1/10000; exact BWT from the graph structure), 150 bp reads with 1 % substitutions"),
-    "long": (150_000_000, 256, 10_000, 30_000, 0.03, 0.02, "configs[4]: long-read stress, 10 kbp reads with 5 % errors (3 % substitutions + 2 % 1-bp indels) on the 256-haplotype 150 Mbp index"),
+    "long": (150_000_000, 256, 10_000, 160_000, 0.03, 0.02, "configs[4]: long-read stress, 10 kbp reads with 5 % errors (3 % substitutions + 2 % 1-bp indels) on the 256-haplotype 150 Mbp index"),
 }
 
 def parse_args():

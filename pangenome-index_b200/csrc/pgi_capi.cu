@@ -1409,10 +1409,16 @@ extern "C" char *pgi_format_text(const pgi_result *r, uint64_t first_seq, int wi
             for (auto &t : th) t.join();
         }
     } catch (const std::exception &) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
-    size_t total = 0; for (auto &p : part) total += p.size();
+    size_t total = 0; std::vector<size_t> at(nt);
+    for (unsigned k = 0; k < nt; ++k) { at[k] = total; total += part[k].size(); }
     char *buf = (char *) std::malloc(total + 1);
     if (!buf) { fail(PGI_ENOMEM, "out of host memory"); return nullptr; }
-    size_t at = 0; for (auto &p : part) { std::memcpy(buf + at, p.data(), p.size()); at += p.size(); }
+    if (nt == 1) std::memcpy(buf, part[0].data(), part[0].size());
+    else {                                                  // the pieces are copied in parallel as well (400 MB per 2 M reads)
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nt; ++k) th.emplace_back([&, k] { std::memcpy(buf + at[k], part[k].data(), part[k].size()); std::string().swap(part[k]); });
+        for (auto &t : th) t.join();
+    }
     buf[total] = 0; *len = total;
     return buf;
 }
