@@ -493,3 +493,18 @@ def test_bad_read_offsets_are_refused(capi):
     with pytest.raises(capi.PgiError): b.run(20, 1)
     d_off = torch.from_numpy(off.astype(np.int64)).cuda(); b.set_device_reads(d_reads.data_ptr(), d_off.data_ptr(), 100, len(reads)); b.run(20, 1)   # the context survives
     compare(b.fetch(text=True), orc.Index(c["ri"], c["tags"], 0).find_mems(reads, off, 20, 1), True)
+
+def test_clone_to_second_gpu(capi):
+    """a replica on ANOTHER GPU (peer copy), queried there. Needs two devices."""
+    if capi.lib().pgi_device_count() < 2: pytest.skip("one GPU visible")
+    c = get_case("synth_enc_compact"); o = orc.Index(c["ri"], c["tags"], 0); g0 = capi.Index(c["ri"], c["tags"], 0, device=0)
+    g1 = g0.clone_to(1)
+    reads, off = datasets.sample_reads(c["text"], 3000, 150, 0.01, seed=4)
+    R = o.find_mems(reads, off, 20, 1)
+    compare(g1.find_mems(reads, off, 20, 1), R, True)
+    compare(g0.find_mems(reads, off, 20, 1), R, True)
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)          # and one built from runs on device 1 directly
+    sym, ln = _runs_of_rlbwt(s["rl_bwt"])
+    b1 = capi.Index.from_runs(sym, ln, device=1)
+    r2, o2 = datasets.sample_reads(s["text"], 1000, 150, 0.01, seed=5)
+    compare(b1.find_mems(r2, o2, 20, 1), orc.Index(s["ri"]).find_mems(r2, o2, 20, 1, with_tags=False), False)
