@@ -80,7 +80,9 @@ struct Batch {
         off = p; off_cap = cap;
     }
     void clear() { n = 0; bytes = 0; reserve_off(2); off[0] = 0; }
-    void add(const char *s, size_t len) {
+    uint64_t expect = 0;                           // reads this batch will hold: the first read sizes the pinned buffers once
+    void add(const char *s, size_t len) {          // (growing them geometrically re-allocated pinned memory a dozen times per batch)
+        if (!reads_cap && expect) { reserve_reads((size_t) expect * (len + 2) + 4096); reserve_off((size_t) expect + 2); }
         reserve_reads(bytes + len + 16); reserve_off(n + 2);
         std::memcpy(reads + bytes, s, len); bytes += len; off[++n] = bytes;
     }
@@ -222,7 +224,7 @@ int main(int argc, char **argv) {
     // reader: non-empty lines -> batches (std::getline semantics: '\n' separated, no other trimming)
     std::thread reader([&] {
         std::vector<char> buf(1 << 24); std::string carry; uint64_t id = 0, seq = 1; Batch *cur = nullptr;
-        auto begin = [&]() { if (!free_q.pop(cur)) return false; cur->clear(); cur->id = id; cur->first_seq = seq; return true; };
+        auto begin = [&]() { if (!free_q.pop(cur)) return false; cur->expect = batch_reads; cur->clear(); cur->id = id; cur->first_seq = seq; return true; };
         auto line = [&](const char *s, size_t len) {
             if (!len) return;                                                 // `if (read.empty()) continue;`
             if (!cur && !begin()) return;
