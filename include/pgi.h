@@ -79,6 +79,7 @@ typedef struct {
     uint64_t has_locate;     /* the file carries samples / last / last_to_run and pgi_locate_batch works on it */
     uint64_t max_length;     /* Header::max_length: SA value = seq_id * max_length + seq_offset (r-index.hpp:424-431) */
     uint64_t seed_k;         /* K of the seed table (4^K entries: the first K backward extensions from the full interval); 0 = none */
+    uint64_t host_resident_bytes; /* out-of-core mode: bytes of the run-block array kept in pinned host memory and read over PCIe (0: all in HBM) */
     uint64_t C[8];
     uint8_t  sym_map[256];
 } pgi_index_info_t;

@@ -4,7 +4,7 @@ import ctypes, os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpgi.so")
+LIB_PATH = os.environ.get("PGI_LIB") or os.path.join(_HERE, "libpgi.so")      # PGI_LIB: the bounds-checking build (csrc/Makefile)
 _lib = None
 
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
@@ -27,7 +27,7 @@ class ResultCompact(ctypes.Structure):
 class IndexInfo(ctypes.Structure):
     _fields_ = [(k, ctypes.c_uint64) for k in ["n", "sigma", "is_encoded", "n_ref_blocks", "n_runs", "n_dev_blocks", "bucket_shift",
                                                "has_quirk_slot", "has_tags", "tag_layout", "tag_runs", "tag_items", "tag_item_width",
-                                               "tag_universe", "device_bytes", "n_crowded_buckets", "has_locate", "max_length", "seed_k"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
+                                               "tag_universe", "device_bytes", "n_crowded_buckets", "has_locate", "max_length", "seed_k", "host_resident_bytes"]] + [("C", ctypes.c_uint64 * 8), ("sym_map", ctypes.c_uint8 * 256)]
 
 class LocateResult(ctypes.Structure):
     _fields_ = [("n", ctypes.c_uint64), ("n_ids", ctypes.c_uint64), ("n_rows", ctypes.c_uint64), ("id_off", ctypes.c_void_p),
@@ -164,7 +164,7 @@ class Index:
             _ck(L.pgi_index_create(ri, len(ri) if ri else 0, tags, len(tags) if tags else 0, tag_layout, device, ctypes.byref(h)))
             self.h = h
         info = IndexInfo(); _ck(L.pgi_index_info(self.h, ctypes.byref(info)))
-        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:19]}
+        self.info = {k: getattr(info, k) for k, _ in IndexInfo._fields_[:20]}
         self.n = info.n; self.sigma = info.sigma; self.has_tags = bool(info.has_tags)
         self.C = list(info.C)[: info.sigma]; self.sym_map = bytes(info.sym_map)
     def clone_to(self, device):

@@ -82,6 +82,8 @@ struct pgi_index {
     uint4 *d_seed = nullptr; uint32_t seed_k = 0;          // seed table (pgi_core.cuh): 4^seed_k entries, built on the device at load
     uint32_t *d_desc = nullptr, *d_desc_c = nullptr;      // extension descriptors; LF-step descriptors of the whole-read search
     std::vector<void *> owned;
+    std::vector<void *> owned_host;                        // sections kept in pinned host memory (out-of-core mode)
+    uint64_t host_resident_bytes = 0;
     // sizes of the uploaded arrays, for clone
     uint64_t n_block_words = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
@@ -114,7 +116,7 @@ static void fill_info(pgi_index *ix, const ImageMeta &m, uint64_t bytes) {
         f.has_tags = 1; f.tag_layout = m.tag_layout; f.tag_runs = m.iv_k.m; f.tag_items = m.tag_n_items;
         f.tag_item_width = m.tag_width; f.tag_universe = m.iv_k.size;
     }
-    f.device_bytes = bytes; f.has_locate = m.k.locate_ok; f.max_length = m.k.max_length; f.seed_k = ix->seed_k;
+    f.device_bytes = bytes; f.host_resident_bytes = ix->host_resident_bytes; f.has_locate = m.k.locate_ok; f.max_length = m.k.max_length; f.seed_k = ix->seed_k;
     for (int i = 0; i < 8; ++i) f.C[i] = m.k.C[i];
     std::memcpy(f.sym_map, m.k.sym_map, 256);
 }
@@ -192,9 +194,23 @@ static pgi_index *upload_view(const IndexView &v, int device, size_t chunk_bytes
         cudaDeviceProp prop; CK(cudaGetDeviceProperties(&prop, device)); ix->sm_count = prop.multiProcessorCount;
         uint64_t bytes = 0;
         Stager stg; stg.init(chunk_bytes);
+        // Out-of-core mode (second half; the role of the reference's ChunkedMemoryMappedIndexManager for an
+        // index that does not fit the device): the run-block array -- by far the largest section -- stays in PINNED HOST memory,
+        // mapped into the device's address space, and the kernels read it over PCIe (zero copy) with the same code. Chosen when
+        // the section does not fit the free HBM (leaving 1/8 of it for work buffers) or when PGI_HOST_BLOCKS=1 forces it (tests).
+        // Functional, not fast: every block fetch becomes a 64-byte PCIe read.
+        size_t free_b = 0, total_b = 0; CK(cudaMemGetInfo(&free_b, &total_b));
+        const char *force = std::getenv("PGI_HOST_BLOCKS");
         auto up = [&](int s, uint64_t &n_elems) -> void * {
             const uint64_t nb = v.bytes[s]; n_elems = nb / kSectionElem[s];
             void *d = nullptr; const size_t alloc = nb ? (size_t) nb : kSectionElem[s];
+            const bool on_host = s == SEC_BLOCKS && nb && ((force && force[0] == '1') || nb > free_b - free_b / 8);
+            if (on_host) {
+                CK(cudaHostAlloc(&d, alloc, cudaHostAllocMapped | cudaHostAllocPortable)); ix->owned_host.push_back(d); ix->host_resident_bytes += alloc;
+                std::memcpy(d, v.ptr[s], (size_t) nb);
+                void *dp = nullptr; CK(cudaHostGetDevicePointer(&dp, d, 0));
+                return dp;
+            }
             CK(cudaMalloc(&d, alloc)); ix->owned.push_back(d); bytes += alloc;
             if (nb) stg.copy(d, v.ptr[s], (size_t) nb); else CK(cudaMemset(d, 0, alloc));
             return d;
@@ -202,7 +218,7 @@ static pgi_index *upload_view(const IndexView &v, int device, size_t chunk_bytes
         RiDev &d = ix->ri; uint64_t nq2 = 0;
         d.blocks = (const uint64_t *) up(SEC_BLOCKS, ix->n_block_words);
         d.q_start = (const uint64_t *) up(SEC_Q_START, ix->n_quirk); d.q_val = (const uint64_t *) up(SEC_Q_VAL, nq2);
-        d.n = m.k.n; d.n_blocks = m.k.n_blocks; d.n_quirk = m.k.n_quirk; d.bshift = m.k.bshift; d.has_quirk = m.k.has_quirk;
+        d.n = m.k.n; d.n_blocks = m.k.n_blocks; d.n_quirk = m.k.n_quirk; d.bshift = m.k.bshift; d.has_quirk = m.k.has_quirk; d.n_buckets_dbg = m.k.n_buckets;
         for (int i = 0; i < 8; ++i) d.C[i] = m.k.C[i];
         std::vector<uint32_t> desc(PGI_DESC_WORDS);      // 512 descriptors, then their 512 x 4 scan tables (pos_rank)
         for (int i = 0; i < 256; ++i) { desc[i] = m.k.desc_b[i]; desc[256 + i] = m.k.desc_f[i]; }
@@ -414,7 +430,7 @@ extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *le
         ix->consts = k; ix->has_ri = true; ix->n_block_words = n_blocks * PGI_BLOCK_WORDS;
         RiDev &d = ix->ri; std::memset(&d, 0, sizeof(d));
         d.blocks = (const uint64_t *) blocks; d.q_start = dev_alloc<uint64_t>(1, ix->owned, bytes, true); d.q_val = dev_alloc<uint64_t>(1, ix->owned, bytes, true);
-        d.n = n; d.n_blocks = n_blocks; d.n_quirk = 0; d.bshift = S; d.has_quirk = 0;
+        d.n = n; d.n_blocks = n_blocks; d.n_quirk = 0; d.bshift = S; d.has_quirk = 0; d.n_buckets_dbg = nb;
         for (int i = 0; i < 8; ++i) d.C[i] = k.C[i];
         std::memset(&ix->loc, 0, sizeof(ix->loc)); std::memset(&ix->tg, 0, sizeof(ix->tg));
         // ---- tag arrays (sdsl-compact semantics: prep_tags_from_runs / merge_tags' writer + load_compressed_tags_compact)
@@ -540,6 +556,7 @@ template <typename T> static T *clone_arr(const T *src, int src_dev, uint64_t n,
 extern "C" int pgi_index_clone_to(const pgi_index *src, int device, pgi_index **out) {
     if (!src || !out) return fail(PGI_EINVAL, "null argument");
     if (int rc = check_device(device)) return rc;
+    if (src->host_resident_bytes) return fail(PGI_EINVAL, "an out-of-core index (run blocks in host memory) is shared, not cloned: open it once per GPU");
     pgi_index *ix = nullptr;
     try {
         DeviceGuard g(device);
@@ -627,6 +644,7 @@ extern "C" void pgi_index_free(pgi_index *ix) {
     for (pgi_batch *b : ix->pool) pgi_batch_free(b);
     int prev = -1; cudaGetDevice(&prev); cudaSetDevice(ix->device);
     for (void *p : ix->owned) cudaFree(p);
+    for (void *p : ix->owned_host) cudaFreeHost(p);
     if (prev >= 0) cudaSetDevice(prev);
     delete ix;
 }

@@ -30,6 +30,7 @@ struct RiDev {
     uint64_t n, n_blocks, n_quirk;
     uint32_t bshift, has_quirk;
     uint64_t C[8];
+    uint64_t n_buckets_dbg;     // primary (bucket) blocks; chunk blocks follow (bounds-checking build only)
 };
 
 struct SparseRankDev {

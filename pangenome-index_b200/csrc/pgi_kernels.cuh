@@ -66,6 +66,13 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 //           writes and the per-lane 4 x LDS.128 reads are free of bank conflicts. 4x fewer L1 wavefronts per block.
 //           (LDG.128 + STS.128 instead of cp.async was measured as well: 17.8 ms against 16.6 ms per 2 M reads.)
 #define PGI_NOBLK 0xFFFFFFFFu
+// Bounds-checking build (make -C csrc bounds -> libpgi_bounds.so; PGI_LIB selects it in the tests): every block / chunk
+// index, staging slot and MEM slot is checked before use and a violation traps (compute-sanitizer is closed on this pool).
+#ifdef PGI_BOUNDS
+#define PGI_CHECK(cond) do { if (!(cond)) { printf("PGI_BOUNDS violated: %s (line %d)\n", #cond, __LINE__); __trap(); } } while (0)
+#else
+#define PGI_CHECK(cond) do { } while (0)
+#endif
 // 16-byte global -> shared copy, skipped (predicated off inside the asm: no branch, no address re-derivation) when blk == PGI_NOBLK.
 __device__ __forceinline__ void cp_async16_if(uint32_t saddr, const void *g, uint32_t blk) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\t@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}" ::"r"(saddr), "l"(g), "r"(blk) : "memory");
@@ -180,6 +187,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     fits = k < a.part_cap; slot = (unsigned long long) part * a.part_cap + k;
                 } else { slot = atomicAdd(a.mem_count, 1ull); fits = slot < a.mem_cap; }
                 if (fits) {
+                    PGI_CHECK(slot < (a.part_cap ? a.part_cap * PGI_SLOT_PARTS : a.mem_cap)); PGI_CHECK(rd < a.n_reads);
                     __stcs(a.mem_buf + 2 * slot, make_uint4(L.x, 0u, L.j, 0u));
                     __stcs(a.mem_buf + 2 * slot + 1, make_uint4((uint32_t) L.b.k, (uint32_t) (L.b.k >> 32), (uint32_t) (uint64_t) L.b.s, (uint32_t) ((uint64_t) L.b.s >> 32)));
                     __stcs(a.mem_key + slot, ((uint64_t) rd << 32) | nm);
@@ -216,6 +224,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         const bool has_sym = need && L.j < L.len;
         if (has_sym) {
             const uint64_t o = base + L.j;
+            PGI_CHECK(o < a.reads_bytes);
             if ((o >> 3) != cwi) {
                 cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
                 if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
@@ -272,6 +281,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
+            PGI_CHECK(b1 == PGI_NOBLK || b1 < a.ix.n_buckets_dbg); PGI_CHECK(b2 == PGI_NOBLK || b2 < a.ix.n_buckets_dbg);
             coop_issue(b1, b2);
             {
                 const unsigned nb = __popc(__ballot_sync(FULL, b1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, b2 != PGI_NOBLK));
@@ -281,6 +291,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             if (OP == 0 && seed_k && __any_sync(FULL, cand)) {
                 if (cand) {
                     const uint32_t sidx = seed_index_packed(sc0, sc1, base + L.j + 1u - seed_k, seed_k);
+                    PGI_CHECK(sidx < (1u << (2u * seed_k))); PGI_CHECK(base + L.j + 1u >= seed_k && base + L.j < a.reads_bytes);
                     seed_ok = true;
                     // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
                     // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
@@ -309,6 +320,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
                 if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
                     __syncwarp();                             // every lane has read its directory words
+                    PGI_CHECK(c1 == PGI_NOBLK || (c1 >= a.ix.n_buckets_dbg && c1 < a.ix.n_blocks)); PGI_CHECK(c2 == PGI_NOBLK || (c2 >= a.ix.n_buckets_dbg && c2 < a.ix.n_blocks));
                     const unsigned nc = __popc(__ballot_sync(FULL, c1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, c2 != PGI_NOBLK));
                     if (lane == 0) s_blk[threadIdx.x >> 5] += nc;
                     coop_fetch(c1, c2);

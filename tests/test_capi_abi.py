@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
 def test_structs_match_header_layout():
     capi = load_package().capi
     assert ctypes.sizeof(capi.Result) == 12 * 8                 # pgi_result: 3 counts, 5 pointers, extensions, seed_lookups, blocks_fetched, owner
-    assert ctypes.sizeof(capi.IndexInfo) == 19 * 8 + 8 * 8 + 256
+    assert ctypes.sizeof(capi.IndexInfo) == 20 * 8 + 8 * 8 + 256
     assert ctypes.sizeof(capi.LocateResult) == 7 * 8
 
 def test_product_does_not_link_the_oracle():

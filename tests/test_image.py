@@ -88,3 +88,21 @@ def test_index_from_image_equals_index_from_files(tmp_path, case):
             assert all(np.array_equal(x, y) for x, y in zip(la, lb))
         b.close()
     a.close()
+
+@pytest.mark.gpu
+def test_out_of_core_run_blocks_in_host_memory(monkeypatch):
+    """SURVEY.md section 8 f4 (second half): with the run-block array kept in pinned host memory and read over PCIe
+    (PGI_HOST_BLOCKS=1 forces what an index larger than the free HBM triggers by itself) every query answers the same."""
+    import orc, datasets
+    capi = load_package().capi
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    reads, off = datasets.sample_reads(s["text"], 4000, 150, 0.01, seed=3)
+    R = orc.Index(s["ri"], s["tags0"], 0).find_mems(reads, off, 20, 1)
+    monkeypatch.setenv("PGI_HOST_BLOCKS", "1")
+    g = capi.Index(s["ri"], s["tags0"], 0)
+    assert g.info["host_resident_bytes"] == g.info["n_dev_blocks"] * 64
+    G = g.find_mems(reads, off, 20, 1)
+    assert G["text"] == R["text"] and np.array_equal(G["mems"], R["mems"]) and np.array_equal(G["tags"], R["tags"])
+    with pytest.raises(capi.PgiError): g.clone_to(0)
+    monkeypatch.delenv("PGI_HOST_BLOCKS")
+    assert capi.Index(s["ri"], s["tags0"], 0).info["host_resident_bytes"] == 0
