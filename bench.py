@@ -269,7 +269,8 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "find_mems reads/s (150bp, MEM + tag query)", "value": rate, "unit": "reads/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int64", "data": "synthetic",
-            "config": {"workload": w.name, "facts": w.facts, "reads_per_step": n, "read_len": L, "min_len": args.min_len, "min_occ": args.min_occ, "note": note},
+            "config": {"workload": w.name, "workload_key": args.workload, "facts": w.facts, "reads_per_step_per_gpu": args.reads_per_step, "read_len": L, "substitution_rate": args.sub, "indel_rate": args.indel,
+                       "min_len": args.min_len, "min_occ": args.min_occ, "sample_reads_per_step": n, "note": note},
             "cpu_baseline": {"value": rate, "unit": "reads/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": rate, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit_json(line)
