@@ -51,3 +51,18 @@ def test_structural_bwt_equals_suffix_array_bwt(ref_len, n_hap, seed, snp, indel
     bad = np.nonzero(gv != val)[0]
     assert len(bad) == 0, "first tag mismatch at row %d" % bad[0]
     assert (np.asarray(d["rl_sym"])[1:] != np.asarray(d["rl_sym"])[:-1]).all()          # maximal runs
+
+def test_sampled_reads_come_from_the_haplotypes():
+    """Error-free reads must occur in the explicit text (both strands, through SNPs / insertions / deletions); reads with
+    substitutions differ from their origin in about the requested fraction of positions."""
+    pkg = load_package(); pg = pkg.pangraph
+    g = pg.make_graph(30000, 6, 9, snp=1 / 100, indel=1 / 300, n_stretch=2)
+    _, strands = pg.prepare(30000, 6, graph=g, device="cpu")
+    seqs, _ = explicit(pg, g); text = b"\n".join(seqs)
+    r = pg.sample_reads(strands, 1500, 150, 0.0, seed=1).numpy()
+    assert all(r[i].tobytes() in text for i in range(len(r)))
+    assert len({r[i].tobytes() for i in range(len(r))}) > 1400
+    e = pg.sample_reads(strands, 1500, 150, 0.02, seed=1).numpy()              # same seed: same origins, 2 % substitutions on top
+    frac = (e != r).mean(); assert 0.012 < frac < 0.03
+    long = pg.sample_reads(strands, 50, 2000, 0.03, seed=2, indel=0.02)
+    assert long.shape == (50, 2000) and set(np.unique(long.numpy())) <= set(b"ACGTN")
