@@ -182,18 +182,13 @@ def make_workload(args, dev_index, rank, world=1, dist=None, need_index=True):
     prepared = pg.prepare(args.ref_len, args.n_hap, seed=3, device=dev_index, log=lg)      # every rank: the graph (reads are sampled from it)
     g = prepared[0]
     t1 = time.time()
+    runs = None
     if rank == 0:
-        d = pg.build(args.ref_len, args.n_hap, prepared=prepared, log=lg); runs = d["dev_runs"]; del d
-        meta = torch.tensor([len(runs["sym"]), len(runs["tag_val"])], dtype=torch.int64, device=dev)
-    else:
-        runs = None; meta = torch.zeros(2, dtype=torch.int64, device=dev)
-    bcast_s = 0.0
+        d = pg.build(args.ref_len, args.n_hap, prepared=prepared, log=lg, host=False); runs = d["dev_runs"]; del d
+    bcast_s = 0.0; bcast_bytes = 0
     if world > 1:
-        dist.broadcast(meta, 0); torch.cuda.synchronize(); tb = time.time()
-        if rank != 0:
-            runs = dict(sym=torch.empty(int(meta[0]), dtype=torch.uint8, device=dev), len=torch.empty(int(meta[0]), dtype=torch.int64, device=dev),
-                        tag_val=torch.empty(int(meta[1]), dtype=torch.int64, device=dev), tag_len=torch.empty(int(meta[1]), dtype=torch.int64, device=dev))
-        for k in ("sym", "len", "tag_val", "tag_len"): dist.broadcast(runs[k], 0)
+        torch.cuda.synchronize(); dist.barrier(); tb = time.time()
+        runs, bcast_bytes = pkg.sharding.broadcast_runs(runs, dev)
         torch.cuda.synchronize(); bcast_s = time.time() - tb
     build_s = time.time() - t1
     w.host_runs = lambda: pg.host_runs(runs)
@@ -204,7 +199,7 @@ def make_workload(args, dev_index, rank, world=1, dist=None, need_index=True):
     w.reads = torch.stack([pg.sample_reads(prepared[1], n, L, args.sub, 4 + 97 * rank + 7 * i, indel=args.indel) for i in range(pool)])
     w.runs = runs
     w.facts = {"n": n_bwt, "r": int(len(runs["sym"])), "sequences": 2 * g.H, "haplotypes": g.H, "reference_bp": g.L, "sites": g.S, "tag_runs": int(len(runs["tag_val"])),
-               "graph_and_bwt_s": round(build_s - bcast_s, 1), "nccl_broadcast_of_runs_s": round(bcast_s, 2), "runs_broadcast_bytes": int(sum(v.numel() * v.element_size() for v in runs.values())) if world > 1 else 0,
+               "graph_and_bwt_s": round(build_s - bcast_s, 1), "nccl_broadcast_of_runs_s": round(bcast_s, 3), "runs_broadcast_bytes": int(bcast_bytes),
                "index_from_runs_on_gpu_s": round(w.index_create_s, 2), "prep_s": round(time.time() - t0, 1)}
     w.name = WORKLOADS[args.workload][6] if args.nominal else ("%s at a NON-NOMINAL size: %d haplotypes x %.1f Mbp" % (args.workload, args.n_hap, args.ref_len / 1e6))
     w.ri = None

@@ -447,7 +447,7 @@ def prepare(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, **kw):
     if log: log("pangraph: haplotype orders at every site (%.1fs)" % (time.time() - t0))
     return g, strands
 
-def build(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, prepared=None, **kw):
+def build(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, prepared=None, host=True, **kw):
     """-> dict(rl_sym uint8, rl_len uint64, tag_val uint64, tag_len uint64 (numpy), n, n_seq, graph, strands, dev_runs)
     Sequences are hap0, rc(hap0), hap1, rc(hap1), ... each followed by its own end marker (written '\\n'), as in synth.py."""
     import time
@@ -459,9 +459,9 @@ def build(ref_len, n_hap, seed=3, device="cpu", log=None, graph=None, prepared=N
     del recs
     n_rec = len(R["hi"])
     if log: log("pangraph: %d records, sorting (%.1fs)" % (n_rec, time.time() - t0))
-    return _assemble(R, strands, g, dev, log, t0)
+    return _assemble(R, strands, g, dev, log, t0, host)
 
-def _assemble(R, strands, g, dev, log, t0):
+def _assemble(R, strands, g, dev, log, t0, host=True):
     import time
     # stable LSD sort: sub, then lo, then hi
     perm = torch.argsort(R["sub"], stable=True)
@@ -487,7 +487,7 @@ def _assemble(R, strands, g, dev, log, t0):
     byte_of = torch.as_tensor(BYTE_OF, device=dev)
     dev_runs = dict(sym=byte_of[sym].contiguous(), len=slen.contiguous(), tag_val=tv.contiguous(), tag_len=tl.contiguous())
     out = dict(n=n, n_seq=2 * g.H, graph=g, strands=strands, dev_runs=dev_runs, r=len(sym), n_tag_runs=len(tv))
-    out.update(host_runs(dev_runs))
+    if host: out.update(host_runs(dev_runs))            # numpy copies (7 GB for config 4): only where the CPU tools need them
     return out
 
 def host_runs(dev_runs):

@@ -64,3 +64,24 @@ def find_mems_sharded(compute, reads, read_off, min_len, min_occ, group=None, ds
     gathered = [None] * world if rank == dst else None
     dist.gather_object(local, gathered, dst=dst, group=group)
     return merge_results(gathered) if rank == dst else None
+
+
+RUN_ARRAYS = (("sym", "uint8"), ("len", "int64"), ("tag_val", "int64"), ("tag_len", "int64"))
+
+def broadcast_runs(runs, device, src=0, group=None):
+    """The index is built ONCE per node: rank `src` holds the run-length BWT (`sym`, `len`) and the run-length tag array
+    (`tag_val`, `tag_len`) as tensors on its device, every other rank passes None; all ranks return the four tensors on
+    `device` (NCCL over NVLink on the GPU box, gloo in the CPU tests). Each rank then constructs its own replica from them
+    (pgi_index_create_from_runs). -> (runs dict, bytes received per rank)"""
+    import torch, torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return runs, 0
+    rank = dist.get_rank(group)
+    meta = torch.zeros(2, dtype=torch.int64, device=device)
+    if rank == src: meta[0] = runs["sym"].numel(); meta[1] = runs["tag_val"].numel()
+    dist.broadcast(meta, src, group=group)
+    n_runs, n_tag = int(meta[0]), int(meta[1])
+    if rank != src:
+        runs = {k: torch.empty(n_runs if k in ("sym", "len") else n_tag, dtype=getattr(torch, dt), device=device) for k, dt in RUN_ARRAYS}
+    for k, _ in RUN_ARRAYS: dist.broadcast(runs[k], src, group=group)
+    return runs, sum(runs[k].numel() * runs[k].element_size() for k, _ in RUN_ARRAYS)

@@ -71,3 +71,32 @@ def test_world_size_2_gloo_equals_single_process():
     assert all(p.exitcode == 0 for p in procs)
     for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(got[k], whole[k]), k
     assert got["n_reads"] == whole["n_reads"] == len(rs) and got["n_mems"] == whole["n_mems"] > 0
+
+
+def _bcast_worker(rank, world, port, q):
+    import torch, torch.distributed as dist
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from conftest import load_package as lp
+    pkg = lp(); sharding = pkg.sharding
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    runs = None
+    if rank == 0:
+        d = pkg.pangraph.build(4000, 5, seed=2, device="cpu", snp=1 / 100, indel=1 / 300, n_stretch=2); runs = d["dev_runs"]
+    got, nbytes = sharding.broadcast_runs(runs, torch.device("cpu"))
+    q.put((rank, {k: v.numpy().copy() for k, v in got.items()}, nbytes))
+    dist.barrier(); dist.destroy_process_group()
+
+def test_world_size_2_gloo_broadcast_of_runs():
+    """bench.py's "index built once per node": rank 0 derives the run-length BWT + tag runs, every rank receives them."""
+    pkg = load_package()
+    want = pkg.pangraph.build(4000, 5, seed=2, device="cpu", snp=1 / 100, indel=1 / 300, n_stretch=2)["dev_runs"]
+    ctx = mp.get_context("spawn"); q = ctx.Queue(); port = free_port()
+    procs = [ctx.Process(target=_bcast_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    got = dict((r, (a, b)) for r, a, b in (q.get(timeout=240) for _ in range(2)))
+    [p.join(timeout=120) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    for r in (0, 1):
+        for k in ("sym", "len", "tag_val", "tag_len"): assert np.array_equal(got[r][0][k], want[k].numpy()), (r, k)
+        assert got[r][1] == sum(v.numel() * v.element_size() for v in want.values())
