@@ -108,3 +108,52 @@ def test_gpu_tag_universe_beyond_2_32(capi):
         nr, tvv = o.tag_query(int(st[i]), int(en[i]))
         a, b = G["tag_off"][i], G["tag_off"][i + 1]
         assert G["n_runs"][i] == nr and np.array_equal(G["tags"][a:b], tvv), i
+
+@pytest.mark.gpu
+def test_gpu_nominal_config3_properties(capi):
+    """BASELINE config 3 at NOMINAL size (64 haplotypes x 50 Mbp + reverse complements, n = 6.4e9, built from the graph's
+    structure on the GPU): size-independent properties of a 400 000-read batch, and every sampled MEM's interval recomputed
+    through an independent path -- character by character with pgi_extend_batch (lane-private block loads, no seed table, no
+    cooperative fetch) -- must equal what the MEM kernel reported; each MEM is right-maximal; a second run is identical."""
+    import torch
+    pkg = load_package(); pg = pkg.pangraph
+    d = pg.build(50_000_000, 64, seed=3, device=0, host=False)
+    assert d["n"] > 6_300_000_000
+    r = d["dev_runs"]; g = capi.Index.from_runs(r["sym"], r["len"], r["tag_val"], r["tag_len"], device=0)
+    n = g.info["n"]; assert n == d["n"] and g.info["has_tags"] == 1
+    N, L, ML = 400_000, 150, 20
+    reads = pg.sample_reads(d["strands"], N, L, 0.01, seed=4).reshape(-1).cpu().numpy(); off = np.arange(N + 1, dtype=np.uint64) * np.uint64(L)
+    del d, r; torch.cuda.empty_cache()
+    G = g.find_mems(reads, off, ML, 1, text=False)
+    G2 = g.find_mems(reads, off, ML, 1, text=False)
+    for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(G[k], G2[k]), k           # idempotent
+    m = G["mems"]; per_read = np.diff(G["mem_off"].astype(np.int64)); rid = np.repeat(np.arange(N), per_read)
+    assert G["n_mems"] > N and (m[:, 1] - m[:, 0] >= ML).all() and (m[:, 1] <= L).all() and (m[:, 3].astype(np.int64) > 0).all()
+    assert (m[:, 2] + m[:, 3] <= n).all() and (m[:, 2] >= (1 << 32)).sum() > 1000
+    same = rid[1:] == rid[:-1]; assert (m[1:, 0][same] > m[:-1, 0][same]).all()                                  # discovery order
+    t0 = G["tag_off"].astype(np.int64); assert (np.diff(t0) >= 1).all() and (np.diff(t0) <= G["n_runs"].astype(np.int64)).all()
+    tg = G["tags"]; inner = np.ones(len(tg), dtype=bool); inner[t0[:-1]] = False
+    assert (tg[1:][inner[1:]] > tg[:-1][inner[1:]]).all()                                                        # sorted unique per MEM
+    rng = np.random.default_rng(1); pick = rng.choice(G["n_mems"], 4000, replace=False)
+    iv = np.zeros((len(pick), 3), dtype=np.uint64); iv[:, 2] = n
+    st = m[pick, 0].astype(np.int64); en = m[pick, 1].astype(np.int64); base = rid[pick].astype(np.int64) * L
+    alive = np.ones(len(pick), dtype=bool)
+    for step in range(int((en - st).max())):
+        pos = en - 1 - step; act = pos >= st
+        if not act.any(): break
+        sym = np.where(act, reads[base + np.maximum(pos, 0)], ord("A")).astype(np.uint8)
+        out = g.extend_batch(iv, sym, np.zeros(len(pick), dtype=np.uint8))
+        iv[act] = out[act]
+    assert np.array_equal(iv[:, 0], m[pick, 2]) and np.array_equal(iv[:, 2], m[pick, 3])                          # same interval, independent path
+    more = en < L                                                                                                  # right-maximal: one more character fails
+    rev = np.zeros((len(pick), 3), dtype=np.uint64)                                                               # forward extension needs the reverse interval: rebuild it by a forward walk
+    rev[:, 2] = n
+    for step in range(int((en - st).max())):
+        pos = st + step; act = pos < en
+        sym = np.where(act, reads[base + np.minimum(pos, L - 1)], ord("A")).astype(np.uint8)
+        out = g.extend_batch(rev, sym, np.ones(len(pick), dtype=np.uint8))
+        rev[act] = out[act]
+    assert np.array_equal(rev[:, 0], m[pick, 2]) and np.array_equal(rev[:, 2], m[pick, 3])                        # forward walk reaches the same interval
+    nxt = np.where(more, reads[base + np.minimum(en, L - 1)], ord("A")).astype(np.uint8)
+    out = g.extend_batch(rev, nxt, np.ones(len(pick), dtype=np.uint8))
+    assert (out[more, 2] == 0).all()
