@@ -149,6 +149,16 @@ int pgi_extend_batch(pgi_index *, uint64_t n, const pgi_bi_interval *in, const u
                      const uint8_t *dir, pgi_bi_interval *out);
 /* Batched FastLocate::rank_at_cached_encoded (src/r-index.cpp:619-641): out8[8*i + j] = R(pos[i])[j], j < sigma. */
 int pgi_rank_batch(pgi_index *, uint64_t n, const uint64_t *pos, uint64_t *out8);
+/* pgi_rank_batch without any device allocation. No counterpart in the reference: added
+ * for callers that may not call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it). Same arguments and results as pgi_rank_batch (host buffers), but the device staging of positions and
+ * rank vectors is a static __device__ array of 72 * PGI_RANK_NOALLOC_MAX bytes (4.5 MiB) that every GPU loading libpgi.so
+ * holds until the process exits; the call issues no cudaMalloc / cudaFree / allocating library routine.
+ * n > PGI_RANK_NOALLOC_MAX fails with PGI_EINVAL (split the batch, or call pgi_rank_batch). All calls share the one
+ * array: calls are serialised inside a process by a mutex and complete before returning; work of other origin that
+ * would touch the array while a call is on the GPU races with it. */
+#define PGI_RANK_NOALLOC_MAX 65536
+int pgi_rank_batch_noalloc(pgi_index *, uint64_t n, const uint64_t *pos, uint64_t *out8);
 /* Batched TagArray::query_compressed_compact (src/tag_arrays.cpp:856-890) / query_compressed (:780-854),
  * chosen by the layout the index was created with. Intervals are [start[i], end[i]] inclusive.
  * Result: tag_off / tags / n_runs of `out` (n_mems = n; mems, mem_off are NULL). Free with pgi_result_free. */

@@ -6,13 +6,14 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PGI_LIB") or os.path.join(_HERE, "libpgi.so")      # PGI_LIB: the bounds-checking build (csrc/Makefile)
 _lib = None
+RANK_NOALLOC_MAX = 65536      # PGI_RANK_NOALLOC_MAX of include/pgi.h
 
 SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_clone_to", "pgi_index_free", "pgi_index_info",
            "pgi_extend_batch", "pgi_rank_batch", "pgi_tag_query_batch", "pgi_find_mems", "pgi_result_free", "pgi_batch_create",
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
            "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
            "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs", "pgi_l2_fetch_granularity", "pgi_find_mems_compact", "pgi_result_compact_free",
-           "pgi_result_expand", "pgi_result_expanded_free", "pgi_batch_upload_fixed", "pgi_batch_fetch_compact"]
+           "pgi_result_expand", "pgi_result_expanded_free", "pgi_batch_upload_fixed", "pgi_batch_fetch_compact", "pgi_rank_batch_noalloc"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -67,6 +68,7 @@ def lib():
         L.pgi_index_info.argtypes = [vp, ctypes.POINTER(IndexInfo)]
         L.pgi_extend_batch.argtypes = [vp, u64, vp, vp, vp, vp]
         L.pgi_rank_batch.argtypes = [vp, u64, vp, vp]
+        L.pgi_rank_batch_noalloc.argtypes = [vp, u64, vp, vp]
         L.pgi_tag_query_batch.argtypes = [vp, u64, vp, vp, ctypes.POINTER(Result)]
         L.pgi_find_mems.argtypes = [vp, vp, vp, u64, u64, u64, vp, ctypes.POINTER(Result)]
         L.pgi_result_free.argtypes = [ctypes.POINTER(Result)]
@@ -184,6 +186,11 @@ class Index:
     def rank_batch(self, pos):
         pos = np.ascontiguousarray(pos, dtype=np.uint64); out = np.zeros((len(pos), 8), dtype=np.uint64)
         _ck(lib().pgi_rank_batch(self.h, len(pos), pos.ctypes.data, out.ctypes.data))
+        return out
+    def rank_batch_noalloc(self, pos):
+        """pgi_rank_batch_noalloc: static device scratch, at most RANK_NOALLOC_MAX positions per call."""
+        pos = np.ascontiguousarray(pos, dtype=np.uint64); out = np.zeros((len(pos), 8), dtype=np.uint64)
+        _ck(lib().pgi_rank_batch_noalloc(self.h, len(pos), pos.ctypes.data, out.ctypes.data))
         return out
     def tag_query_batch(self, start, end):
         start = np.ascontiguousarray(start, dtype=np.uint64); end = np.ascontiguousarray(end, dtype=np.uint64)

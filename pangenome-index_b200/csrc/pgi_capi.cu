@@ -1379,6 +1379,57 @@ extern "C" int pgi_rank_batch(pgi_index *ix, uint64_t n, const uint64_t *pos, ui
     } PGI_CATCH
 }
 
+// ------------------------------------------------------------------------------------------ allocation-free rank batch
+// pgi_rank_batch for callers that may not allocate device memory (code under CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc). The two staging buffers pgi_rank_batch takes from cudaMalloc (positions in, rank vectors out)
+// live in ONE file-scope __device__ array instead, which every GPU that loads libpgi.so holds until the process exits:
+//   bytes [0, 8 * MAX)          positions
+//   bytes [8 * MAX, 72 * MAX)   rank vectors, 8 u64 per position
+// In host code `g_rank_scratch` is only the host-side stand-in of the symbol: its device address is taken once per device,
+// with that device current, by cudaGetSymbolAddress, and that pointer is what the kernel receives. Every call shares the
+// array (it keeps the previous call's contents; rank_kernel writes all 8 words of every position below n and nothing is
+// read beyond them, so nothing has to start at zero, but the call clears the part of the output it is about to use anyway so
+// that a kernel that did not run cannot pass for one that did). Calls are serialised inside one process by a mutex; calls
+// from different processes do not share the array (one copy per context).
+static __device__ __align__(256) unsigned char g_rank_scratch[(size_t) PGI_RANK_NOALLOC_MAX * 72];
+static_assert(((size_t) PGI_RANK_NOALLOC_MAX * 8) % 256 == 0, "the output half of the scratch array stays 256-byte aligned");
+
+extern "C" int pgi_rank_batch_noalloc(pgi_index *ix, uint64_t n, const uint64_t *pos, uint64_t *out8) {
+    static std::mutex mu;
+    static unsigned char *scratch_of[64];                   // device address of g_rank_scratch, per device
+    if (!ix || ((!pos || !out8) && n)) return fail(PGI_EINVAL, "null argument");
+    if (!ix->has_ri) return fail(PGI_EINVAL, "index was created without an r-index (tags only)");
+    if (n > (uint64_t) PGI_RANK_NOALLOC_MAX)
+        return fail(PGI_EINVAL, "pgi_rank_batch_noalloc: n = " + std::to_string(n) + " exceeds PGI_RANK_NOALLOC_MAX = " +
+                    std::to_string((uint64_t) PGI_RANK_NOALLOC_MAX) + " (static scratch); split the batch or call pgi_rank_batch");
+    if (ix->device < 0 || ix->device >= 64) return fail(PGI_EINVAL, "pgi_rank_batch_noalloc: device index beyond 63");
+    if (!n) return PGI_OK;
+    std::lock_guard<std::mutex> lock(mu);
+    int prev = -1; cudaGetDevice(&prev);
+    cudaError_t e = cudaSetDevice(ix->device);
+    const char *what = "cudaSetDevice";
+    if (e == cudaSuccess && !scratch_of[ix->device]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_rank_scratch); what = "cudaGetSymbolAddress(g_rank_scratch)";
+        if (e == cudaSuccess) scratch_of[ix->device] = (unsigned char *) p;
+    }
+    if (e == cudaSuccess) {
+        unsigned char *base = scratch_of[ix->device];
+        uint64_t *d_pos = (uint64_t *) base, *d_out = (uint64_t *) (base + (size_t) PGI_RANK_NOALLOC_MAX * 8);
+        SlotTable st; for (int i = 0; i < 8; ++i) st.s[i] = ix->consts.slot[i]; st.sigma = (uint32_t) ix->consts.sigma;
+        e = cudaMemcpy(d_pos, pos, n * 8, cudaMemcpyHostToDevice); what = "cudaMemcpy(positions)";
+        if (e == cudaSuccess) { e = cudaMemset(d_out, 0xff, n * 64); what = "cudaMemset(rank vectors)"; }
+        if (e == cudaSuccess) {
+            rank_kernel<<<grid_for(n, 128), 128>>>(ix->ri, st, n, d_pos, d_out);
+            e = cudaGetLastError(); what = "rank_kernel launch";
+        }
+        if (e == cudaSuccess) { e = cudaMemcpy(out8, d_out, n * 64, cudaMemcpyDeviceToHost); what = "cudaMemcpy(rank vectors)"; }
+    }
+    if (prev >= 0) cudaSetDevice(prev);
+    if (e != cudaSuccess) return fail(PGI_ECUDA, std::string("pgi_rank_batch_noalloc: ") + what + ": " + cudaGetErrorString(e));
+    return PGI_OK;
+}
+
 // ------------------------------------------------------------------------------------------ text + microbenchmark
 static inline void put_u64(std::string &s, uint64_t v) {
     char buf[24]; int i = 24;
