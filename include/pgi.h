@@ -245,9 +245,17 @@ int pgi_batch_upload(pgi_batch *, const char *reads, const uint64_t *read_off, u
  * total_bytes = d_read_off[n_reads], the byte length of the reads -- the seed pre-pass packs exactly that many bytes). */
 int pgi_batch_set_device_reads(pgi_batch *, const char *d_reads, const uint64_t *d_read_off,
                                uint64_t n_reads, uint64_t total_bytes);
-/* Run MEM finding + tag lookup on the staged reads; results stay in HBM. Returns after the last kernel
- * has completed (it has to read sizes back to size the next stage). */
+/* Run MEM finding + tag lookup on the staged reads (the body of the read loop, src/find_mems.cpp:94-139, for the whole
+ * batch); results stay in HBM. Returns after the last kernel has completed. */
 int pgi_batch_run(pgi_batch *, uint64_t min_len, uint64_t min_occ);
+/* The same step in two halves, for callers that keep several batches in flight on one GPU from one host thread:
+ * pgi_batch_run_async queues every kernel of the step on the batch's stream and returns at once (the step is one
+ * stream-ordered sequence; nothing on the host is waited for); pgi_batch_wait blocks until the step has finished, fetches
+ * its counters and -- rarely -- runs a step again whose buffers did not fit. pgi_batch_run = the two back to back. Steps
+ * of different batches (different streams) overlap on the GPU: the next step's persistent MEM kernel fills the SMs that the
+ * previous one's last reads leave idle. The reads of a batch must stay untouched between the two calls. */
+int pgi_batch_run_async(pgi_batch *, uint64_t min_len, uint64_t min_occ);
+int pgi_batch_wait(pgi_batch *);
 /* Device pointers of the last run's result. */
 int pgi_batch_device_result(pgi_batch *, pgi_result *out);
 /* Copy the last run's result into the batch's pinned host buffers and wait for it. */

@@ -13,7 +13,7 @@ SYMBOLS = ["pgi_last_error", "pgi_device_count", "pgi_index_create", "pgi_index_
            "pgi_batch_free", "pgi_batch_upload", "pgi_batch_set_device_reads", "pgi_batch_run", "pgi_batch_device_result",
            "pgi_batch_fetch", "pgi_batch_stage_ms", "pgi_format_text", "pgi_free", "pgi_query_tags", "pgi_batch_run_query_tags", "pgi_format_query_tags_text", "pgi_locate_batch", "pgi_locate_result_free", "pgi_random_access_gbs", "pgi_host_alloc", "pgi_host_free",
            "pgi_image_write", "pgi_image_info", "pgi_image_source_sum", "pgi_index_open_image", "pgi_index_create_from_runs", "pgi_l2_fetch_granularity", "pgi_find_mems_compact", "pgi_result_compact_free",
-           "pgi_result_expand", "pgi_result_expanded_free", "pgi_batch_upload_fixed", "pgi_batch_fetch_compact", "pgi_rank_batch_noalloc"]
+           "pgi_result_expand", "pgi_result_expanded_free", "pgi_batch_upload_fixed", "pgi_batch_fetch_compact", "pgi_rank_batch_noalloc", "pgi_batch_run_async", "pgi_batch_wait"]
 
 class Result(ctypes.Structure):
     _fields_ = [("n_reads", ctypes.c_uint64), ("n_mems", ctypes.c_uint64), ("n_tags", ctypes.c_uint64),
@@ -77,6 +77,8 @@ def lib():
         L.pgi_batch_upload.argtypes = [vp, vp, vp, u64]
         L.pgi_batch_set_device_reads.argtypes = [vp, vp, vp, u64, u64]
         L.pgi_batch_run.argtypes = [vp, u64, u64]
+        L.pgi_batch_run_async.argtypes = [vp, u64, u64]
+        L.pgi_batch_wait.argtypes = [vp]
         L.pgi_batch_device_result.argtypes = [vp, ctypes.POINTER(Result)]
         L.pgi_batch_fetch.argtypes = [vp, ctypes.POINTER(Result)]
         L.pgi_batch_stage_ms.argtypes = [vp, ctypes.POINTER(ctypes.c_double * 8)]
@@ -274,6 +276,10 @@ class Batch:
         _ck(lib().pgi_batch_set_device_reads(self.h, d_reads_ptr, d_off_ptr, n_reads, total_bytes))
     def run(self, min_len, min_occ):
         _ck(lib().pgi_batch_run(self.h, min_len, min_occ))
+    def run_async(self, min_len, min_occ):
+        _ck(lib().pgi_batch_run_async(self.h, min_len, min_occ))
+    def wait(self):
+        _ck(lib().pgi_batch_wait(self.h))
     def run_query_tags(self):
         _ck(lib().pgi_batch_run_query_tags(self.h))
     def stage_ms(self):

@@ -88,6 +88,9 @@ struct pgi_index {
     uint64_t n_block_words = 0, n_quirk = 0, n_iv_dir = 0, n_iv_low = 0, n_starts = 0, n_words = 0, n_stream = 0;
     pgi_index_info_t info;
     std::mutex compute_mu;                                  // see pgi_find_mems
+    // How the steps that concurrent callers / in-flight batches enqueue on this index share the GPU (batch_enqueue):
+    // ev_end = end of the step enqueued last, ev_k1 = end of its fmd_mem_kernel launch; written under compute_mu.
+    cudaEvent_t ev_end = nullptr, ev_k1 = nullptr; bool ev_end_set = false, ev_k1_set = false;
     std::mutex upload_mu, download_mu;                      // one bulk copy per direction at a time (pgi_find_mems)
     std::mutex pool_mu; std::vector<pgi_batch *> pool;     // idle batch contexts used by pgi_find_mems
     int sm_count = 0;
@@ -619,6 +622,10 @@ struct pgi_batch {
     uint64_t n_mems = 0, n_tags = 0, extensions = 0, seed_lookups = 0, blocks_fetched = 0;
     double stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     bool has_result = false;
+    bool want_compact = false;                              // pack the result into the compact wire form INSIDE the step (pgi_find_mems_compact)
+    bool compact_done = false;                              // ... and this step did
+    bool chain_k1 = false;                                  // this step's K1 launch is ordered behind the previous step's (PGI_CHAIN=3)
+    bool run_pending = false, run_count_mode = false, run_mutex_held = false; uint64_t run_min_len = 0, run_min_occ = 0; int run_launches = 0;   // step enqueued, not yet waited for
     void release_all() {
         DevBuf *db[] = {&d_slot_ctr, &d_codes, &d_read_flags, &d_reads, &d_read_off, &d_ctr, &d_mem_buf, &d_mem_key, &d_nmems, &d_mem_off, &d_mems, &d_cub, &d_n_runs, &d_cnt,
                         &d_raw_off, &d_first, &d_skip, &d_raw, &d_raw2, &d_ucnt, &d_tag_off, &d_tags, &d_large, &d_seg_b, &d_seg_e, &d_c_cnt, &d_c_rec, &d_c_rt, &d_c_tags};
@@ -643,6 +650,8 @@ extern "C" void pgi_index_free(pgi_index *ix) {
     if (!ix) return;
     for (pgi_batch *b : ix->pool) pgi_batch_free(b);
     int prev = -1; cudaGetDevice(&prev); cudaSetDevice(ix->device);
+    if (ix->ev_end) cudaEventDestroy(ix->ev_end);
+    if (ix->ev_k1) cudaEventDestroy(ix->ev_k1);
     for (void *p : ix->owned) cudaFree(p);
     for (void *p : ix->owned_host) cudaFreeHost(p);
     if (prev >= 0) cudaSetDevice(prev);
@@ -675,7 +684,7 @@ extern "C" int pgi_batch_upload(pgi_batch *b, const char *reads, const uint64_t 
         if (total) CK(cudaMemcpyAsync(b->d_reads.p, reads, total, cudaMemcpyHostToDevice, b->stream));
         CK(cudaMemsetAsync((char *) b->d_reads.p + total, 0, 16, b->stream));
         CK(cudaMemcpyAsync(b->d_read_off.p, read_off, (n_reads + 1) * 8, cudaMemcpyHostToDevice, b->stream));
-        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false;
+        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false; b->compact_done = false;
         b->reads_bytes = total;
         return PGI_OK;
     } catch (const CudaError &e) { return fail(PGI_ECUDA, std::string(e.what) + ": " + cudaGetErrorString(e.e)); }
@@ -685,7 +694,7 @@ extern "C" int pgi_batch_set_device_reads(pgi_batch *b, const char *d_reads, con
     if (!b || !d_read_off || (!d_reads && n_reads)) return fail(PGI_EINVAL, "null argument");
     if (((uintptr_t) d_reads & 7) != 0) return fail(PGI_EINVAL, "device reads must be 8-byte aligned");
     b->reads_bytes = total_bytes;
-    b->reads64 = (const uint64_t *) d_reads; b->read_off = d_read_off; b->n_reads = n_reads; b->has_result = false;
+    b->reads64 = (const uint64_t *) d_reads; b->read_off = d_read_off; b->n_reads = n_reads; b->has_result = false; b->compact_done = false;
     return PGI_OK;
 }
 
@@ -718,7 +727,7 @@ void exclusive_scan(pgi_batch *b, const uint64_t *in, uint64_t *out, uint64_t n_
 //   [4] items to decode (raw_off[nm]), [5] long lists, [6] raw overflow flag, [7] unique tags (tag_off[nm]), [9] run blocks fetched
 // A counter reaches the host through a KERNEL writing pinned memory (unified addressing), not a cudaMemcpyAsync: a copy,
 // however small, queues on the device-to-host copy engine behind the result download of whichever call finished before.
-enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_BLK = 5, ST_BADOFF = 6, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_WORDS = 16 };
+enum { ST_CURSOR = 0, ST_SLOTS = 1, ST_EXT = 2, ST_SEED = 4, ST_BLK = 5, ST_BADOFF = 6, ST_NMEMS = 8, ST_MAXPART = 9, ST_NM = 10, ST_LARGE = 12, ST_RAWOVF = 13, ST_NOFIT = 14, ST_WORDS = 16 };
 
 __global__ void mem_finalize_kernel(unsigned long long *st, const unsigned long long *slot_ctr, uint64_t part_cap, uint64_t mems_cap) {
     __shared__ unsigned long long s_sum[PGI_SLOT_PARTS], s_max[PGI_SLOT_PARTS];
@@ -740,7 +749,7 @@ __global__ void collect_kernel(const unsigned long long *st, const uint64_t *raw
     if (threadIdx.x == 0) {
         const uint64_t nm = st[ST_NM];
         host[0] = st[ST_NMEMS]; host[1] = st[ST_MAXPART]; host[2] = st[ST_EXT]; host[3] = st[ST_SEED];
-        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0; host[9] = st[ST_BLK]; host[10] = st[ST_BADOFF];
+        host[4] = raw_off ? raw_off[nm] : 0; host[5] = st[ST_LARGE]; host[6] = st[ST_RAWOVF]; host[7] = tag_off ? tag_off[nm] : 0; host[9] = st[ST_BLK]; host[10] = st[ST_BADOFF]; host[12] = st[ST_NOFIT];
         __threadfence_system();
     }
 }
@@ -836,9 +845,11 @@ void enqueue_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &la
     a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.bad_off = st + ST_BADOFF; a.reads_bytes = b->reads_bytes; a.mem_cap = cap;
     a.slot_ctr = b->d_slot_ctr.as<unsigned long long>(); a.part_cap = part_cap;
     a.mem_buf = b->d_mem_buf.as<uint4>(); a.mem_key = b->d_mem_key.as<uint64_t>(); a.read_nmems = b->d_nmems.as<uint64_t>();
+    if (b->chain_k1 && ix->ev_k1_set) CK(cudaStreamWaitEvent(b->stream, ix->ev_k1, 0));
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { k1.fn<<<grid, k1.threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
     CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
+    if (b->chain_k1) { CK(cudaEventRecord(ix->ev_k1, b->stream)); ix->ev_k1_set = true; }
     mem_finalize_kernel<<<1, PGI_SLOT_PARTS, 0, b->stream>>>(st, a.slot_ctr, part_cap, b->mems_cap);
     ++launches; CK(cudaGetLastError());
     CK(cudaEventRecord(b->ev[EV_MEM], b->stream));
@@ -867,9 +878,11 @@ void enqueue_count_stage(pgi_batch *b, int &launches) {
     a.n_reads = n; a.min_len = 1; a.min_occ = 0; a.seed = nullptr; a.seed_k = 0; a.pad = 0; a.codes32 = nullptr; a.read_flags = nullptr;
     a.cursor = st + ST_CURSOR; a.mem_count = st + ST_SLOTS; a.ext_count = st + ST_EXT; a.seed_count = st + ST_SEED; a.blk_count = st + ST_BLK; a.bad_off = st + ST_BADOFF; a.reads_bytes = b->reads_bytes; a.mem_cap = n; a.slot_ctr = nullptr; a.part_cap = 0;
     a.mem_buf = b->d_mems.as<uint4>(); a.mem_key = nullptr; a.read_nmems = nullptr;
+    if (b->chain_k1 && ix->ev_k1_set) CK(cudaStreamWaitEvent(b->stream, ix->ev_k1, 0));
     CK(cudaEventRecord(b->ev[EV_K1A], b->stream));
     if (n) { fn<<<grid, threads, 0, b->stream>>>(a); ++launches; CK(cudaGetLastError()); }
     CK(cudaEventRecord(b->ev[EV_K1B], b->stream));
+    if (b->chain_k1) { CK(cudaEventRecord(ix->ev_k1, b->stream)); ix->ev_k1_set = true; }
     iota_kernel<<<grid_for(n + 1, 256), 256, 0, b->stream>>>(n + 1, b->d_mem_off.as<uint64_t>());
     set_nm_kernel<<<1, 1, 0, b->stream>>>(st, n);
     launches += 2; CK(cudaGetLastError());
@@ -937,13 +950,65 @@ void enqueue_tag_stage(pgi_batch *b, uint64_t cap, const uint4 *mems, const uint
     }
 }
 
+// ---- compact wire form of the result (pgi_result_compact)
+__global__ void iota_mul_kernel(uint64_t n_plus_1, uint64_t mul, uint64_t *out) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i < n_plus_1) out[i] = i * mul;
+}
+// flags[0] set when a value does not fit the compact form
+__global__ void compact_reads_kernel(uint64_t n_reads, const uint64_t *mem_off, uint32_t *cnt, unsigned long long *flags) {
+    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (i >= n_reads) return;
+    const uint64_t c = mem_off[i + 1] - mem_off[i];
+    if (c >> 32) flags[0] = 1ull;
+    cnt[i] = (uint32_t) c;
+}
+// n_mems = the count, or -- nm_dev != nullptr, launched inside the step -- the capacity, the count being read from device memory
+__global__ void compact_mems_kernel(uint64_t n_mems, const uint64_t *nm_dev, const uint4 *mems, const uint64_t *tag_off, const uint64_t *n_runs, const uint64_t *tags, unsigned tag_bytes,
+                                    uint64_t *rec, uint32_t *runs_tags, uint8_t *ctags, unsigned long long *flags) {
+    const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (m >= n_mems || (nm_dev && m >= *nm_dev)) return;
+    const uint4 a = mems[2 * m], b = mems[2 * m + 1];
+    const uint64_t start = a.x | (uint64_t) a.y << 32, end = a.z | (uint64_t) a.w << 32, k = b.x | (uint64_t) b.y << 32, sz = b.z | (uint64_t) b.w << 32;
+    const uint64_t t0 = tag_off[m], nt = tag_off[m + 1] - t0, nr = n_runs[m];
+    if ((start >> 24) || ((end - start) >> 24) || (k >> 40) || (sz >> 40) || (nt >> 32) || (nr >> 32)) flags[0] = 1ull;
+    rec[2 * m] = (k & 0xFFFFFFFFFFull) | start << 40; rec[2 * m + 1] = (sz & 0xFFFFFFFFFFull) | (end - start) << 40;
+    runs_tags[2 * m] = (uint32_t) nr; runs_tags[2 * m + 1] = (uint32_t) nt;
+    for (uint64_t t = 0; t < nt; ++t) {
+        const uint64_t v = tags[t0 + t]; uint8_t *d = ctags + (t0 + t) * tag_bytes;
+        if (tag_bytes < 8 && (v >> (8 * tag_bytes))) flags[0] = 1ull;
+        for (unsigned q = 0; q < tag_bytes; ++q) d[q] = (uint8_t) (v >> (8 * q));
+    }
+}
+
+unsigned compact_tag_bytes(const pgi_index *ix) { return (ix->has_tags && ix->tg.layout == 0 && ix->tg.width <= 40) ? 5u : 8u; }
+// The compact wire form packed INSIDE the step (behind the tag stage, over the step's capacities, counts read from device
+// memory), so that the download of a finished step is copies only. Packed behind the step instead, the two kernels wait for
+// the NEXT caller's persistent fmd_mem_kernel to leave the SMs (9 ms) before the download can even start.
+void enqueue_compact(pgi_batch *b, bool with_tags, int &launches) {
+    const uint64_t n = b->n_reads, cap = b->mems_cap; cudaStream_t st = b->stream;
+    const unsigned tag_bytes = compact_tag_bytes(b->ix);
+    unsigned long long *stw = b->d_ctr.as<unsigned long long>();
+    b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((cap + 1) * 16); b->d_c_rt.need((cap + 1) * 8);
+    b->d_c_tags.need(((with_tags ? b->raw_cap : 0) + 1) * (uint64_t) tag_bytes);
+    if (n) { compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), stw + ST_NOFIT); ++launches; }
+    if (cap) {
+        compact_mems_kernel<<<grid_for(cap, 256), 256, 0, st>>>(cap, (const uint64_t *) (stw + ST_NM), b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(),
+                                                                b->d_tags.as<uint64_t>(), tag_bytes, b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), stw + ST_NOFIT);
+        ++launches;
+    }
+    CK(cudaGetLastError());
+}
+
 // The ONE synchronisation of a step: fetch the counters, decide whether everything fitted. Returns true when the step has
 // to be run again (capacity hints of the batch were raised).
-bool collect_and_check(pgi_batch *b, bool with_tags, bool mem_stage) {
+void enqueue_collect(pgi_batch *b, bool with_tags) {
     unsigned long long *st = b->d_ctr.as<unsigned long long>();
     collect_kernel<<<1, 32, 0, b->stream>>>(st, with_tags ? b->d_raw_off.as<uint64_t>() : nullptr, with_tags ? b->d_tag_off.as<uint64_t>() : nullptr, b->h_ctr.as<uint64_t>());
     CK(cudaGetLastError());
     CK(cudaEventRecord(b->ev[EV_END], b->stream));
+}
+bool wait_and_check(pgi_batch *b, bool with_tags, bool mem_stage) {
     CK(cudaStreamSynchronize(b->stream));
     volatile uint64_t *h = b->h_ctr.as<volatile uint64_t>();
     const uint64_t total = h[0], maxpart = h[1], total_raw = h[4], n_large = h[5], raw_ovf = h[6];
@@ -974,7 +1039,21 @@ float ev_ms(pgi_batch *b, int from, int to) { float ms = 0; cudaEventElapsedTime
     catch (const std::bad_alloc &) { return fail(PGI_ENOMEM, "out of host memory"); } \
     catch (const std::exception &e) { return fail(PGI_EINVAL, e.what()); }
 
-static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t min_occ) {
+// A step = batch_enqueue (everything of the step queued on the batch's stream, nothing waited for) + batch_finish (the one
+// synchronisation: counters fetched, the rare step that did not fit its buffers run again).
+// Steps enqueued on one index by concurrent callers or by several batches in flight are ordered ON THE GPU (PGI_CHAIN, read
+// per step; the mutex is held while a step is enqueued, never while one runs):
+//   1  a step starts when the step enqueued before it has ended (chain event ev_end): one step at a time, but the next one is
+//      already queued when this one ends -- no host wake-up, mutex hand-over and two dozen launches between two steps
+//   3  only the fmd_mem_kernel launches are ordered (ev_k1): the next step's persistent grid starts when this one's has
+//      ended, and this step's short ordering / tag / packing kernels run beside it
+//   2  no ordering: the streams overlap as the hardware schedules them
+//   0  (one-call API only) the round-1 scheme: the caller holds the mutex until its step has finished
+static int chain_mode() {
+    if (const char *e = std::getenv("PGI_CHAIN")) { const int m = std::atoi(e); if (m >= 0 && m <= 3) return m; }
+    return 1;
+}
+static int batch_enqueue(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t min_occ, bool mutex_held = false) {
     if (!b) return fail(PGI_EINVAL, "null argument");
     if (!b->read_off) return fail(PGI_EINVAL, "no reads staged: call pgi_batch_upload or pgi_batch_set_device_reads first");
     if (b->n_reads >> 32) return fail(PGI_EINVAL, "more than 2^32 reads in one batch");
@@ -984,33 +1063,66 @@ static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t m
                                  "file (src/r-index.cpp:577), its count_encoded results are not reproduced");
     try {
         DeviceGuard g(b->ix->device);
-        int launches = 0, reruns = 0;
         const bool with_tags = b->ix->has_tags;
-        for (;; ++reruns) {
-            if (reruns > 8) return fail(PGI_ECUDA, "internal: the work buffers of a step did not converge");
-            launches = 0;
-            CK(cudaEventRecord(b->ev[EV_START], b->stream));
-            if (count_mode) enqueue_count_stage(b, launches);
-            else enqueue_mem_stage(b, min_len, min_occ, launches);
-            if (with_tags) enqueue_tag_stage(b, b->mems_cap, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
-            else {
-                b->d_tag_off.need((b->mems_cap + 1) * 8); b->d_n_runs.need((b->mems_cap + 1) * 8); b->d_tags.need(8);
-                CK(cudaMemsetAsync(b->d_tag_off.p, 0, (b->mems_cap + 1) * 8, b->stream));
-                CK(cudaMemsetAsync(b->d_n_runs.p, 0, (b->mems_cap + 1) * 8, b->stream));
-                CK(cudaEventRecord(b->ev[EV_PLAN], b->stream)); CK(cudaEventRecord(b->ev[EV_DECODE], b->stream));
-            }
-            ++launches;                                      // collect_kernel
-            if (!collect_and_check(b, with_tags, !count_mode)) break;
+        int launches = 0;
+        b->has_result = false; b->compact_done = false;
+        b->run_count_mode = count_mode; b->run_min_len = min_len; b->run_min_occ = min_occ; b->run_mutex_held = mutex_held;
+        pgi_index *ix = b->ix;
+        const int mode = mutex_held ? 0 : chain_mode();
+        std::unique_lock<std::mutex> order(ix->compute_mu, std::defer_lock);
+        if (!mutex_held && mode != 2) order.lock();
+        if ((mode == 1 || mode == 3) && !ix->ev_end) {
+            CK(cudaEventCreateWithFlags(&ix->ev_end, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&ix->ev_k1, cudaEventDisableTiming));
         }
-        // [0] the K1 launch alone (device time between two in-stream events)
-        b->stage_ms[0] = ev_ms(b, EV_K1A, EV_K1B); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
-        b->stage_ms[3] = ev_ms(b, EV_PLAN, EV_DECODE); b->stage_ms[4] = ev_ms(b, EV_DECODE, EV_END); b->stage_ms[5] = ev_ms(b, EV_START, EV_END);
-        b->stage_ms[6] = launches; b->stage_ms[7] = reruns;
-        b->has_result = true;
+        b->chain_k1 = mode == 3;
+        if (mode == 1 && ix->ev_end_set) CK(cudaStreamWaitEvent(b->stream, ix->ev_end, 0));
+        CK(cudaEventRecord(b->ev[EV_START], b->stream));
+        if (count_mode) enqueue_count_stage(b, launches);
+        else enqueue_mem_stage(b, min_len, min_occ, launches);
+        if (with_tags) enqueue_tag_stage(b, b->mems_cap, b->d_mems.as<uint4>(), nullptr, nullptr, launches);
+        else {
+            b->d_tag_off.need((b->mems_cap + 1) * 8); b->d_n_runs.need((b->mems_cap + 1) * 8); b->d_tags.need(8);
+            CK(cudaMemsetAsync(b->d_tag_off.p, 0, (b->mems_cap + 1) * 8, b->stream));
+            CK(cudaMemsetAsync(b->d_n_runs.p, 0, (b->mems_cap + 1) * 8, b->stream));
+            CK(cudaEventRecord(b->ev[EV_PLAN], b->stream)); CK(cudaEventRecord(b->ev[EV_DECODE], b->stream));
+        }
+        if (b->want_compact) enqueue_compact(b, with_tags, launches);
+        ++launches;                                          // collect_kernel
+        enqueue_collect(b, with_tags);
+        if (mode == 1) { CK(cudaEventRecord(ix->ev_end, b->stream)); ix->ev_end_set = true; }
+        b->run_launches = launches; b->run_pending = true;
         return PGI_OK;
     } PGI_CATCH
 }
+static int batch_finish(pgi_batch *b) {
+    if (!b) return fail(PGI_EINVAL, "null argument");
+    if (!b->run_pending) return fail(PGI_EINVAL, "no step enqueued on this batch");
+    try {
+        DeviceGuard g(b->ix->device);
+        const bool with_tags = b->ix->has_tags;
+        int reruns = 0;
+        while (wait_and_check(b, with_tags, !b->run_count_mode)) {
+            if (++reruns > 8) { b->run_pending = false; return fail(PGI_ECUDA, "internal: the work buffers of a step did not converge"); }
+            const int rc = batch_enqueue(b, b->run_count_mode, b->run_min_len, b->run_min_occ, b->run_mutex_held);
+            if (rc != PGI_OK) { b->run_pending = false; return rc; }
+        }
+        b->run_pending = false;
+        b->compact_done = b->want_compact;
+        // [0] the K1 launch alone (device time between two in-stream events)
+        b->stage_ms[0] = ev_ms(b, EV_K1A, EV_K1B); b->stage_ms[1] = ev_ms(b, EV_MEM, EV_ORDER); b->stage_ms[2] = ev_ms(b, EV_ORDER, EV_PLAN);
+        b->stage_ms[3] = ev_ms(b, EV_PLAN, EV_DECODE); b->stage_ms[4] = ev_ms(b, EV_DECODE, EV_END); b->stage_ms[5] = ev_ms(b, EV_START, EV_END);
+        b->stage_ms[6] = b->run_launches; b->stage_ms[7] = reruns;
+        b->has_result = true;
+        return PGI_OK;
+    } catch (...) { b->run_pending = false; try { throw; } PGI_CATCH }
+}
+static int batch_run(pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t min_occ, bool mutex_held = false) {
+    const int rc = batch_enqueue(b, count_mode, min_len, min_occ, mutex_held);
+    return rc == PGI_OK ? batch_finish(b) : rc;
+}
 
+extern "C" int pgi_batch_run_async(pgi_batch *b, uint64_t min_len, uint64_t min_occ) { return batch_enqueue(b, false, min_len, min_occ); }
+extern "C" int pgi_batch_wait(pgi_batch *b) { return batch_finish(b); }
 extern "C" int pgi_batch_run(pgi_batch *b, uint64_t min_len, uint64_t min_occ) { return batch_run(b, false, min_len, min_occ); }
 extern "C" int pgi_batch_run_query_tags(pgi_batch *b) { return batch_run(b, true, 0, 0); }
 
@@ -1052,37 +1164,7 @@ extern "C" int pgi_batch_fetch(pgi_batch *b, pgi_result *out) {
     } PGI_CATCH
 }
 
-// ------------------------------------------------------------------------------------------ compact wire form
-namespace {
-__global__ void iota_mul_kernel(uint64_t n_plus_1, uint64_t mul, uint64_t *out) {
-    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (i < n_plus_1) out[i] = i * mul;
-}
-// flags[0] set when a value does not fit the compact form
-__global__ void compact_reads_kernel(uint64_t n_reads, const uint64_t *mem_off, uint32_t *cnt, unsigned long long *flags) {
-    const uint64_t i = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (i >= n_reads) return;
-    const uint64_t c = mem_off[i + 1] - mem_off[i];
-    if (c >> 32) flags[0] = 1ull;
-    cnt[i] = (uint32_t) c;
-}
-__global__ void compact_mems_kernel(uint64_t n_mems, const uint4 *mems, const uint64_t *tag_off, const uint64_t *n_runs, const uint64_t *tags, unsigned tag_bytes,
-                                    uint64_t *rec, uint32_t *runs_tags, uint8_t *ctags, unsigned long long *flags) {
-    const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
-    if (m >= n_mems) return;
-    const uint4 a = mems[2 * m], b = mems[2 * m + 1];
-    const uint64_t start = a.x | (uint64_t) a.y << 32, end = a.z | (uint64_t) a.w << 32, k = b.x | (uint64_t) b.y << 32, sz = b.z | (uint64_t) b.w << 32;
-    const uint64_t t0 = tag_off[m], nt = tag_off[m + 1] - t0, nr = n_runs[m];
-    if ((start >> 24) || ((end - start) >> 24) || (k >> 40) || (sz >> 40) || (nt >> 32) || (nr >> 32)) flags[0] = 1ull;
-    rec[2 * m] = (k & 0xFFFFFFFFFFull) | start << 40; rec[2 * m + 1] = (sz & 0xFFFFFFFFFFull) | (end - start) << 40;
-    runs_tags[2 * m] = (uint32_t) nr; runs_tags[2 * m + 1] = (uint32_t) nt;
-    for (uint64_t t = 0; t < nt; ++t) {
-        const uint64_t v = tags[t0 + t]; uint8_t *d = ctags + (t0 + t) * tag_bytes;
-        if (tag_bytes < 8 && (v >> (8 * tag_bytes))) flags[0] = 1ull;
-        for (unsigned q = 0; q < tag_bytes; ++q) d[q] = (uint8_t) (v >> (8 * q));
-    }
-}
-} // namespace
+// ------------------------------------------------------------------------------------------ compact wire form (kernels: above, before collect_and_check)
 
 extern "C" int pgi_batch_upload_fixed(pgi_batch *b, const char *reads, uint64_t n_reads, uint64_t read_len) {
     if (!b || (!reads && n_reads)) return fail(PGI_EINVAL, "null argument");
@@ -1094,7 +1176,7 @@ extern "C" int pgi_batch_upload_fixed(pgi_batch *b, const char *reads, uint64_t 
         CK(cudaMemsetAsync((char *) b->d_reads.p + total, 0, 16, b->stream));
         iota_mul_kernel<<<grid_for(n_reads + 1, 256), 256, 0, b->stream>>>(n_reads + 1, read_len, b->d_read_off.as<uint64_t>());
         CK(cudaGetLastError());
-        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false; b->reads_bytes = total;
+        b->reads64 = b->d_reads.as<uint64_t>(); b->read_off = b->d_read_off.as<uint64_t>(); b->n_reads = n_reads; b->has_result = false; b->compact_done = false; b->reads_bytes = total;
         return PGI_OK;
     } PGI_CATCH
 }
@@ -1105,16 +1187,18 @@ extern "C" int pgi_batch_fetch_compact(pgi_batch *b, pgi_result_compact *out) {
     try {
         DeviceGuard g(b->ix->device);
         const uint64_t n = b->n_reads, nm = b->n_mems, nt = b->n_tags; cudaStream_t st = b->stream;
-        const unsigned tag_bytes = (b->ix->has_tags && b->ix->tg.layout == 0 && b->ix->tg.width <= 40) ? 5u : 8u;
-        b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((nm + 1) * 16); b->d_c_rt.need((nm + 1) * 8); b->d_c_tags.need((nt + 1) * tag_bytes);
+        const unsigned tag_bytes = compact_tag_bytes(b->ix);
         b->h_c_cnt.need((n + 1) * 4); b->h_c_rec.need((nm + 1) * 16); b->h_c_rt.need((nm + 1) * 8); b->h_c_tags.need((nt + 1) * tag_bytes);
-        unsigned long long *flags = b->d_ctr.as<unsigned long long>() + 14;
-        CK(cudaMemsetAsync(flags, 0, 8, st));
-        if (n) compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), flags);
-        if (nm) compact_mems_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes,
-                                                                     b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), flags);
-        CK(cudaGetLastError());
-        peek_kernel<<<1, 32, 0, st>>>((const uint64_t *) flags, b->h_ctr.as<uint64_t>() + 12, 1);
+        if (!b->compact_done) {                             // a step run through pgi_batch_run: pack now (pgi_find_mems_compact packs inside the step)
+            b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((nm + 1) * 16); b->d_c_rt.need((nm + 1) * 8); b->d_c_tags.need((nt + 1) * tag_bytes);
+            unsigned long long *flags = b->d_ctr.as<unsigned long long>() + ST_NOFIT;
+            CK(cudaMemsetAsync(flags, 0, 8, st));
+            if (n) compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), flags);
+            if (nm) compact_mems_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, nullptr, b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes,
+                                                                         b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), flags);
+            CK(cudaGetLastError());
+            peek_kernel<<<1, 32, 0, st>>>((const uint64_t *) flags, b->h_ctr.as<uint64_t>() + 12, 1);
+        }
         if (n) CK(cudaMemcpyAsync(b->h_c_cnt.p, b->d_c_cnt.p, n * 4, cudaMemcpyDeviceToHost, st));
         if (nm) { CK(cudaMemcpyAsync(b->h_c_rec.p, b->d_c_rec.p, nm * 16, cudaMemcpyDeviceToHost, st)); CK(cudaMemcpyAsync(b->h_c_rt.p, b->d_c_rt.p, nm * 8, cudaMemcpyDeviceToHost, st)); }
         if (nt) CK(cudaMemcpyAsync(b->h_c_tags.p, b->d_c_tags.p, nt * tag_bytes, cudaMemcpyDeviceToHost, st));
@@ -1157,6 +1241,11 @@ extern "C" void pgi_result_expanded_free(pgi_result *r) {
 }
 
 // ------------------------------------------------------------------------------------------ one-call API
+static int run_shared(pgi_index *ix, pgi_batch *b, bool count_mode, uint64_t min_len, uint64_t min_occ) {
+    if (chain_mode() != 0) return batch_run(b, count_mode, min_len, min_occ);
+    std::lock_guard<std::mutex> token(ix->compute_mu);     // PGI_CHAIN=0: one step at a time, ordered on the host
+    return batch_run(b, count_mode, min_len, min_occ, true);
+}
 static pgi_batch *pool_take(pgi_index *ix) {
     { std::lock_guard<std::mutex> l(ix->pool_mu); if (!ix->pool.empty()) { pgi_batch *b = ix->pool.back(); ix->pool.pop_back(); return b; } }
     pgi_batch *b = nullptr;
@@ -1190,7 +1279,7 @@ static int one_call(pgi_index *ix, bool count_mode, const char *reads, const uin
     // delay each other's short follow-up kernels), and the device->host copy again runs outside the token. In steady state
     // call k+1 uploads and call k-1 downloads while call k computes.
     if (trace) t1 = now_ms();
-    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = batch_run(b, count_mode, min_len, min_occ); }
+    if (rc == PGI_OK) { b->want_compact = false; rc = run_shared(ix, b, count_mode, min_len, min_occ); }
     const double t2 = trace ? now_ms() : 0;
     if (rc == PGI_OK) { std::lock_guard<std::mutex> down(ix->download_mu); rc = pgi_batch_fetch(b, out); }
     if (trace) std::fprintf(stderr, "[pgi] ctx %p reads %llu: enter %.2f uploaded %.2f run_done %.2f (mem kernel %.2f, stages %.2f ms) fetched %.2f\n", (void *) b,
@@ -1223,7 +1312,8 @@ extern "C" int pgi_find_mems_compact(pgi_index *ix, const char *reads, const uin
         rc = read_off ? pgi_batch_upload(b, reads, read_off, n_reads) : pgi_batch_upload_fixed(b, reads, n_reads, read_len);
         if (rc == PGI_OK && cudaStreamSynchronize(b->stream) != cudaSuccess) rc = fail(PGI_ECUDA, "host to device copy failed");
     }
-    if (rc == PGI_OK) { std::lock_guard<std::mutex> token(ix->compute_mu); rc = batch_run(b, false, min_len, min_occ); }
+    if (rc == PGI_OK) { b->want_compact = true; rc = run_shared(ix, b, false, min_len, min_occ); }
+    b->want_compact = false;
     if (rc == PGI_OK) { std::lock_guard<std::mutex> down(ix->download_mu); rc = pgi_batch_fetch_compact(b, out); }
     b->stream = own;
     if (rc != PGI_OK) { pool_give(ix, b); return rc; }
@@ -1263,7 +1353,8 @@ extern "C" int pgi_tag_query_batch(pgi_index *ix, uint64_t n, const uint64_t *st
             CK(cudaGetLastError());
             b->mems_cap = n; b->part_cap = 0; b->mem_slots = n;
             enqueue_tag_stage(b, n, nullptr, ds, de, launches);
-            if (!collect_and_check(b, true, false)) break;
+            enqueue_collect(b, true);
+            if (!wait_and_check(b, true, false)) break;
         }
         b->n_reads = 0; b->n_mems = n; b->extensions = 0; b->seed_lookups = 0; b->has_result = true;
         b->d_mem_off.need(8); CK(cudaMemsetAsync(b->d_mem_off.p, 0, 8, b->stream));

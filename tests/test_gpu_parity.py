@@ -508,3 +508,39 @@ def test_clone_to_second_gpu(capi):
     b1 = capi.Index.from_runs(sym, ln, device=1)
     r2, o2 = datasets.sample_reads(s["text"], 1000, 150, 0.01, seed=5)
     compare(b1.find_mems(r2, o2, 20, 1), orc.Index(s["ri"]).find_mems(r2, o2, 20, 1, with_tags=False), False)
+
+def test_async_steps_overlap_and_compact_in_step(capi):
+    """pgi_batch_run_async / pgi_batch_wait: three batches in flight on one GPU from one host thread return what
+    pgi_batch_run returns for each of them (incl. a first step whose buffers must grow: the re-run happens inside wait), and
+    pgi_find_mems_compact (result packed inside the step, steps of concurrent callers chained on the GPU) expands to the
+    arrays of pgi_find_mems, for every PGI_CHAIN mode."""
+    import os, threading
+    s = datasets.synth_index(ref_len=20000, n_hap=8, seed=21, encoded=True)
+    g = capi.Index(s["ri"], s["tags0"], 0)
+    sets = [datasets.sample_reads(s["text"], 120000 + 7000 * i, 150, 0.02, seed=30 + i) for i in range(3)]
+    want = []
+    for reads, off in sets:
+        b = capi.Batch(g); b.upload(reads.ctypes.data, off.ctypes.data, len(off) - 1); b.run(20, 1); want.append(b.fetch()); b.close()
+    bs = [capi.Batch(g) for _ in sets]
+    for rep in range(2):                                       # second round: the batches' buffers are sized, no re-run
+        for b, (reads, off) in zip(bs, sets): b.upload(reads.ctypes.data, off.ctypes.data, len(off) - 1); b.run_async(20, 1)
+        for b, W in zip(bs, want):
+            b.wait(); S = b.fetch()
+            for k in ("n_mems", "n_tags", "extensions"): assert S[k] == W[k], k
+            for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(S[k], W[k]), k
+    with pytest.raises(capi.PgiError): bs[0].wait()             # nothing enqueued
+    old = os.environ.get("PGI_CHAIN")
+    try:
+        for mode in ("1", "0", "2"):
+            os.environ["PGI_CHAIN"] = mode
+            outs = [None] * 6
+            def call(i):
+                reads, off = sets[i % 3]
+                outs[i] = g.find_mems_compact(reads, 150, 20, 1, read_off=(off if i == 1 else None)) if i < 3 else g.find_mems(reads, off, 20, 1, text=False)
+            ths = [threading.Thread(target=call, args=(i,)) for i in range(6)]
+            [t.start() for t in ths]; [t.join() for t in ths]
+            for i, o_ in enumerate(outs):
+                for k in ("mem_off", "mems", "tag_off", "tags", "n_runs"): assert np.array_equal(o_[k], want[i % 3][k]), (mode, i, k)
+    finally:
+        if old is None: os.environ.pop("PGI_CHAIN", None)
+        else: os.environ["PGI_CHAIN"] = old
