@@ -151,6 +151,20 @@ __global__ void header_kernel(uint32_t *blocks, const uint64_t *before, uint64_t
     put(blocks + b * PGI_BLOCK_U32, pre);
 }
 
+// Last pass over all blocks: the construction above keeps one count per header word (w1..w4 = A C G T low halves, w5 NL,
+// w6 N, high bytes in w7 / w8: scan inputs and outputs are plain words); the layout the queries read is the limb form of
+// pgi_layout.h.
+__global__ void pack_headers_kernel(uint32_t *blocks, uint64_t n_blocks) {
+    const uint64_t b = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (b >= n_blocks) return;
+    uint32_t *w = blocks + b * PGI_BLOCK_U32;
+    uint64_t cnt[6];
+    cnt[0] = w[5]; cnt[4] = w[6];
+    cnt[1] = w[1] | (uint64_t) ((w[7] >> 8) & 0xFFu) << 32; cnt[2] = w[2] | (uint64_t) ((w[7] >> 16) & 0xFFu) << 32;
+    cnt[3] = w[3] | (uint64_t) (w[7] >> 24) << 32; cnt[5] = w[4] | (uint64_t) (w[8] & 0xFFu) << 32;
+    pgi_put_header(w, cnt);
+}
+
 // ---- tags
 struct Pieces { const uint64_t *len; __host__ __device__ uint64_t operator()(uint64_t i) const { return (len[i] + 510) / 511; } };
 struct NodeOf { const uint64_t *val; __host__ __device__ uint64_t operator()(uint64_t i) const { return val[i] >> 11; } };

@@ -415,6 +415,8 @@ extern "C" int pgi_index_create_from_runs(const uint8_t *sym, const uint64_t *le
                 B::header_kernel<<<grid_of(nb, 256), 256>>>(blocks, before, nb, field, n_chunks, chunk_base);
                 CK(cudaGetLastError());
             }
+            B::pack_headers_kernel<<<grid_of(n_blocks, 256), 256>>>(blocks, n_blocks);
+            CK(cudaGetLastError());
             CK(cudaDeviceSynchronize());
             tmp.drop(before);
         }
@@ -770,7 +772,7 @@ struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads
 const K1Variant &k1_variant() {
     static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
         {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
-        {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256},
+        {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256}, {"24", fmd_mem_kernel<2, 256, 4>, 256},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process
     if (e) for (const K1Variant &v : table) if (!std::strcmp(v.name, e)) return v;

@@ -92,9 +92,14 @@ PGI_HD uint32_t min_u16x2(uint32_t a, uint32_t b) {                 // VIMNMX.U1
     return (al < bl ? al : bl) | (ah < bh ? ah : bh) << 16;
 #endif
 }
+// Selector nibbles are run codes: 0..7 in every block that is scanned with a non-zero offset (pgi_layout.h), so the raw PRMT
+// is used (__byte_perm masks the selector with 0x7777 first: 14 LOP3 per extension). The 0xF marker nibble of a directory
+// block selects a sign-replicated byte, and that block is only ever scanned at offset 0, where every product is 0 * byte.
 PGI_HD uint32_t byte_perm(uint32_t lo, uint32_t hi, uint32_t sel) { // PRMT: result byte i = byte (sel nibble i) of {hi:lo}
 #if defined(__CUDA_ARCH__)
-    return __byte_perm(lo, hi, sel);
+    uint32_t r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(lo), "r"(hi), "r"(sel));
+    return r;
 #else
     const uint64_t t = (uint64_t) hi << 32 | lo; uint32_t r = 0;
     for (int i = 0; i < 4; ++i) r |= (uint32_t) ((t >> (8 * ((sel >> (4 * i)) & 7u))) & 0xFFu) << (8 * i);
@@ -113,6 +118,15 @@ PGI_HD uint32_t dp2a_hi(uint32_t a, uint32_t b, uint32_t c) {       // IDP.2A.HI
     return __dp2a_hi(a, b, c);
 #else
     return (a & 0xFFFFu) * ((b >> 16) & 0xFFu) + (a >> 16) * (b >> 24) + c;
+#endif
+}
+
+PGI_HD uint32_t dp4a_u8(uint32_t a, uint32_t b, uint32_t c) {       // IDP.4A.U8.U8: sum of the four byte products + c
+#if defined(__CUDA_ARCH__)
+    return __dp4a(a, b, c);
+#else
+    for (int i = 0; i < 4; ++i) c += ((a >> (8 * i)) & 0xFFu) * ((b >> (8 * i)) & 0xFFu);
+    return c;
 #endif
 }
 
@@ -153,16 +167,20 @@ PGI_HD PosRank pos_rank(const uint32_t w[16], uint32_t rel, uint32_t tbl, const 
         aw = dp2a_hi(m1, bw, dp2a_lo(m0, bw, aw)); an = dp2a_hi(m1, bn, dp2a_lo(m0, bn, an));
         fw = dp2a_hi(m1, bf, dp2a_lo(m0, bf, fw)); fn = dp2a_hi(m1, bg, dp2a_lo(m0, bg, fn));
     }
-    // header: cumulative counts before the block; code c lives in word {5,1,2,3,6,4}[c], high byte as in pgi_layout.h
-    const uint32_t wNL = tbl & 7u, wA = (tbl >> 4) & 7u, wC = (tbl >> 8) & 7u, wG = (tbl >> 12) & 7u, wN = (tbl >> 16) & 7u, wT = (tbl >> 20) & 7u;
-    const uint32_t mNL = (tbl >> 3) & 1u, mA = (tbl >> 7) & 1u, mC = (tbl >> 11) & 1u, mG = (tbl >> 15) & 1u, mN = (tbl >> 19) & 1u, mT = (tbl >> 23) & 1u;
-    const uint32_t hA = (w[7] >> 8) & 0xFFu, hC = (w[7] >> 16) & 0xFFu, hG = w[7] >> 24, hT = w[8] & 0xFFu;
-    uint64_t Wl = (uint64_t) w[5] * wNL + (uint64_t) w[1] * wA + (uint64_t) w[2] * wC + (uint64_t) w[3] * wG + (uint64_t) w[6] * wN + (uint64_t) w[4] * wT;
-    uint64_t Ml = (uint64_t) w[5] * mNL + (uint64_t) w[1] * mA + (uint64_t) w[2] * mC + (uint64_t) w[3] * mG + (uint64_t) w[6] * mN + (uint64_t) w[4] * mT;
-    const uint32_t Wh = hA * wA + hC * wC + hG * wG + hT * wT, Mh = hA * mA + hC * mC + hG * mG + hT * mT;
+    // header: the six counts before the block in limb form (pgi_layout.h), code order = byte order of the tables T, so the
+    // weighted sums are dot products as well: bits 0..15 and 16..31 of the counts three dp2a each, bits 32..39 two dp4a
+    // (the code nibbles in the upper half of w8 meet the zero bytes 2, 3 of T.y / T.w). No weight extraction, no 64-bit
+    // multiplies: 20 instructions per position for W and M together (the per-count form took 37 plus 12 shared).
+    const uint32_t w0 = dp2a_lo(w[3], T.y, dp2a_hi(w[2], T.x, dp2a_lo(w[1], T.x, 0u)));
+    const uint32_t w1 = dp2a_lo(w[6], T.y, dp2a_hi(w[5], T.x, dp2a_lo(w[4], T.x, 0u)));
+    const uint32_t w2 = dp4a_u8(w[8], T.y, dp4a_u8(w[7], T.x, 0u));
+    const uint32_t m0 = dp2a_lo(w[3], T.w, dp2a_hi(w[2], T.z, dp2a_lo(w[1], T.z, 0u)));
+    const uint32_t m1h = dp2a_lo(w[6], T.w, dp2a_hi(w[5], T.z, dp2a_lo(w[4], T.z, 0u)));
+    const uint32_t m2 = dp4a_u8(w[8], T.w, dp4a_u8(w[7], T.z, 0u));
+    (void) tbl;
     PosRank o;
-    o.W = Wl + ((uint64_t) Wh << 32) + (uint64_t) (aw - an);
-    o.M = Ml + ((uint64_t) Mh << 32) + (uint64_t) (fw - fn);
+    o.W = (uint64_t) w0 + ((uint64_t) w1 << 16) + ((uint64_t) w2 << 32) + (uint64_t) (aw - an);
+    o.M = (uint64_t) m0 + ((uint64_t) m1h << 16) + ((uint64_t) m2 << 32) + (uint64_t) (fw - fn);
     return o;
 }
 PGI_HD bool is_dir_block(const uint32_t w[16]) { return (w[9] & 0xFu) == PGI_CODE_DIRBLOCK; }

@@ -185,14 +185,13 @@ inline void write_block(uint64_t *dst, const uint64_t cum[6], const uint32_t *co
         throw FormatError("index longer than 2^40 positions is not supported by the device layout");
     if (cum[0] >> 32 || cum[4] >> 32)
         throw FormatError("more than 2^32 endmarkers or N symbols is not supported by the device layout");
-    const uint64_t A = cum[1], C = cum[2], G = cum[3], T = cum[5], NL = cum[0], N = cum[4];
     uint32_t w[PGI_BLOCK_U32];
-    w[0] = w0; w[1] = (uint32_t) A; w[2] = (uint32_t) C; w[3] = (uint32_t) G; w[4] = (uint32_t) T; w[5] = (uint32_t) NL; w[6] = (uint32_t) N;
-    w[7] = (uint32_t) (A >> 32) << 8 | (uint32_t) (C >> 32) << 16 | (uint32_t) (G >> 32) << 24;
+    w[0] = w0;
     uint64_t codes = 0;
     for (unsigned i = 0; i < PGI_RUNS_PER_BLOCK; ++i) codes |= (uint64_t) (i < ne ? code[i] : PGI_CODE_UNUSED) << (4 * i);
     auto e = [&](unsigned i) -> uint32_t { return ne ? end[i < ne ? i : ne - 1] : 0u; };     // unused runs repeat the last end offset
-    w[8] = (uint32_t) (T >> 32) | (uint32_t) (codes >> 32) << 16;
+    w[8] = (uint32_t) (codes >> 32) << 16;
+    pgi_put_header(w, cum);
     w[9] = (uint32_t) codes;
     for (unsigned j = 0; j < 6; ++j) w[10 + j] = e(2 * j) | e(2 * j + 1) << 16;
     for (unsigned j = 0; j < PGI_BLOCK_WORDS; ++j) dst[j] = (uint64_t) w[2 * j] | (uint64_t) w[2 * j + 1] << 32;

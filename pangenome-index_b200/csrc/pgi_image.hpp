@@ -31,7 +31,7 @@ static const uint32_t kSectionElem[SEC_COUNT] = {8, 8, 8, 8, 1, 8, 1, 8, 8, 8, 1
 struct SectionEntry { uint64_t offset, bytes, checksum; };
 
 #define PGI_IMAGE_MAGIC 0x31474D4949475050ull   /* "PPGIIMG1" */
-#define PGI_IMAGE_VERSION 2u   /* 2: crowded buckets as arithmetic sub-buckets, bucket shift up to 12 */
+#define PGI_IMAGE_VERSION 3u   /* 2: crowded buckets as arithmetic sub-buckets, bucket shift up to 12; 3: block headers in limb form */
 #define PGI_IMAGE_ALIGN 4096u
 
 // Everything of an index that is not a big array. POD, written verbatim.

@@ -77,12 +77,23 @@ __device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefe
 __device__ __forceinline__ void cp_async16_if(uint32_t saddr, const void *g, uint32_t blk) {
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\t@p cp.async.cg.shared.global [%0], [%1], 16;\n\t}" ::"r"(saddr), "l"(g), "r"(blk) : "memory");
 }
+// The same with the address formed inside: 16 bytes at base + 64 * blk (one IMAD.WIDE; MODE 2).
+__device__ __forceinline__ void cp_async16_blk(uint32_t saddr, const char *base, uint32_t blk) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\tmad.wide.u32 a, %2, 64, %1;\n\t@p cp.async.cg.shared.global [%0], [a], 16;\n\t}" ::"r"(saddr), "l"(base), "r"(blk) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Words of the lane's own staged block (slot = lane) of position `which`.
+// MODE 2: instead of XOR-swizzling the four parts inside a slot, slot L starts 16 (L >> 1) bytes late (16 bytes of padding
+// behind every second slot): the same part of 8 consecutive lanes then lies in 8 distinct 16-byte bank groups (slot start / 16
+// mod 8 = 0 4 1 5 2 6 3 7), the quad-wise writes stay conflict-free as well, and the four parts sit at IMMEDIATE offsets of
+// one per-lane base address -- no per-trip swizzle arithmetic (MODE 1 spends 21 integer instructions per trip on the
+// addresses of its 8 LDS.128). 4608 instead of 4096 bytes per warp.
+template <int MODE> __device__ __forceinline__ constexpr unsigned stage_slot(unsigned slot) { return MODE == 2 ? 4u * slot + (slot >> 1) : 4u * slot; }   // in 16-byte units
+template <int MODE>
 __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned which, unsigned lane, uint32_t w[16]) {
-    const uint4 *sl = warp_stage + which * 128u + lane * 4u;
-    const unsigned z = (lane >> 1) & 3u;
+    const uint4 *sl = warp_stage + which * stage_slot<MODE>(32u) + stage_slot<MODE>(lane);
+    const unsigned z = MODE == 2 ? 0u : (lane >> 1) & 3u;
     const uint4 a = sl[0u ^ z], b = sl[1u ^ z], c = sl[2u ^ z], d = sl[3u ^ z];
     w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
@@ -104,7 +115,8 @@ template <int MODE, int THREADS, int BPS, int OP = 0>
 __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) {
     __shared__ uint32_t s_desc[512];
     __shared__ uint4 s_tab[MODE ? 512 : 1];                              // scan tables of the descriptors (pos_rank)
-    __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 256 : 1];   // per warp: 2 positions x 32 slots x 4 parts of 16 B
+    constexpr unsigned POS = stage_slot<MODE>(32u), ROUND = stage_slot<MODE>(8u);     // staging geometry in 16-byte units: one position (32 slots), one fetch round (8 slots)
+    __shared__ uint4 s_stage[MODE ? (THREADS / 32) * 2 * POS : 1];       // per warp: 2 positions x 32 slots x 4 parts of 16 B (MODE 2: + 16 B of padding per two slots)
     __shared__ uint32_t s_blk[THREADS / 32];                              // per warp: run blocks fetched (work counter, kept out of the registers)
     if (threadIdx.x < THREADS / 32) s_blk[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < 512; i += blockDim.x) {
@@ -115,9 +127,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     const unsigned lane = threadIdx.x & 31u, FULL = 0xFFFFFFFFu;
     const unsigned lt_mask = (1u << lane) - 1u;
     const uint32_t n_reads = (uint32_t) a.n_reads, min_len = (uint32_t) a.min_len;
-    uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 256u : 0u);
+    uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 2u * POS : 0u);
     // loop-invariant half of the cooperative fetch (MODE 1): where this lane's part of round 0 / position 0 lands in the staging area
-    const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + ((lane >> 2) * 4u + ((lane & 3u) ^ ((lane >> 3) & 3u))) * 16u;
+    const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + (stage_slot<MODE>(lane >> 2) + (MODE == 2 ? (lane & 3u) : ((lane & 3u) ^ ((lane >> 3) & 3u)))) * 16u;
     MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0, n_seed = 0;
@@ -276,8 +288,13 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 for (unsigned r = 0; r < 4; ++r) {
                     const unsigned src = 8u * r + (lane >> 2);
                     const uint32_t x1 = __shfl_sync(FULL, i1, src), x2 = __shfl_sync(FULL, i2, src);
-                    cp_async16_if(st_dst + 512u * r, part_bytes + (uint64_t) x1 * 64u, x1);
-                    cp_async16_if(st_dst + 2048u + 512u * r, part_bytes + (uint64_t) x2 * 64u, x2);
+                    if (MODE == 2) {
+                        cp_async16_blk(st_dst + 16u * ROUND * r, part_bytes, x1);
+                        cp_async16_blk(st_dst + 16u * POS + 16u * ROUND * r, part_bytes, x2);
+                    } else {
+                        cp_async16_if(st_dst + 512u * r, part_bytes + (uint64_t) x1 * 64u, x1);
+                        cp_async16_if(st_dst + 2048u + 512u * r, part_bytes + (uint64_t) x2 * 64u, x2);
+                    }
                 }
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
@@ -295,7 +312,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     seed_ok = true;
                     // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
                     // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
-                    cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + lane * 4u), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
+                    cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
                 }
             }
             cp_async_wait_all();
@@ -313,8 +330,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     if (p2 > a.ix.n) p2 = a.ix.n;
                     if (p1 > a.ix.n) p1 = a.ix.n;
                     const uint32_t mask = (1u << a.ix.bshift) - 1u, rel1 = (uint32_t) p1 & mask, rel2 = (uint32_t) p2 & mask;
-                    const unsigned z = (lane >> 1) & 3u;
-                    const uint4 *sl1 = wstage + lane * 4u, *sl2 = wstage + which2 * 128u + lane * 4u;
+                    const unsigned z = MODE == 2 ? 0u : (lane >> 1) & 3u;
+                    const uint4 *sl1 = wstage + stage_slot<MODE>(lane), *sl2 = wstage + which2 * POS + stage_slot<MODE>(lane);
                     if (rel1 && (sl1[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c1 = staged_chunk_of(sl1, z, rel1);
                     if (rel2 && (sl2[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c2 = staged_chunk_of(sl2, z, rel2);
                 }
@@ -340,9 +357,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 ScanTab T; T.x = tq.x; T.y = tq.y; T.z = tq.z; T.w = tq.w;
                 const uint32_t mask = (1u << a.ix.bshift) - 1u;
                 uint32_t w[16];
-                ld_staged(wstage, 0u, lane, w);
+                ld_staged<MODE>(wstage, 0u, lane, w);
                 const PosRank r1 = pos_rank(w, (uint32_t) p1 & mask, tbl, T);
-                ld_staged(wstage, which2, lane, w);
+                ld_staged<MODE>(wstage, which2, lane, w);
                 const PosRank r2 = pos_rank(w, (uint32_t) p2 & mask, tbl, T);
                 t = extend_finish(a.ix, t, d, r1, r2, p1, p2);
                 BiInt u; u.k = fwd ? t.kp : t.k; u.kp = fwd ? t.k : t.kp; u.s = t.s;
@@ -354,7 +371,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             }
             if (OP == 0 && cand) {
                 if (seed_ok) {
-                    const uint4 e = wstage[lane * 4u];
+                    const uint4 e = wstage[stage_slot<MODE>(lane)];
                     SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
                     const BiInt t = seed_unpack(q);
                     seed_ok = !ext_failed(t, a.min_occ);

@@ -10,10 +10,13 @@
 //
 // One block = 64 bytes = 16 little-endian u32 words (two 32-byte DRAM sectors, one aligned 64 B burst):
 //   w0      normal block: 0;  directory block (below): index of its first chunk block
-//   w1..w4  A, C, G, T, low 32 bits     symbol counts before the first position of the block's runs (40 bits each)
-//   w5, w6  NL, N                       endmarker / 'N' counts before it (32 bits each)
-//   w7      0 | A_hi << 8 | C_hi << 16 | G_hi << 24             (bits 32..39 of the 40-bit fields)
-//   w8      T_hi | spare << 8 | codes 8..11 << 16               (one nibble per run)
+//   w1..w8  the symbol counts before the first position of the block's runs (A, C, G, T: 40 bits; NL, N: 32 bits), cut into
+//           LIMBS and stored in code order ('\n' A C G N T = codes 0..5), so that the weighted sum over the six counts is a
+//           handful of byte dot products against the same 8-byte weight tables the run scan uses (pos_rank):
+//   w1..w3  bits 0..15 of  NL | A << 16,   C | G << 16,   N | T << 16
+//   w4..w6  bits 16..31 of the same pairs
+//   w7      bits 32..39:   0 | A << 8 | C << 16 | G << 24
+//   w8                     0 | T << 8 | codes 8..11 << 16         (one nibble per run)
 //   w9      codes 0..7                                          (one nibble per run, run 0 in the low nibble)
 //   w10..w15 E_0..E_11, two per word (even run in the low half)
 // Run i of the block has symbol code c_i = index into nuc = {'\n','A','C','G','N','T'}
@@ -39,6 +42,20 @@
 // more dependent 64-byte access: dense stretches are rare by the choice of bshift (but not negligible: the first n_seq
 // BWT rows are runs of length 1 next to C['A'], where every search for an 'A' starts).
 #define PGI_BLOCK_U32 16
+// Header words of a block from its six counts cnt[c], c = nuc code ('\n' A C G N T). Leaves the code half of w8 alone.
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+static inline void pgi_put_header(uint32_t *w, const uint64_t cnt[6]) {
+    w[1] = (uint32_t) (cnt[0] & 0xFFFFu) | (uint32_t) (cnt[1] & 0xFFFFu) << 16;
+    w[2] = (uint32_t) (cnt[2] & 0xFFFFu) | (uint32_t) (cnt[3] & 0xFFFFu) << 16;
+    w[3] = (uint32_t) (cnt[4] & 0xFFFFu) | (uint32_t) (cnt[5] & 0xFFFFu) << 16;
+    w[4] = (uint32_t) ((cnt[0] >> 16) & 0xFFFFu) | (uint32_t) ((cnt[1] >> 16) & 0xFFFFu) << 16;
+    w[5] = (uint32_t) ((cnt[2] >> 16) & 0xFFFFu) | (uint32_t) ((cnt[3] >> 16) & 0xFFFFu) << 16;
+    w[6] = (uint32_t) ((cnt[4] >> 16) & 0xFFFFu) | (uint32_t) ((cnt[5] >> 16) & 0xFFFFu) << 16;
+    w[7] = (uint32_t) ((cnt[1] >> 32) & 0xFFu) << 8 | (uint32_t) ((cnt[2] >> 32) & 0xFFu) << 16 | (uint32_t) ((cnt[3] >> 32) & 0xFFu) << 24;
+    w[8] = (w[8] & 0xFFFF0000u) | (uint32_t) ((cnt[5] >> 32) & 0xFFu) << 8;
+}
 #define PGI_BLOCK_WORDS 8            /* the same block counted in u64 words (host vectors are u64) */
 #define PGI_RUNS_PER_BLOCK 12
 #define PGI_CODE_UNUSED 7u

@@ -9,7 +9,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import bench
 
 def main():
-    variants = "04,14,15,16,24,25"
+    variants = "14,24"
     if "--variants" in sys.argv:
         i = sys.argv.index("--variants"); variants = sys.argv[i + 1]; del sys.argv[i:i + 2]
     args = bench.parse_args()
@@ -18,12 +18,12 @@ def main():
     capi = load_package().capi
     torch.cuda.set_device(0)
     w = bench.make_workload(args, 0, 0)
-    ix = capi.Index(w["ri"], w["tags"], w["layout"], device=0)
-    L = args.read_len; n = args.reads_per_step; pool = w["reads"].shape[0]
+    ix = w.ix
+    L = args.read_len; n = args.reads_per_step; pool = w.reads.shape[0]
     d_off = torch.arange(n + 1, dtype=torch.int64, device="cuda") * L
     stream = torch.cuda.current_stream()
     batch = capi.Batch(ix, stream=stream.cuda_stream)
-    d_reads = [torch.cat([w["reads"][i].reshape(-1), torch.zeros(16, dtype=torch.uint8, device="cuda")]) for i in range(pool)]
+    d_reads = [torch.cat([w.reads[i].reshape(-1), torch.zeros(16, dtype=torch.uint8, device="cuda")]) for i in range(pool)]
     out = {}; ref = None
     for v in variants.split(","):
         os.environ["PGI_K1"] = v
@@ -37,7 +37,7 @@ def main():
         if ref is None: ref = sig
         out[v] = {"k1_ms_median": float(np.median(ms)), "k1_ms_min": float(min(ms)), "counts": sig, "same_counts_as_first": sig == ref}
         print("[sweep]", v, out[v], file=sys.stderr, flush=True)
-    print(json.dumps({"reads_per_step": n, "facts": w["facts"], "variants": out}))
+    print(json.dumps({"reads_per_step": n, "facts": w.facts, "variants": out}))
 
 if __name__ == "__main__":
     main()
