@@ -772,7 +772,7 @@ struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads
 const K1Variant &k1_variant() {
     static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
         {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
-        {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256}, {"24", fmd_mem_kernel<2, 256, 4>, 256},
+        {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256}, {"24", fmd_mem_kernel<2, 256, 4>, 256}, {"34", fmd_mem_kernel<3, 256, 4>, 256}, {"3a", fmd_mem_kernel<3, 128, 8>, 128},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process
     if (e) for (const K1Variant &v : table) if (!std::strcmp(v.name, e)) return v;

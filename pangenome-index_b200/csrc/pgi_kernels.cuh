@@ -89,11 +89,11 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // mod 8 = 0 4 1 5 2 6 3 7), the quad-wise writes stay conflict-free as well, and the four parts sit at IMMEDIATE offsets of
 // one per-lane base address -- no per-trip swizzle arithmetic (MODE 1 spends 21 integer instructions per trip on the
 // addresses of its 8 LDS.128). 4608 instead of 4096 bytes per warp.
-template <int MODE> __device__ __forceinline__ constexpr unsigned stage_slot(unsigned slot) { return MODE == 2 ? 4u * slot + (slot >> 1) : 4u * slot; }   // in 16-byte units
+template <int MODE> __device__ __forceinline__ constexpr unsigned stage_slot(unsigned slot) { return MODE >= 2 ? 4u * slot + (slot >> 1) : 4u * slot; }   // in 16-byte units
 template <int MODE>
 __device__ __forceinline__ void ld_staged(const uint4 *warp_stage, unsigned which, unsigned lane, uint32_t w[16]) {
     const uint4 *sl = warp_stage + which * stage_slot<MODE>(32u) + stage_slot<MODE>(lane);
-    const unsigned z = MODE == 2 ? 0u : (lane >> 1) & 3u;
+    const unsigned z = MODE >= 2 ? 0u : (lane >> 1) & 3u;
     const uint4 a = sl[0u ^ z], b = sl[1u ^ z], c = sl[2u ^ z], d = sl[3u ^ z];
     w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
     w[8] = c.x; w[9] = c.y; w[10] = c.z; w[11] = c.w; w[12] = d.x; w[13] = d.y; w[14] = d.z; w[15] = d.w;
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     const uint32_t n_reads = (uint32_t) a.n_reads, min_len = (uint32_t) a.min_len;
     uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 2u * POS : 0u);
     // loop-invariant half of the cooperative fetch (MODE 1): where this lane's part of round 0 / position 0 lands in the staging area
-    const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + (stage_slot<MODE>(lane >> 2) + (MODE == 2 ? (lane & 3u) : ((lane & 3u) ^ ((lane >> 3) & 3u)))) * 16u;
+    const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + (stage_slot<MODE>(lane >> 2) + (MODE >= 2 ? (lane & 3u) : ((lane & 3u) ^ ((lane >> 3) & 3u)))) * 16u;
     MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0, n_seed = 0;
@@ -137,6 +137,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     // 1: the seed lookup of the pending walk was tried and its entry fails the occurrence test: extend step by step;
     // 2: the read holds a byte other than A / C / G / T: no lookups at all (until the next read)
     uint32_t stepwise = 0;
+    // MODE 3: chunk blocks of the pending extension's two positions, found in the previous trip (see (2b)); PGI_NOBLK = none
+    uint32_t pend1 = PGI_NOBLK, pend2 = PGI_NOBLK;
     const uint32_t seed_k = OP == 0 ? a.seed_k : 0u;
     for (;;) {
         // ---- hand out reads to idle lanes
@@ -275,6 +277,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 b1 = (uint32_t) (p1 >> a.ix.bshift);
                 const uint32_t bb = (uint32_t) (p2 >> a.ix.bshift);
                 if (bb != b1) b2 = bb;
+                if (MODE == 3) { if (pend1 != PGI_NOBLK) b1 = pend1; if (pend2 != PGI_NOBLK) b2 = pend2; }
             }
             // (2) the warp fetches the blocks together: quad q of round r serves slot 8 r + q
             const unsigned part = lane & 3u;
@@ -288,7 +291,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 for (unsigned r = 0; r < 4; ++r) {
                     const unsigned src = 8u * r + (lane >> 2);
                     const uint32_t x1 = __shfl_sync(FULL, i1, src), x2 = __shfl_sync(FULL, i2, src);
-                    if (MODE == 2) {
+                    if (MODE >= 2) {
                         cp_async16_blk(st_dst + 16u * ROUND * r, part_bytes, x1);
                         cp_async16_blk(st_dst + 16u * POS + 16u * ROUND * r, part_bytes, x2);
                     } else {
@@ -298,7 +301,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
-            PGI_CHECK(b1 == PGI_NOBLK || b1 < a.ix.n_buckets_dbg); PGI_CHECK(b2 == PGI_NOBLK || b2 < a.ix.n_buckets_dbg);
+            PGI_CHECK(b1 == PGI_NOBLK || b1 < (MODE == 3 ? a.ix.n_blocks : a.ix.n_buckets_dbg)); PGI_CHECK(b2 == PGI_NOBLK || b2 < (MODE == 3 ? a.ix.n_blocks : a.ix.n_buckets_dbg));
             coop_issue(b1, b2);
             {
                 const unsigned nb = __popc(__ballot_sync(FULL, b1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, b2 != PGI_NOBLK));
@@ -322,7 +325,12 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             // below stays ONE converged code path (a per-lane slow path here ran at 1.8 active lanes and cost half as many
             // warp instructions as the scan itself: every fresh interval starts at position 0 of the crowded bucket 0).
             // Offset 0 needs no chunk: the directory block's own header holds the counts before the bucket.
+            // MODE 3 takes the second fetch OUT of the trip: a lane that finds a directory block remembers its chunk blocks
+            // (pend1 / pend2), skips this trip's scan and fetches them as ITS blocks in the next trip, together with everybody
+            // else's (a chunk block is never a directory). One extension in 17 then takes two trips, but no trip waits for
+            // two dependent memory round trips any more -- and some lane of a warp met a directory in 84 % of the trips.
             unsigned which2 = b2 != PGI_NOBLK ? 1u : 0u;
+            bool defer = false;
             {
                 uint32_t c1 = PGI_NOBLK, c2 = PGI_NOBLK;
                 if (need) {
@@ -330,12 +338,15 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     if (p2 > a.ix.n) p2 = a.ix.n;
                     if (p1 > a.ix.n) p1 = a.ix.n;
                     const uint32_t mask = (1u << a.ix.bshift) - 1u, rel1 = (uint32_t) p1 & mask, rel2 = (uint32_t) p2 & mask;
-                    const unsigned z = MODE == 2 ? 0u : (lane >> 1) & 3u;
+                    const unsigned z = MODE >= 2 ? 0u : (lane >> 1) & 3u;
                     const uint4 *sl1 = wstage + stage_slot<MODE>(lane), *sl2 = wstage + which2 * POS + stage_slot<MODE>(lane);
                     if (rel1 && (sl1[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c1 = staged_chunk_of(sl1, z, rel1);
                     if (rel2 && (sl2[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c2 = staged_chunk_of(sl2, z, rel2);
                 }
-                if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
+                if (MODE == 3) {
+                    defer = (c1 & c2) != PGI_NOBLK;
+                    if (defer) { pend1 = c1; pend2 = c2; }
+                } else if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
                     __syncwarp();                             // every lane has read its directory words
                     PGI_CHECK(c1 == PGI_NOBLK || (c1 >= a.ix.n_buckets_dbg && c1 < a.ix.n_blocks)); PGI_CHECK(c2 == PGI_NOBLK || (c2 >= a.ix.n_buckets_dbg && c2 < a.ix.n_blocks));
                     const unsigned nc = __popc(__ballot_sync(FULL, c1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, c2 != PGI_NOBLK));
@@ -347,7 +358,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             asm volatile("" : "+l"(cw));                      // pins the use of the read window behind the wait
             if (has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
             // (3) every lane with work scans its own blocks out of shared memory
-            if (need) {
+            if (need && !defer) {
+                if (MODE == 3) pend1 = pend2 = PGI_NOBLK;
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
                 uint64_t p1 = t.k, p2 = p1 + (uint64_t) t.s;
                 if (p2 > a.ix.n) p2 = a.ix.n;
