@@ -359,6 +359,29 @@ def main():
         log("device-only run: %.3f ms per step, fmd_mem_kernel %.3f ms, L2 fetch granularity %d B, K1 variant %s" % (dev_ms / args.steps, k1_ms / args.steps, l2_fetch, os.environ.get("PGI_K1", "default")))
         sampler.stop_flag = True
         return
+    # ---- the same steps with TWO batches in flight from this one host thread (pgi_batch_run_async / pgi_batch_wait, only the
+    # fmd_mem_kernel launches ordered on the GPU: PGI_CHAIN=3): the next step's persistent grid takes the SMs that the previous
+    # one's last reads leave idle and the short ordering / tag kernels run beside it. Reported next to `value`, not as it: the
+    # per-kernel timings of the roofline object need one step at a time.
+    pipelined = None
+    if not args.no_extras:
+        old_chain = os.environ.get("PGI_CHAIN"); os.environ["PGI_CHAIN"] = "3"
+        b2 = [batch, capi.Batch(ix)]
+        def run_pipe(k_steps, first):
+            fl = []
+            for i in range(k_steps):
+                b = b2[i % 2]
+                if len(fl) == 2: fl.pop(0).wait()
+                b.set_device_reads(d_reads[(first + i) % pool].data_ptr(), d_off.data_ptr(), n, n * L); b.run_async(args.min_len, args.min_occ); fl.append(b)
+            for b in fl: b.wait()
+        run_pipe(max(2, args.warmup), 0); barrier()
+        tp = time.perf_counter(); run_pipe(args.steps, args.warmup); torch.cuda.synchronize(); pipe_ms = 1e3 * (time.perf_counter() - tp)
+        barrier()
+        b2[1].close()
+        if old_chain is None: os.environ.pop("PGI_CHAIN", None)
+        else: os.environ["PGI_CHAIN"] = old_chain
+        pipelined = {"value": n * args.steps / (pipe_ms * 1e-3), "unit": "reads/s per GPU (rank 0)", "ms_per_step": pipe_ms / args.steps, "batches_in_flight": 2,
+                     "note": "pgi_batch_run_async / pgi_batch_wait, fmd_mem_kernel launches chained on the GPU (PGI_CHAIN=3); host wall clock"}
     # ---- end-to-end timing: K calls of pgi_find_mems (pinned host buffers in, all result arrays out to pinned host memory),
     # issued by E2E_CALLERS host threads the way the batched find_mems driver does, so the copies of one call overlap the
     # kernels of another. Wall clock around all K calls (every call blocks until its result is in host memory).
@@ -509,6 +532,7 @@ def main():
                        "parity_vs_reference_code": parity_ref, "parity_small_batch_path": parity_small, "batch_digest": batch_digest, "positions_beyond_32_bits": wide,
                        "mems_per_read": float(cnt[2]) / total_reads, "tags_per_read": float(cnt[3]) / total_reads,
                        "extensions_per_read": float(cnt[1]) / total_reads, "step_reruns": reruns},
+            "pipelined": pipelined,
             "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": n * L, "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e2e_ms / args.steps, "concurrent_callers": E2E_CALLERS,
                     "api": "pgi_find_mems_compact: pinned host reads in (fixed length, no offset array), every result array out to pinned host memory in the compact wire form (packed on the GPU; pgi_result_expand restores the reference-layout arrays on the host when a caller wants them)",
                     "bytes_per_read": (n * L + d2h / args.steps) / n,

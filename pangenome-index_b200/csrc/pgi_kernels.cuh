@@ -137,8 +137,6 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     // 1: the seed lookup of the pending walk was tried and its entry fails the occurrence test: extend step by step;
     // 2: the read holds a byte other than A / C / G / T: no lookups at all (until the next read)
     uint32_t stepwise = 0;
-    // MODE 3: chunk blocks of the pending extension's two positions, found in the previous trip (see (2b)); PGI_NOBLK = none
-    uint32_t pend1 = PGI_NOBLK, pend2 = PGI_NOBLK;
     const uint32_t seed_k = OP == 0 ? a.seed_k : 0u;
     for (;;) {
         // ---- hand out reads to idle lanes
@@ -170,8 +168,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                         L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) a.ix.n;
                     }
                     const char *rp = reinterpret_cast<const char *>(a.reads64) + base;      // pull the read towards L2
-                    for (uint32_t o = 0; o < L.len && o < 512; o += 128) prefetch_l2(rp + o);
-                    if (OP == 0 && seed_k && !stepwise) {                   // and its 2-bit codes (a quarter of the bytes): the seed lookups read them
+                    if (!(OP == 0 && seed_k && !stepwise)) for (uint32_t o = 0; o < L.len && o < 512; o += 128) prefetch_l2(rp + o);
+                    if (OP == 0 && seed_k && !stepwise) {                   // or its 2-bit codes (a quarter of the bytes): symbols and seed lookups read those
                         const char *cp = reinterpret_cast<const char *>(a.codes32) + (base >> 2);
                         for (uint32_t o = 0; o < (L.len >> 2) + 4u && o < 1024; o += 128) prefetch_l2(cp + o);
                     }
@@ -233,18 +231,32 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 need = false;                                             // no run blocks for this lane in this trip
             }
         }
+        // The symbol comes from the lane's cached 8-byte window of the read. A read of nothing but A / C / G / T (no flag from
+        // pack_reads_kernel) is walked through its 2-BIT CODES instead of its bytes: one window then holds 32 symbols instead
+        // of 8. The L2 turns over every 25 us under this kernel (5 TB/s through 126 MB), so every new window of a read is a
+        // DRAM access of its own: 19 per pass over a 150-base read as bytes, 5 as codes (reads + codes were 11 % of the
+        // kernel's DRAM traffic, profiles/r02r).
         uint32_t sym = 0;
         const bool fwd = OP == 0 && L.phase == PH_P2;
         const bool has_sym = need && L.j < L.len;
+        const bool by_code = OP == 0 && seed_k != 0 && !(stepwise & 2u);
         if (has_sym) {
             const uint64_t o = base + L.j;
             PGI_CHECK(o < a.reads_bytes);
-            if ((o >> 3) != cwi) {
-                cwi = o >> 3; cw = __ldcs(a.reads64 + cwi);
-                if (L.len > 512) prefetch_l2(a.reads64 + cwi + (fwd ? 16 : -16));       // long reads: stay ahead in the walking direction
+            const uint64_t wi = by_code ? (o >> 5) | (1ull << 63) : o >> 3;           // the tag keeps the two kinds of window apart
+            if (wi != cwi) {
+                const uint64_t *src = by_code ? reinterpret_cast<const uint64_t *>(a.codes32) + (o >> 5) : a.reads64 + (o >> 3);
+                cwi = wi; cw = __ldcs(src);
+                if (L.len > 512) prefetch_l2(src + (fwd ? 16 : -16));                  // long reads: stay ahead in the walking direction
             }
         }
-        if (MODE == 0 && has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
+        auto symbol_of = [&](uint64_t win) -> uint32_t {
+            const uint32_t o = (uint32_t) (base + L.j);
+            const uint32_t as_code = (0x47544341u >> (8u * ((uint32_t) (win >> (2u * (o & 31u))) & 3u))) & 0xFFu;   // "ACTG"[code] (pgi_core.cuh seed_symbol)
+            const uint32_t as_byte = (uint32_t) (win >> ((o & 7u) * 8u)) & 0xFFu;
+            return by_code ? as_code : as_byte;
+        };
+        if (MODE == 0 && has_sym) sym = symbol_of(cw);
         if (MODE == 0 && OP == 0 && cand) {
             bool ok = true;
             {
@@ -277,7 +289,6 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 b1 = (uint32_t) (p1 >> a.ix.bshift);
                 const uint32_t bb = (uint32_t) (p2 >> a.ix.bshift);
                 if (bb != b1) b2 = bb;
-                if (MODE == 3) { if (pend1 != PGI_NOBLK) b1 = pend1; if (pend2 != PGI_NOBLK) b2 = pend2; }
             }
             // (2) the warp fetches the blocks together: quad q of round r serves slot 8 r + q
             const unsigned part = lane & 3u;
@@ -301,7 +312,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
             };
             auto coop_fetch = [&](uint32_t i1, uint32_t i2) { coop_issue(i1, i2); cp_async_wait_all(); __syncwarp(); };
-            PGI_CHECK(b1 == PGI_NOBLK || b1 < (MODE == 3 ? a.ix.n_blocks : a.ix.n_buckets_dbg)); PGI_CHECK(b2 == PGI_NOBLK || b2 < (MODE == 3 ? a.ix.n_blocks : a.ix.n_buckets_dbg));
+            PGI_CHECK(b1 == PGI_NOBLK || b1 < a.ix.n_buckets_dbg); PGI_CHECK(b2 == PGI_NOBLK || b2 < a.ix.n_buckets_dbg);
             coop_issue(b1, b2);
             {
                 const unsigned nb = __popc(__ballot_sync(FULL, b1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, b2 != PGI_NOBLK));
@@ -325,12 +336,10 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
             // below stays ONE converged code path (a per-lane slow path here ran at 1.8 active lanes and cost half as many
             // warp instructions as the scan itself: every fresh interval starts at position 0 of the crowded bucket 0).
             // Offset 0 needs no chunk: the directory block's own header holds the counts before the bucket.
-            // MODE 3 takes the second fetch OUT of the trip: a lane that finds a directory block remembers its chunk blocks
-            // (pend1 / pend2), skips this trip's scan and fetches them as ITS blocks in the next trip, together with everybody
-            // else's (a chunk block is never a directory). One extension in 17 then takes two trips, but no trip waits for
-            // two dependent memory round trips any more -- and some lane of a warp met a directory in 84 % of the trips.
+            // (Taking this second fetch OUT of the trip -- the lane remembers its chunk blocks, skips the scan and fetches them
+            // as its blocks in the next trip -- was measured: 8.67 ms against 8.47 ms, profiles/r02z: the kernel is bound by
+            // DRAM accesses, not by the dependent round trip, and the deferred lanes fetch their other block twice.)
             unsigned which2 = b2 != PGI_NOBLK ? 1u : 0u;
-            bool defer = false;
             {
                 uint32_t c1 = PGI_NOBLK, c2 = PGI_NOBLK;
                 if (need) {
@@ -343,10 +352,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     if (rel1 && (sl1[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c1 = staged_chunk_of(sl1, z, rel1);
                     if (rel2 && (sl2[2u ^ z].y & 0xFu) == PGI_CODE_DIRBLOCK) c2 = staged_chunk_of(sl2, z, rel2);
                 }
-                if (MODE == 3) {
-                    defer = (c1 & c2) != PGI_NOBLK;
-                    if (defer) { pend1 = c1; pend2 = c2; }
-                } else if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
+                if (__any_sync(FULL, (c1 & c2) != PGI_NOBLK)) {
                     __syncwarp();                             // every lane has read its directory words
                     PGI_CHECK(c1 == PGI_NOBLK || (c1 >= a.ix.n_buckets_dbg && c1 < a.ix.n_blocks)); PGI_CHECK(c2 == PGI_NOBLK || (c2 >= a.ix.n_buckets_dbg && c2 < a.ix.n_blocks));
                     const unsigned nc = __popc(__ballot_sync(FULL, c1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, c2 != PGI_NOBLK));
@@ -356,10 +362,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
             }
             asm volatile("" : "+l"(cw));                      // pins the use of the read window behind the wait
-            if (has_sym) sym = (uint32_t) (cw >> (((base + L.j) & 7) * 8)) & 0xFFu;
+            if (has_sym) sym = symbol_of(cw);
             // (3) every lane with work scans its own blocks out of shared memory
-            if (need && !defer) {
-                if (MODE == 3) pend1 = pend2 = PGI_NOBLK;
+            if (need) {
                 BiInt t; t.k = fwd ? L.b.kp : L.b.k; t.kp = fwd ? L.b.k : L.b.kp; t.s = L.b.s;
                 uint64_t p1 = t.k, p2 = p1 + (uint64_t) t.s;
                 if (p2 > a.ix.n) p2 = a.ix.n;

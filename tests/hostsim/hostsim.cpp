@@ -15,6 +15,8 @@ using namespace pgi;
 
 struct sim_index { RiImage ri; TagImage tg; bool has_tags = false; RiDev rd; TagDev td; uint32_t seed_k = 0; std::vector<SeedWord> seed; };
 static thread_local std::string g_err;
+// optional trace of the positions every executed extension ranks (tools/trace_blocks.py: which blocks does a batch touch?)
+static std::vector<uint64_t> *g_trace = nullptr;
 
 static void bind(sim_index *s) {
     RiDev &d = s->rd; const RiImage &im = s->ri;
@@ -104,6 +106,7 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
         stepwise &= 2u;
         const unsigned a = L.j < len ? (unsigned char) read[L.j] : 0;
         BiInt t = L.b;
+        if (g_trace) { const uint64_t p1 = L.phase == PH_P2 ? t.kp : t.k; g_trace->push_back(p1); g_trace->push_back(p1 + (uint64_t) t.s); g_trace->push_back(L.phase); }
         if (L.phase == PH_P2) { std::swap(t.k, t.kp); t = extend_desc(s->rd, t, s->ri.k.desc_f[a]); std::swap(t.k, t.kp); }
         else t = extend_desc(s->rd, t, s->ri.k.desc_b[a]);
         ++ext;
@@ -112,6 +115,16 @@ uint64_t sim_find_mems(const sim_index *s, const char *read, uint64_t len, uint6
     if (n_ext) *n_ext = ext;
     return nm;
 }
+// Trace control: sim_trace(1) starts recording {p1, p2, phase} per executed extension, sim_trace(0) stops; sim_trace_read copies.
+void sim_trace(int on) { delete g_trace; g_trace = on ? new std::vector<uint64_t>() : nullptr; }
+uint64_t sim_trace_read(uint64_t *out, uint64_t cap) {
+    if (!g_trace) return 0;
+    const uint64_t n = std::min<uint64_t>(cap, g_trace->size());
+    if (out) std::memcpy(out, g_trace->data(), n * 8);
+    return g_trace->size();
+}
+// one block as 16 u32 words (tools)
+void sim_block(const sim_index *s, uint64_t b, uint32_t *w16) { for (int i = 0; i < 8; ++i) { w16[2 * i] = (uint32_t) s->ri.blocks[b * 8 + i]; w16[2 * i + 1] = (uint32_t) (s->ri.blocks[b * 8 + i] >> 32); } }
 // Whole-read backward search through the count descriptors (desc_c) and extend_desc, as fmd_mem_kernel's OP 1 does:
 // out2 = {range.first, size} (no match: {1, 0}). Returns 0, or 1 when the index refuses counting (count_ok == 0).
 int sim_count(const sim_index *s, const char *read, uint64_t len, uint64_t *out2) {
