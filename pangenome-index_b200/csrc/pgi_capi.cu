@@ -771,7 +771,7 @@ uint64_t read_back(pgi_batch *b, const void *dptr) {              // locate only
 struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads; };
 const K1Variant &k1_variant() {
     static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
-        {"24", fmd_mem_kernel<2, 256, 4>, 256}, {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
+        {"44", fmd_mem_kernel<4, 256, 4>, 256}, {"24", fmd_mem_kernel<2, 256, 4>, 256}, {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
         {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256}, {"2a", fmd_mem_kernel<2, 128, 8>, 128},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process
@@ -871,7 +871,7 @@ __global__ void iota_kernel(uint64_t n_plus_1, uint64_t *out) {
 void enqueue_count_stage(pgi_batch *b, int &launches) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
     b->d_mem_off.need((n + 1) * 8); b->d_mems.need((n + 1) * 32);
-    void (*fn)(const MemArgs) = fmd_mem_kernel<2, 256, 4, 1>; const unsigned threads = 256;
+    void (*fn)(const MemArgs) = fmd_mem_kernel<4, 256, 4, 1>; const unsigned threads = 256;
     const unsigned grid = persistent_grid(ix, fn, threads, n);
     unsigned long long *st = b->d_ctr.as<unsigned long long>();
     CK(cudaMemsetAsync(st, 0, ST_WORDS * 8, b->stream));

@@ -81,6 +81,17 @@ __device__ __forceinline__ void cp_async16_if(uint32_t saddr, const void *g, uin
 __device__ __forceinline__ void cp_async16_blk(uint32_t saddr, const char *base, uint32_t blk) {
     asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\tmad.wide.u32 a, %2, 64, %1;\n\t@p cp.async.cg.shared.global [%0], [a], 16;\n\t}" ::"r"(saddr), "l"(base), "r"(blk) : "memory");
 }
+// MODE 4: the same copy with an L2 evict-first policy: run blocks and seed entries are random accesses without reuse, and at
+// 5 TB/s they turn the whole L2 over every 25 us, taking the batch's 2-bit codes (75 MB, written by pack_reads_kernel just
+// before, read again window by window) with them. Measured: 7.98 ms against 8.04 ms (profiles/r03e; asking the code loads
+// for evict-last on top changed nothing).
+__device__ __forceinline__ uint64_t l2_evict_first_policy() { uint64_t p; asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p; }
+__device__ __forceinline__ void cp_async16_blk_ef(uint32_t saddr, const char *base, uint32_t blk, uint64_t pol) {
+    asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\tmad.wide.u32 a, %2, 64, %1;\n\t@p cp.async.cg.shared.global.L2::cache_hint [%0], [a], 16, %3;\n\t}" ::"r"(saddr), "l"(base), "r"(blk), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async16_ef(uint32_t saddr, const void *g, uint64_t pol) {
+    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(saddr), "l"(g), "l"(pol) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // Words of the lane's own staged block (slot = lane) of position `which`.
@@ -130,6 +141,7 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
     uint4 *const wstage = s_stage + (MODE ? (threadIdx.x >> 5) * 2u * POS : 0u);
     // loop-invariant half of the cooperative fetch (MODE 1): where this lane's part of round 0 / position 0 lands in the staging area
     const uint32_t st_dst = (uint32_t) __cvta_generic_to_shared(wstage) + (stage_slot<MODE>(lane >> 2) + (MODE >= 2 ? (lane & 3u) : ((lane & 3u) ^ ((lane >> 3) & 3u)))) * 16u;
+    const uint64_t l2pol = MODE >= 4 ? l2_evict_first_policy() : 0ull;
     MemLane L; L.phase = PH_DONE; L.len = 0; L.x = 0; L.j = 0; L.b.k = L.b.kp = 0; L.b.s = 0;
     uint64_t base = 0, cw = 0, cwi = ~0ull;      // cw: cached 8-byte window of the read
     uint32_t rd = 0, wq_next = 0, wq_end = 0, n_ext = 0, nm = 0, n_seed = 0;
@@ -302,7 +314,10 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 for (unsigned r = 0; r < 4; ++r) {
                     const unsigned src = 8u * r + (lane >> 2);
                     const uint32_t x1 = __shfl_sync(FULL, i1, src), x2 = __shfl_sync(FULL, i2, src);
-                    if (MODE >= 2) {
+                    if (MODE >= 4) {
+                        cp_async16_blk_ef(st_dst + 16u * ROUND * r, part_bytes, x1, l2pol);
+                        cp_async16_blk_ef(st_dst + 16u * POS + 16u * ROUND * r, part_bytes, x2, l2pol);
+                    } else if (MODE >= 2) {
                         cp_async16_blk(st_dst + 16u * ROUND * r, part_bytes, x1);
                         cp_async16_blk(st_dst + 16u * POS + 16u * ROUND * r, part_bytes, x2);
                     } else {
@@ -326,7 +341,8 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                     seed_ok = true;
                     // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
                     // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
-                    cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
+                    if (MODE >= 4) cp_async16_ef((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, l2pol);
+                    else cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
                 }
             }
             cp_async_wait_all();
