@@ -295,46 +295,51 @@ PGI_HD void lane_begin(MemLane &L, uint64_t len, uint32_t min_len, uint64_t n) {
     lane_return(L, 0, min_len, n);
 }
 
-// Advance through loop heads until the lane needs an extension (LANE_EXTEND; symbol position = L.j, forward iff
+// Advance through the loop heads until the lane needs an extension (LANE_EXTEND; symbol position = L.j, forward iff
 // phase == PH_P2), has the MEM {x, j, b.k, b.s} to write (LANE_EMIT; call lane_emitted, then settle again) or is done.
+// STRAIGHT-LINE: every transition is a select, taken in the one order in which they can follow each other
+//     P3 walked down to x: `return j + 1` -> next find_mems_function call (P1) or done
+//     P1 walked down to x: bint2 = bint, j = x + min_len (P2)
+//     P2 reached the end of the read: emit
+// so the 32 lanes of a warp, which sit in different phases, execute it once together (the switch-in-a-loop form of round 1
+// ran once per phase present in the warp: 15 of 32 threads active, a seventh of the kernel's instructions). One call
+// passes at most one emit; after an emit the lane is in P3 with j = e >= x + min_len, i.e. it extends next when
+// min_len >= 1 (callers that allow min_len = 0 call again, like the host harness does after every emit).
 PGI_HD int lane_settle(MemLane &L, uint32_t min_len, uint64_t n) {
-    for (;;) {
-        switch (L.phase) {
-        case PH_P1:
-            if ((int32_t) L.j >= (int32_t) L.x) return LANE_EXTEND;
-            L.j = L.x + min_len; L.phase = PH_P2;                                    // bint2 = bint
-            break;
-        case PH_P2:
-            if (L.j < L.len) return LANE_EXTEND;
-            L.phase = PH_EMIT;
-            break;
-        case PH_EMIT:
-            return LANE_EMIT;                                                          // output.push_back({x, e = j, bint2})
-        case PH_P3:
-            if (L.j > L.x) return LANE_EXTEND;
-            lane_return(L, L.j + 1, min_len, n);
-            break;
-        default:
-            return LANE_DONE;
-        }
-    }
+    uint32_t ph = L.phase, j = L.j, x = L.x;
+    const uint32_t len = L.len;
+    // `return v` of find_mems_function, the `while (x < len)` of find_all_mems and the entry checks of the next call
+    const bool ret = ph == PH_P3 && j <= x;
+    const uint32_t v = j + 1u;
+    const bool done = v >= len || len - v < min_len;
+    const bool again = ret && !done;
+    x = ret ? (done ? len : v) : x;
+    ph = ret ? (done ? (uint32_t) PH_DONE : (uint32_t) PH_P1) : ph;
+    j = again ? v + min_len - 1u : j;
+    L.b.k = again ? 0ull : L.b.k; L.b.kp = again ? 0ull : L.b.kp; L.b.s = again ? (int64_t) n : L.b.s;
+    const bool p1_end = ph == PH_P1 && (int32_t) j < (int32_t) x;
+    j = p1_end ? x + min_len : j; ph = p1_end ? (uint32_t) PH_P2 : ph;                 // bint2 = bint
+    ph = (ph == PH_P2 && j >= len) ? (uint32_t) PH_EMIT : ph;                            // output.push_back({x, e = j, bint2})
+    L.phase = ph; L.j = j; L.x = x;
+    return ph == PH_EMIT ? LANE_EMIT : ph == PH_DONE ? LANE_DONE : LANE_EXTEND;
 }
 PGI_HD void lane_emitted(MemLane &L, uint64_t n) {
     L.b.k = 0; L.b.kp = 0; L.b.s = (int64_t) n; L.phase = PH_P3;                       // back = full interval; j = e
 }
 
-// Bookkeeping after the extension requested by lane_settle produced t (in the orientation of L.b).
+// Bookkeeping after the extension requested by lane_settle produced t (in the orientation of L.b). Selects only.
+// Walking left (P1 / P3) a failure is `return j + 1`: handed to lane_settle as "P3 arrived at x = j"; a success steps to
+// j - 1, which may wrap below zero at j = 0 -- lane_settle compares j and x as signed numbers.
 PGI_HD void lane_after_ext(MemLane &L, const BiInt &t, uint32_t min_len, uint64_t min_occ, uint64_t n) {
+    (void) min_len; (void) n;
     const bool fail = ext_failed(t, min_occ);
-    if (L.phase == PH_P2) {
-        if (fail) L.phase = PH_EMIT;                                                   // b stays bint2
-        else { L.b = t; ++L.j; }
-    } else {                                                                           // PH_P1 / PH_P3: walking left
-        L.b = t;
-        if (fail) lane_return(L, L.j + 1, min_len, n);
-        else if (L.phase == PH_P1 && L.j == 0) { L.j = L.x + min_len; L.phase = PH_P2; }
-        else --L.j;
-    }
+    const bool p2 = L.phase == PH_P2;
+    const bool commit = !(p2 && fail);                                                  // a failed forward extension is not committed: b stays bint2
+    L.b.k = commit ? t.k : L.b.k; L.b.kp = commit ? t.kp : L.b.kp; L.b.s = commit ? t.s : L.b.s;
+    const bool left_fail = !p2 && fail;
+    L.x = left_fail ? L.j : L.x;
+    L.phase = p2 ? (fail ? (uint32_t) PH_EMIT : (uint32_t) PH_P2) : (left_fail ? (uint32_t) PH_P3 : L.phase);
+    L.j = p2 ? (fail ? L.j : L.j + 1u) : (fail ? L.j : L.j - 1u);
 }
 
 // ------------------------------------------------------------------------------------ seed table
@@ -389,16 +394,15 @@ PGI_HD uint32_t seed_index_packed(uint32_t c0, uint32_t c1, uint64_t lo, uint32_
 }
 // Does the extension lane_settle just asked for start from the full interval with K symbols in reach?
 PGI_HD bool lane_seed_ready(const MemLane &L, uint32_t K, uint64_t n) {
-    if (L.b.s != (int64_t) n || (L.b.k | L.b.kp) != 0) return false;
-    if (L.phase == PH_P1) return L.j + 1u >= L.x + K;                                 // symbols j, j - 1, ..., j - K + 1 >= x
-    if (L.phase == PH_P3) return L.j < L.len && L.j >= L.x + K;                       // ... >= x + 1; pattern[len] is not a read byte
-    return false;
+    const bool full = L.b.s == (int64_t) n && (L.b.k | L.b.kp) == 0;
+    const bool p1 = L.phase == PH_P1 && L.j + 1u >= L.x + K;                           // symbols j, j - 1, ..., j - K + 1 >= x
+    const bool p3 = L.phase == PH_P3 && L.j < L.len && L.j >= L.x + K;                 // ... >= x + 1; pattern[len] is not a read byte
+    return full && (p1 || p3);
 }
-// K successful lane_after_ext steps at once (t = the table entry, known to pass ext_failed).
+// K successful lane_after_ext steps at once (t = the table entry, known to pass ext_failed). j may wrap below zero like there.
 PGI_HD void lane_seed_apply(MemLane &L, const BiInt &t, uint32_t K, uint32_t min_len) {
-    L.b = t;
-    if (L.phase == PH_P1 && L.j + 1u == K) { L.j = L.x + min_len; L.phase = PH_P2; }  // the K-th step was the one at j == 0
-    else L.j -= K;
+    (void) min_len;
+    L.b = t; L.j -= K;
 }
 // Entry of K-mer idx: K backward extensions from the full interval; {0, 0, 0} as soon as one comes back empty.
 PGI_HD SeedWord seed_entry(const RiDev &ix, const uint32_t *desc_b, uint32_t idx, uint32_t K) {

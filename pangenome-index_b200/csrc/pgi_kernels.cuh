@@ -89,8 +89,8 @@ __device__ __forceinline__ uint64_t l2_evict_first_policy() { uint64_t p; asm("c
 __device__ __forceinline__ void cp_async16_blk_ef(uint32_t saddr, const char *base, uint32_t blk, uint64_t pol) {
     asm volatile("{\n\t.reg .pred p;\n\t.reg .u64 a;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\tmad.wide.u32 a, %2, 64, %1;\n\t@p cp.async.cg.shared.global.L2::cache_hint [%0], [a], 16, %3;\n\t}" ::"r"(saddr), "l"(base), "r"(blk), "l"(pol) : "memory");
 }
-__device__ __forceinline__ void cp_async16_ef(uint32_t saddr, const void *g, uint64_t pol) {
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(saddr), "l"(g), "l"(pol) : "memory");
+__device__ __forceinline__ void cp_async16_if_ef(uint32_t saddr, const void *g, uint32_t blk, uint64_t pol) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0xffffffff;\n\t@p cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %3;\n\t}" ::"r"(saddr), "l"(g), "r"(blk), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
@@ -202,8 +202,9 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 have = false;
             }
         } else if (have) {
-            int st;
-            while ((st = lane_settle(L, min_len, a.ix.n)) == LANE_EMIT) {
+            // lane_settle is straight-line (pgi_core.cuh): one call, at most one MEM to write, and behind an emit the lane
+            // extends (min_len >= 1); only min_len = 0 -- a uniform branch -- needs the call repeated
+            auto emit = [&]() {
                 unsigned long long slot; bool fits;
                 if (a.part_cap) {
                     const unsigned part = (blockIdx.x * (THREADS / 32u) + (threadIdx.x >> 5)) & (PGI_SLOT_PARTS - 1u);
@@ -218,6 +219,11 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 }
                 ++nm;
                 lane_emitted(L, a.ix.n);
+            };
+            int st = lane_settle(L, min_len, a.ix.n);
+            if (st == LANE_EMIT) {
+                emit(); st = LANE_EXTEND;
+                if (min_len == 0) while ((st = lane_settle(L, min_len, a.ix.n)) == LANE_EMIT) emit();
             }
             need = st == LANE_EXTEND;
             if (!need) { a.read_nmems[rd] = nm; have = false; }
@@ -233,15 +239,15 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         // reach fetches ONE table entry in this trip instead of its run blocks and advances seed_k steps at once. The
         // window of the read is requested here; the index is formed and the entry's cp.async joins the block fetch's
         // group below, so the lookup costs no dependent latency beyond the one the trip pays anyway.
-        bool cand = false; uint32_t sc0 = 0, sc1 = 0;
+        bool cand = false; uint32_t sc0 = 0, sc1 = 0; uint64_t slo = 0;
         if (OP == 0 && seed_k) {
             cand = need && !stepwise && lane_seed_ready(L, seed_k, a.ix.n);
-            if (cand) {
-                const uint64_t slo = base + L.j + 1u - seed_k;           // first byte of the window
-                const uint32_t *p = a.codes32 + (slo >> 4);              // bit 2 lo of the code stream
-                sc0 = __ldg(p); sc1 = __ldg(p + 1);
-                need = false;                                             // no run blocks for this lane in this trip
-            }
+            // no branch around the two loads: every lane loads, the others from the start of the code stream (one line for the
+            // whole warp) -- the divergent form ran at 1.9 active threads in three trips out of four
+            slo = cand ? base + L.j + 1u - seed_k : 0ull;                    // first byte of the window
+            const uint32_t *p = a.codes32 + (slo >> 4);                      // bit 2 lo of the code stream
+            sc0 = __ldg(p); sc1 = __ldg(p + 1);
+            need = need && !cand;                                             // no run blocks for a candidate in this trip
         }
         // The symbol comes from the lane's cached 8-byte window of the read. A read of nothing but A / C / G / T (no flag from
         // pack_reads_kernel) is walked through its 2-BIT CODES instead of its bytes: one window then holds 32 symbols instead
@@ -252,15 +258,15 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
         const bool fwd = OP == 0 && L.phase == PH_P2;
         const bool has_sym = need && L.j < L.len;
         const bool by_code = OP == 0 && seed_k != 0 && !(stepwise & 2u);
-        if (has_sym) {
+        {
             const uint64_t o = base + L.j;
-            PGI_CHECK(o < a.reads_bytes);
+            PGI_CHECK(!has_sym || o < a.reads_bytes);
             const uint64_t wi = by_code ? (o >> 5) | (1ull << 63) : o >> 3;           // the tag keeps the two kinds of window apart
-            if (wi != cwi) {
-                const uint64_t *src = by_code ? reinterpret_cast<const uint64_t *>(a.codes32) + (o >> 5) : a.reads64 + (o >> 3);
-                cwi = wi; cw = __ldcs(src);
-                if (L.len > 512) prefetch_l2(src + (fwd ? 16 : -16));                  // long reads: stay ahead in the walking direction
-            }
+            const bool miss = has_sym && wi != cwi;
+            const uint64_t *src = by_code ? reinterpret_cast<const uint64_t *>(a.codes32) + (o >> 5) : a.reads64 + (o >> 3);
+            if (miss) cw = __ldcs(src);
+            cwi = miss ? wi : cwi;
+            if (miss && L.len > 512) prefetch_l2(src + (fwd ? 16 : -16));             // long reads: stay ahead in the walking direction
         }
         auto symbol_of = [&](uint64_t win) -> uint32_t {
             const uint32_t o = (uint32_t) (base + L.j);
@@ -333,17 +339,15 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 const unsigned nb = __popc(__ballot_sync(FULL, b1 != PGI_NOBLK)) + __popc(__ballot_sync(FULL, b2 != PGI_NOBLK));
                 if (lane == 0) s_blk[threadIdx.x >> 5] += nb;
             }
-            bool seed_ok = false;
-            if (OP == 0 && seed_k && __any_sync(FULL, cand)) {
-                if (cand) {
-                    const uint32_t sidx = seed_index_packed(sc0, sc1, base + L.j + 1u - seed_k, seed_k);
-                    PGI_CHECK(sidx < (1u << (2u * seed_k))); PGI_CHECK(base + L.j + 1u >= seed_k && base + L.j < a.reads_bytes);
-                    seed_ok = true;
-                    // destination: the first 16 bytes of the lane's OWN staging slot -- it fetches no run block in this trip
-                    // (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
-                    if (MODE >= 4) cp_async16_ef((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, l2pol);
-                    else cp_async16_if((uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane)), a.seed + sidx, seed_ok ? 0u : PGI_NOBLK);
-                }
+            if (MODE && OP == 0 && seed_k) {
+                // every lane forms an index (a non-candidate from the start of the code stream) and the copy is predicated:
+                // no divergent block. Destination: the first 16 bytes of the lane's OWN staging slot -- a candidate fetches
+                // no run block in this trip (b1 = b2 = PGI_NOBLK, no chunk either), so nobody else writes there
+                const uint32_t sidx = seed_index_packed(sc0, sc1, slo, seed_k);
+                PGI_CHECK(sidx < (1u << (2u * seed_k))); PGI_CHECK(!cand || (base + L.j + 1u >= seed_k && base + L.j < a.reads_bytes));
+                const uint32_t sdst = (uint32_t) __cvta_generic_to_shared(wstage + stage_slot<MODE>(lane));
+                if (MODE >= 4) cp_async16_if_ef(sdst, a.seed + sidx, cand ? 0u : PGI_NOBLK, l2pol);
+                else cp_async16_if(sdst, a.seed + sidx, cand ? 0u : PGI_NOBLK);
             }
             cp_async_wait_all();
             __syncwarp();
@@ -402,15 +406,15 @@ __global__ void __launch_bounds__(THREADS, BPS) fmd_mem_kernel(const MemArgs a) 
                 else { L.b = u; --L.j; }
                 stepwise &= 2u;                               // whatever walk comes next may use the table again
             }
-            if (OP == 0 && cand) {
-                if (seed_ok) {
-                    const uint4 e = wstage[stage_slot<MODE>(lane)];
-                    SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
-                    const BiInt t = seed_unpack(q);
-                    seed_ok = !ext_failed(t, a.min_occ);
-                    if (seed_ok) { lane_seed_apply(L, t, seed_k, min_len); n_ext += seed_k; ++n_seed; }
-                }
-                stepwise = seed_ok ? 0u : 1u;                 // too few occurrences: the walk goes step by step
+            if (OP == 0 && seed_k) {                          // uniform; the candidates take their entry by selects
+                const uint4 e = wstage[stage_slot<MODE>(lane)];
+                SeedWord q; q.x = e.x; q.y = e.y; q.z = e.z; q.w = e.w;
+                const BiInt t = seed_unpack(q);
+                const bool ok = cand && !ext_failed(t, a.min_occ);
+                L.b.k = ok ? t.k : L.b.k; L.b.kp = ok ? t.kp : L.b.kp; L.b.s = ok ? t.s : L.b.s;   // lane_seed_apply
+                L.j = ok ? L.j - seed_k : L.j;
+                n_ext += ok ? seed_k : 0u; n_seed += ok ? 1u : 0u;
+                stepwise = cand ? (ok ? 0u : 1u) : stepwise;  // too few occurrences: the walk goes step by step
             }
             __syncwarp();                                     // the staging area is rewritten by the next trip
         }
