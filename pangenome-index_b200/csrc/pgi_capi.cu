@@ -871,7 +871,11 @@ __global__ void iota_kernel(uint64_t n_plus_1, uint64_t *out) {
 void enqueue_count_stage(pgi_batch *b, int &launches) {
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
     b->d_mem_off.need((n + 1) * 8); b->d_mems.need((n + 1) * 32);
-    void (*fn)(const MemArgs) = fmd_mem_kernel<4, 256, 4, 1>; const unsigned threads = 256;
+    // whole-read backward search (OP 1). Fetch mode 1 is the measured best HERE (4.37 ms per 2 M reads against 5.2 ms for
+    // modes 2 and 4, profiles/r03k: nearly every LF step of a whole-read search ranks two positions in different buckets);
+    // PGI_K1C = 2 / 4 selects the others for tuning runs
+    void (*fn)(const MemArgs) = fmd_mem_kernel<1, 256, 4, 1>; const unsigned threads = 256;
+    if (const char *e = std::getenv("PGI_K1C")) { if (e[0] == '4') fn = fmd_mem_kernel<4, 256, 4, 1>; else if (e[0] == '2') fn = fmd_mem_kernel<2, 256, 4, 1>; }
     const unsigned grid = persistent_grid(ix, fn, threads, n);
     unsigned long long *st = b->d_ctr.as<unsigned long long>();
     CK(cudaMemsetAsync(st, 0, ST_WORDS * 8, b->stream));

@@ -39,8 +39,13 @@ def main():
             if i >= args.warmup: st = batch.stage_ms(); ms.append(st[0]); tot.append(st[5])
             if i == 0:
                 r = batch.device_result(); sig = (int(r.n_mems), int(r.n_tags), int(r.extensions)); blk = int(r.blocks_fetched); sl = int(r.seed_lookups)
+        qt = []
+        for i in range(args.warmup + args.steps):
+            batch.set_device_reads(d_reads[i % pool].data_ptr(), d_off.data_ptr(), n, n * L)
+            batch.run_query_tags()
+            if i >= args.warmup: qt.append(batch.stage_ms()[5])
         if ref is None: ref = sig
-        out[setting] = {"k1_ms_median": round(float(np.median(ms)), 3), "k1_ms_min": round(float(min(ms)), 3), "step_ms_median": round(float(np.median(tot)), 3), "same_counts_as_first": sig == ref,
+        out[setting] = {"k1_ms_median": round(float(np.median(ms)), 3), "k1_ms_min": round(float(min(ms)), 3), "step_ms_median": round(float(np.median(tot)), 3), "query_tags_step_ms": round(float(np.median(qt)), 3), "same_counts_as_first": sig == ref,
                         "blocks_fetched": blk, "seed_lookups": sl, "bucket_shift": ix.info["bucket_shift"], "seed_k": ix.info["seed_k"], "n_dev_blocks": ix.info["n_dev_blocks"],
                         "n_crowded_buckets": ix.info["n_crowded_buckets"], "device_bytes": ix.info["device_bytes"], "index_create_s": round(t_load, 2)}
         print("[sweep]", setting, out[setting], file=sys.stderr, flush=True)
