@@ -970,8 +970,8 @@ __global__ void compact_reads_kernel(uint64_t n_reads, const uint64_t *mem_off, 
     cnt[i] = (uint32_t) c;
 }
 // n_mems = the count, or -- nm_dev != nullptr, launched inside the step -- the capacity, the count being read from device memory
-__global__ void compact_mems_kernel(uint64_t n_mems, const uint64_t *nm_dev, const uint4 *mems, const uint64_t *tag_off, const uint64_t *n_runs, const uint64_t *tags, unsigned tag_bytes,
-                                    uint64_t *rec, uint32_t *runs_tags, uint8_t *ctags, unsigned long long *flags) {
+__global__ void compact_mems_kernel(uint64_t n_mems, const uint64_t *nm_dev, const uint4 *mems, const uint64_t *tag_off, const uint64_t *n_runs,
+                                    uint64_t *rec, uint32_t *runs_tags, unsigned long long *flags) {
     const uint64_t m = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
     if (m >= n_mems || (nm_dev && m >= *nm_dev)) return;
     const uint4 a = mems[2 * m], b = mems[2 * m + 1];
@@ -980,11 +980,26 @@ __global__ void compact_mems_kernel(uint64_t n_mems, const uint64_t *nm_dev, con
     if ((start >> 24) || ((end - start) >> 24) || (k >> 40) || (sz >> 40) || (nt >> 32) || (nr >> 32)) flags[0] = 1ull;
     rec[2 * m] = (k & 0xFFFFFFFFFFull) | start << 40; rec[2 * m + 1] = (sz & 0xFFFFFFFFFFull) | (end - start) << 40;
     runs_tags[2 * m] = (uint32_t) nr; runs_tags[2 * m + 1] = (uint32_t) nt;
-    for (uint64_t t = 0; t < nt; ++t) {
-        const uint64_t v = tags[t0 + t]; uint8_t *d = ctags + (t0 + t) * tag_bytes;
-        if (tag_bytes < 8 && (v >> (8 * tag_bytes))) flags[0] = 1ull;
-        for (unsigned q = 0; q < tag_bytes; ++q) d[q] = (uint8_t) (v >> (8 * q));
-    }
+}
+// The tags of the batch narrowed to tag_bytes (5 or 8) each: one thread per FOUR tags, which are 20 bytes = five aligned
+// 32-bit words in the 5-byte form (the per-MEM loop of byte stores this replaces took a third of the packing time).
+// n_tags = tag_off[nm], nm read from device memory inside a step (nm_dev) or given (nm_host).
+__global__ void compact_tags_kernel(uint64_t cap_groups, const uint64_t *nm_dev, uint64_t nm_host, const uint64_t *tag_off, const uint64_t *tags, unsigned tag_bytes,
+                                    uint32_t *ctags32, unsigned long long *flags) {
+    const uint64_t g = blockIdx.x * (uint64_t) blockDim.x + threadIdx.x;
+    if (g >= cap_groups) return;
+    const uint64_t nt = tag_off[nm_dev ? *nm_dev : nm_host], first = 4 * g;
+    if (first >= nt) return;
+    uint64_t v[4];
+    for (unsigned i = 0; i < 4; ++i) v[i] = first + i < nt ? tags[first + i] : 0ull;
+    if (tag_bytes == 8) { for (unsigned i = 0; i < 4; ++i) if (first + i < nt) reinterpret_cast<uint64_t *>(ctags32)[first + i] = v[i]; return; }
+    if ((v[0] | v[1] | v[2] | v[3]) >> 40) flags[0] = 1ull;
+    uint32_t *d = ctags32 + 5 * g;
+    d[0] = (uint32_t) v[0];
+    d[1] = (uint32_t) ((v[0] >> 32) & 0xFFu) | (uint32_t) (v[1] & 0xFFFFFFu) << 8;
+    d[2] = (uint32_t) ((v[1] >> 24) & 0xFFFFu) | (uint32_t) (v[2] & 0xFFFFu) << 16;
+    d[3] = (uint32_t) ((v[2] >> 16) & 0xFFFFFFu) | (uint32_t) (v[3] & 0xFFu) << 24;
+    d[4] = (uint32_t) (v[3] >> 8);
 }
 
 unsigned compact_tag_bytes(const pgi_index *ix) { return (ix->has_tags && ix->tg.layout == 0 && ix->tg.width <= 40) ? 5u : 8u; }
@@ -996,11 +1011,17 @@ void enqueue_compact(pgi_batch *b, bool with_tags, int &launches) {
     const unsigned tag_bytes = compact_tag_bytes(b->ix);
     unsigned long long *stw = b->d_ctr.as<unsigned long long>();
     b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((cap + 1) * 16); b->d_c_rt.need((cap + 1) * 8);
-    b->d_c_tags.need(((with_tags ? b->raw_cap : 0) + 1) * (uint64_t) tag_bytes);
+    const uint64_t tag_cap = with_tags ? b->raw_cap : 0;
+    b->d_c_tags.need((tag_cap + 1) * (uint64_t) tag_bytes + 32);
     if (n) { compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), stw + ST_NOFIT); ++launches; }
     if (cap) {
         compact_mems_kernel<<<grid_for(cap, 256), 256, 0, st>>>(cap, (const uint64_t *) (stw + ST_NM), b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(),
-                                                                b->d_tags.as<uint64_t>(), tag_bytes, b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), stw + ST_NOFIT);
+                                                                b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), stw + ST_NOFIT);
+        ++launches;
+    }
+    if (tag_cap) {
+        compact_tags_kernel<<<grid_for(tag_cap / 4 + 1, 256), 256, 0, st>>>(tag_cap / 4 + 1, (const uint64_t *) (stw + ST_NM), 0, b->d_tag_off.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes,
+                                                                            b->d_c_tags.as<uint32_t>(), stw + ST_NOFIT);
         ++launches;
     }
     CK(cudaGetLastError());
@@ -1196,12 +1217,13 @@ extern "C" int pgi_batch_fetch_compact(pgi_batch *b, pgi_result_compact *out) {
         const unsigned tag_bytes = compact_tag_bytes(b->ix);
         b->h_c_cnt.need((n + 1) * 4); b->h_c_rec.need((nm + 1) * 16); b->h_c_rt.need((nm + 1) * 8); b->h_c_tags.need((nt + 1) * tag_bytes);
         if (!b->compact_done) {                             // a step run through pgi_batch_run: pack now (pgi_find_mems_compact packs inside the step)
-            b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((nm + 1) * 16); b->d_c_rt.need((nm + 1) * 8); b->d_c_tags.need((nt + 1) * tag_bytes);
+            b->d_c_cnt.need((n + 1) * 4); b->d_c_rec.need((nm + 1) * 16); b->d_c_rt.need((nm + 1) * 8); b->d_c_tags.need((nt + 1) * tag_bytes + 32);
             unsigned long long *flags = b->d_ctr.as<unsigned long long>() + ST_NOFIT;
             CK(cudaMemsetAsync(flags, 0, 8, st));
             if (n) compact_reads_kernel<<<grid_for(n, 256), 256, 0, st>>>(n, b->d_mem_off.as<uint64_t>(), b->d_c_cnt.as<uint32_t>(), flags);
-            if (nm) compact_mems_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, nullptr, b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes,
-                                                                         b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), b->d_c_tags.as<uint8_t>(), flags);
+            if (nm) compact_mems_kernel<<<grid_for(nm, 256), 256, 0, st>>>(nm, nullptr, b->d_mems.as<uint4>(), b->d_tag_off.as<uint64_t>(), b->d_n_runs.as<uint64_t>(),
+                                                                         b->d_c_rec.as<uint64_t>(), b->d_c_rt.as<uint32_t>(), flags);
+            if (nt) compact_tags_kernel<<<grid_for(nt / 4 + 1, 256), 256, 0, st>>>(nt / 4 + 1, nullptr, nm, b->d_tag_off.as<uint64_t>(), b->d_tags.as<uint64_t>(), tag_bytes, b->d_c_tags.as<uint32_t>(), flags);
             CK(cudaGetLastError());
             peek_kernel<<<1, 32, 0, st>>>((const uint64_t *) flags, b->h_ctr.as<uint64_t>() + 12, 1);
         }
