@@ -514,7 +514,7 @@ def main():
         import hashlib as _h
         hh = _h.sha256()
         for f in sorted(os.listdir(os.path.join(ROOT, "pangenome-index_b200", "csrc"))):
-            if f.endswith((".cuh", ".cu", ".h", ".hpp")): hh.update(open(os.path.join(ROOT, "pangenome-index_b200", "csrc", f), "rb").read())
+            if f in ("pgi_kernels.cuh", "pgi_core.cuh", "pgi_layout.h"): hh.update(open(os.path.join(ROOT, "pangenome-index_b200", "csrc", f), "rb").read())
         tj = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
         for e in tj:
             if e["csrc_sha256"] == hh.hexdigest() and e["workload"] == args.workload and e["nominal"] == args.nominal and e["reads_per_step"] == n:

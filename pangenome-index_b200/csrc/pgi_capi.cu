@@ -768,15 +768,19 @@ uint64_t read_back(pgi_batch *b, const void *dptr) {              // locate only
 
 // K1 instantiations: block-fetch mode x CTA shape (pgi_kernels.cuh). PGI_K1=<name> picks one for tuning runs
 // (e.g. PGI_K1=04 is the lane-private fetch, 256 threads x 4 CTAs per SM); the default is the measured best.
+// Default: mode 4 (padded staging + L2 evict-first hint) for an index whose run blocks live in DRAM -- config 4: 7.62 ms
+// against 7.79 ms for mode 1 -- but mode 1 for one whose run blocks fit the L2: there the kernel is bound by issue / shared
+// memory, not by DRAM, and the padded staging costs 2.3 x (shipped xy index, 1 M reads: 2.79 ms against 6.45 ms, profiles/r03o).
+#define PGI_K1_HOT_INDEX_BYTES (64ull << 20)
 struct K1Variant { const char *name; void (*fn)(const MemArgs); unsigned threads; };
-const K1Variant &k1_variant() {
-    static const K1Variant table[] = {          // first = default: the measured best (tools/k1_sweep.py, profiles/r01f_k1_sweep.json)
+const K1Variant &k1_variant(const pgi_index *ix) {
+    static const K1Variant table[] = {          // first = default for DRAM-resident indexes (tools/k1_sweep.py, tools/index_sweep.py)
         {"44", fmd_mem_kernel<4, 256, 4>, 256}, {"24", fmd_mem_kernel<2, 256, 4>, 256}, {"14", fmd_mem_kernel<1, 256, 4>, 256}, {"1a", fmd_mem_kernel<1, 128, 8>, 128}, {"1b", fmd_mem_kernel<1, 128, 9>, 128},
         {"15", fmd_mem_kernel<1, 256, 5>, 256}, {"04", fmd_mem_kernel<0, 256, 4>, 256}, {"2a", fmd_mem_kernel<2, 128, 8>, 128},
     };
     const char *e = std::getenv("PGI_K1");                  // read per call: tools/k1_sweep.py switches variants in one process
     if (e) for (const K1Variant &v : table) if (!std::strcmp(v.name, e)) return v;
-    return table[0];
+    return ix->n_block_words * 8ull <= PGI_K1_HOT_INDEX_BYTES ? table[2] : table[0];
 }
 
 // The persistent grid is sized for the occupancy the kernel's static shared memory allows (4 CTAs x 43 KB per SM). With the
@@ -813,7 +817,7 @@ void enqueue_mem_stage(pgi_batch *b, uint64_t min_len, uint64_t min_occ, int &la
     pgi_index *ix = b->ix; const uint64_t n = b->n_reads;
     b->d_nmems.need((n + 1) * 8); b->d_mem_off.need((n + 1) * 8);
     const uint64_t cap = std::max<uint64_t>(1024, b->mem_cap_hint ? b->mem_cap_hint : (uint64_t) ((double) n * b->mems_per_read * 1.25) + 1024);
-    const K1Variant &k1 = k1_variant();
+    const K1Variant &k1 = k1_variant(ix);
     const unsigned grid = persistent_grid(ix, k1.fn, k1.threads, n);
     unsigned long long *st = b->d_ctr.as<unsigned long long>();
     if (ix->seed_k && n) {                                   // K0: 2-bit codes + per-read flags for the seed lookups

@@ -544,3 +544,22 @@ def test_async_steps_overlap_and_compact_in_step(capi):
     finally:
         if old is None: os.environ.pop("PGI_CHAIN", None)
         else: os.environ["PGI_CHAIN"] = old
+
+@pytest.mark.parametrize("variant", ["44", "24", "14", "04"])
+def test_find_mems_forced_kernel_variants(capi, variant):
+    """Every block-fetch mode of fmd_mem_kernel (PGI_K1; the default is chosen by index size: mode 1 for an L2-resident
+    index, mode 4 otherwise) returns the oracle's MEMs, tags and extension count on the synthetic and the shipped indexes."""
+    import os
+    old = os.environ.get("PGI_K1"); os.environ["PGI_K1"] = variant
+    try:
+        for name in ("synth_enc_compact", "xy_legacy_bytecode", "x_encoded_sigma5"):
+            c = get_case(name)
+            o = orc.Index(c["ri"], c["tags"], c["layout"]); g = capi.Index(c["ri"], c["tags"], c["layout"])
+            reads, off = datasets.sample_reads(c["text"], 3000, 150, 0.02, seed=17)
+            for ml, mo in ((20, 1), (5, 2)):
+                G = g.find_mems(reads, off, ml, mo); R = o.find_mems(reads, off, ml, mo, count_work=True)
+                compare(G, R, c["tags"] is not None)
+                assert G["extensions"] == R["counters"]["E"]
+    finally:
+        if old is None: os.environ.pop("PGI_K1", None)
+        else: os.environ["PGI_K1"] = old

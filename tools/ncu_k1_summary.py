@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """Summarise an `ncu --set full` capture of fmd_mem_kernel: writes profiles/<tag>_fmd_mem_kernel_raw.txt (selected raw
-metrics, per launch) and records the DRAM bytes per launch in profiles/k1_traffic.json keyed by the SHA-256 of csrc/ (bench.py
+metrics, per launch) and records the DRAM bytes per launch in profiles/k1_traffic.json keyed by the SHA-256 of the files that
+define fmd_mem_kernel and its data layout (csrc/pgi_kernels.cuh, pgi_core.cuh, pgi_layout.h; bench.py
 quotes `roofline.traffic` only from an entry whose hash matches the kernel it is running).
 usage: tools/ncu_k1_summary.py report.ncu-rep tag workload reads_per_step [nominal=1]"""
 import csv, hashlib, io, json, os, subprocess, sys
@@ -27,7 +28,7 @@ def to_bytes(k):
     return sum(float(r[i]) for r in data) / len(data) * mul
 hh = hashlib.sha256(); d = os.path.join(ROOT, "pangenome-index_b200", "csrc")
 for f in sorted(os.listdir(d)):
-    if f.endswith((".cuh", ".cu", ".h", ".hpp")): hh.update(open(os.path.join(d, f), "rb").read())
+    if f in ("pgi_kernels.cuh", "pgi_core.cuh", "pgi_layout.h"): hh.update(open(os.path.join(d, f), "rb").read())
 p = os.path.join(ROOT, "profiles", "k1_traffic.json")
 tj = json.load(open(p)) if os.path.exists(p) else []
 tj = [e for e in tj if not (e["csrc_sha256"] == hh.hexdigest() and e["workload"] == workload and e["reads_per_step"] == reads)]
