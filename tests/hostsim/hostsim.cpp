@@ -123,6 +123,15 @@ uint64_t sim_trace_read(uint64_t *out, uint64_t cap) {
     if (out) std::memcpy(out, g_trace->data(), n * 8);
     return g_trace->size();
 }
+// Header arithmetic alone: a block with the six counts cnt[] before it and no runs, ranked at offset 0 with the descriptor
+// fields tbl (pos_rank's limb dot products against Python's big integers, up to the 40-bit / 32-bit limits of the layout).
+void sim_header_sums(const uint64_t *cnt, uint32_t tbl, uint64_t *WM) {
+    uint32_t w[16]; for (int i = 0; i < 16; ++i) w[i] = 0;
+    w[8] = 0x7777u << 16; w[9] = 0x77777777u;                           // twelve unused runs
+    pgi_put_header(w, cnt);
+    const PosRank r = pos_rank(w, 0u, tbl, scan_tab(tbl));
+    WM[0] = r.W; WM[1] = r.M;
+}
 // one block as 16 u32 words (tools)
 void sim_block(const sim_index *s, uint64_t b, uint32_t *w16) { for (int i = 0; i < 8; ++i) { w16[2 * i] = (uint32_t) s->ri.blocks[b * 8 + i]; w16[2 * i + 1] = (uint32_t) (s->ri.blocks[b * 8 + i] >> 32); } }
 // Whole-read backward search through the count descriptors (desc_c) and extend_desc, as fmd_mem_kernel's OP 1 does:

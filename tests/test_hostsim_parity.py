@@ -168,3 +168,23 @@ def test_forced_bucket_shift(shift, monkeypatch):
         for i in range(60):
             mems, ne = g.find_mems(reads[int(off[i]):int(off[i + 1])].tobytes(), 12, 1)
             assert np.array_equal(mems, R["mems"][int(R["mem_off"][i]):int(R["mem_off"][i + 1])]), i
+
+def test_header_limb_sums_at_the_limits_of_the_layout():
+    """pos_rank's header arithmetic (counts stored as 16-bit limbs, weighted sums as dp2a / dp4a against the descriptor's byte
+    tables) against plain integer arithmetic: random and extreme counts up to 2^40 - 1 (A, C, G, T) / 2^32 - 1 (NL, N), every
+    weight 0..7, every position of the main flag."""
+    import ctypes, sim
+    L = sim.lib(); L.sim_header_sums.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_void_p]
+    rng = np.random.default_rng(5)
+    lim = [(1 << 32) - 1, (1 << 40) - 1, (1 << 40) - 1, (1 << 40) - 1, (1 << 32) - 1, (1 << 40) - 1]     # code order: NL A C G N T
+    out = np.zeros(2, dtype=np.uint64)
+    cases = [np.array(lim, dtype=np.uint64), np.zeros(6, dtype=np.uint64), np.array([1, 1 << 16, 1 << 32, (1 << 32) - 1, 1 << 31, (1 << 39) + 12345], dtype=np.uint64)]
+    cases += [np.array([int(rng.integers(0, l + 1)) for l in lim], dtype=np.uint64) for _ in range(400)]
+    for k, cnt in enumerate(cases):
+        wts = [7] * 6 if k == 0 else [int(x) for x in rng.integers(0, 8, 6)]
+        main = int(rng.integers(0, 7))                                   # 6: no main symbol
+        tbl = 0
+        for c in range(6): tbl |= (wts[c] | (8 if c == main else 0)) << (4 * c)
+        L.sim_header_sums(cnt.ctypes.data, tbl, out.ctypes.data)
+        W = sum(int(cnt[c]) * wts[c] for c in range(6)); M = int(cnt[main]) if main < 6 else 0
+        assert int(out[0]) == W % (1 << 64) and int(out[1]) == M, (k, cnt, wts, main)
